@@ -1,0 +1,171 @@
+// host/gpu_path_integrator.cpp -- Integrator "path" on the B200.
+//
+// Product host code.  Implements the reference's Integrator interface
+// (src/core/integrator.h:53-58: `virtual void Render(const Scene &)`) on top of
+// the C ABI in include/sptx.h: flatten the parsed scene, upload, render every
+// sample on the device, read the spectral film back and hand it to the
+// reference's own Film::WriteImage (src/core/film.cpp:180-310), so the .dat /
+// .exr writers and everything before WorldEnd stay the reference's host C++.
+//
+// Binding.  The reference resolves integrator names in a static if-chain
+// (RenderOptions::MakeIntegrator, src/core/api.cpp:1750-1771: name == "path"
+// -> CreatePathIntegrator).  A maintainer adds one branch there
+// (INTEGRATION.md).  This in-place build does not edit the reference: it
+// defines pbrt::CreatePathIntegrator itself and links ahead of the archive, so
+// the CPU PathIntegrator object is never pulled in.  There is no CPU fallback:
+// if the device path fails, Render reports the error and aborts.
+#include <algorithm>
+#include <chrono>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <fstream>
+#include <functional>
+#include <iostream>
+#include <limits>
+#include <map>
+#include <memory>
+#include <mutex>
+#include <sstream>
+#include <string>
+#include <vector>
+#include <glog/logging.h>
+
+#define private public
+#define protected public
+#include "camera.h"
+#include "film.h"
+#include "integrator.h"
+#include "integrators/path.h"
+#include "paramset.h"
+#include "sampler.h"
+#include "scene.h"
+#include "spectrum.h"
+#undef private
+#undef protected
+
+#include "error.h"
+#include "flatten.h"
+#include "sptx.h"
+
+namespace pbrt {
+
+class GpuPathIntegrator : public Integrator {
+  public:
+    GpuPathIntegrator(const sptx_host::PathParams &params,
+                      std::shared_ptr<const Camera> camera,
+                      std::shared_ptr<Sampler> sampler)
+        : params(params), camera(camera), sampler(sampler) {}
+    void Render(const Scene &scene) override;
+
+  private:
+    sptx_host::PathParams params;
+    std::shared_ptr<const Camera> camera;
+    std::shared_ptr<Sampler> sampler;
+};
+
+static void Die(sptx_ctx *ctx, const char *what) {
+    // No CPU fallback (north star): a failed device path is fatal, reported
+    // the way the reference reports unrecoverable errors.
+    Error("GpuPathIntegrator: %s failed: %s", what, sptx_last_error(ctx));
+    std::exit(1);
+}
+
+void GpuPathIntegrator::Render(const Scene &scene) {
+    sptx_host::FlatScene flat;
+    std::string err;
+    if (!sptx_host::FlattenScene(scene, *camera, *sampler, params, &flat,
+                                 &err)) {
+        Error("GpuPathIntegrator: scene is outside the GPU hot path: %s",
+              err.c_str());
+        std::exit(1);
+    }
+    if (const char *dump = std::getenv("SPTX_DUMP_SCENE")) {
+        if (sptx_scene_save(dump, &flat.desc) != 0) Die(nullptr, "scene save");
+        if (std::getenv("SPTX_DUMP_ONLY")) return;
+    }
+
+    int device = 0;
+    if (const char *d = std::getenv("SPTX_DEVICE")) device = std::atoi(d);
+    sptx_ctx *ctx = nullptr;
+    if (sptx_create(device, &ctx) != 0) Die(nullptr, "sptx_create");
+    if (sptx_upload_scene(ctx, &flat.desc) != 0) Die(ctx, "sptx_upload_scene");
+    if (sptx_film_clear(ctx) != 0) Die(ctx, "sptx_film_clear");
+    auto t0 = std::chrono::steady_clock::now();
+    if (sptx_render(ctx, nullptr, 0, (int)sampler->samplesPerPixel) != 0)
+        Die(ctx, "sptx_render");
+    auto t1 = std::chrono::steady_clock::now();
+
+    // Film pixels back into the reference's Film, then its own writer.
+    Film *film = camera->film;
+    Bounds2i cb = film->croppedPixelBounds;
+    int w = cb.pMax.x - cb.pMin.x, h = cb.pMax.y - cb.pMin.y;
+    size_t nPix = (size_t)std::max(0, w) * std::max(0, h);
+    std::vector<float> contrib(nPix * SPTX_NBINS), weight(nPix);
+    if (sptx_film_download(ctx, contrib.data(), weight.data()) != 0)
+        Die(ctx, "sptx_film_download");
+    for (size_t i = 0; i < nPix; ++i) {
+        Film::Pixel &px = film->pixels[i];
+        Spectrum L;
+        for (int b = 0; b < SPTX_NBINS; ++b) L[b] = contrib[i * SPTX_NBINS + b];
+        // MergeFilmTile (src/core/film.cpp:124-142): XYZ for the RGB writer,
+        // the raw spectrum for the spectral one.
+        Float xyz[3];
+        L.ToXYZ(xyz);
+        for (int c = 0; c < 3; ++c) px.xyz[c] += xyz[c];
+        px.filterWeightSum += weight[i];
+        if (film->spectralFlag) px.L += L;
+    }
+    sptx_counters c;
+    std::memset(&c, 0, sizeof(c));
+    sptx_get_counters(ctx, &c);
+    double wall = std::chrono::duration<double>(t1 - t0).count();
+    double nSamples = (double)c.camera_rays;
+    fprintf(stderr,
+            "GpuPathIntegrator: %.0f camera samples, %.3f s device "
+            "(%.2f Msamples/s), %.3f s wall; rays: %llu closest-hit, %llu "
+            "shadow\n",
+            nSamples, c.render_ms * 1e-3,
+            c.render_ms > 0 ? nSamples / (c.render_ms * 1e3) : 0.0, wall,
+            (unsigned long long)c.closest_hit_rays,
+            (unsigned long long)c.shadow_rays);
+    sptx_destroy(ctx);
+    film->WriteImage();
+}
+
+// Same parameter handling as the reference factory
+// (src/integrators/path.cpp:190-213).  The return type is dictated by the
+// declaration api.cpp was compiled against; api.cpp only ever converts the
+// result to Integrator* (a no-op for single inheritance).
+PathIntegrator *CreatePathIntegrator(const ParamSet &params,
+                                     std::shared_ptr<Sampler> sampler,
+                                     std::shared_ptr<const Camera> camera) {
+    sptx_host::PathParams pp;
+    pp.maxDepth = params.FindOneInt("maxdepth", 5);
+    int np;
+    const int *pb = params.FindInt("pixelbounds", &np);
+    Bounds2i pixelBounds = camera->film->GetSampleBounds();
+    if (pb) {
+        if (np != 4)
+            Error("Expected four values for \"pixelbounds\" parameter. Got %d.",
+                  np);
+        else {
+            pixelBounds = Intersect(pixelBounds,
+                                    Bounds2i{{pb[0], pb[2]}, {pb[1], pb[3]}});
+            if (pixelBounds.Area() == 0)
+                Error("Degenerate \"pixelbounds\" specified.");
+        }
+    }
+    pp.pixelBounds[0] = pixelBounds.pMin.x;
+    pp.pixelBounds[1] = pixelBounds.pMin.y;
+    pp.pixelBounds[2] = pixelBounds.pMax.x;
+    pp.pixelBounds[3] = pixelBounds.pMax.y;
+    pp.rrThreshold = params.FindOneFloat("rrthreshold", 1.);
+    pp.lightSampleStrategy =
+        params.FindOneString("lightsamplestrategy", "spatial");
+    Integrator *gpu = new GpuPathIntegrator(pp, camera, sampler);
+    return reinterpret_cast<PathIntegrator *>(gpu);
+}
+
+}  // namespace pbrt

@@ -1,13 +1,13 @@
-// oracle/shim/glog/logging.h -- TEST INFRASTRUCTURE ONLY.
+// host/shim/glog/logging.h -- build shim (not part of the GPU core).
 //
 // Minimal stand-in for <glog/logging.h> so that the reference's own source
-// files (compiled in place from /root/reference by oracle/Makefile) build
+// files (compiled in place from /root/reference by host/Makefile) build
 // without glog's cmake-generated headers.  It implements only the macro
 // surface the reference uses: LOG(sev), VLOG(n), CHECK*/DCHECK*, the FLAGS_*
 // globals touched by src/main/pbrt.cpp:78-132 and google::InitGoogleLogging.
-// Nothing here is product code.
-#ifndef SPTX_ORACLE_GLOG_SHIM_H
-#define SPTX_ORACLE_GLOG_SHIM_H
+// It carries no path arithmetic.
+#ifndef SPTX_GLOG_SHIM_H
+#define SPTX_GLOG_SHIM_H
 
 #include <cstdlib>
 #include <iostream>
@@ -18,7 +18,7 @@ namespace sptx_glog_shim {
 
 enum Severity { INFO = 0, WARNING = 1, ERROR = 2, FATAL = 3 };
 
-extern int min_log_level;  // defined in oracle/shim/shim_stubs.cpp
+extern int min_log_level;  // defined in host/shim/shim_stubs.cpp
 
 class Message {
   public:
@@ -118,4 +118,4 @@ extern std::string FLAGS_log_dir;
 #define DCHECK_GE(a, b) CHECK_GE(a, b)
 #endif
 
-#endif  // SPTX_ORACLE_GLOG_SHIM_H
+#endif  // SPTX_GLOG_SHIM_H

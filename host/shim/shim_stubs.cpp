@@ -1,6 +1,6 @@
-// oracle/shim/shim_stubs.cpp -- TEST INFRASTRUCTURE ONLY.
+// host/shim/shim_stubs.cpp -- build shim for compiling the reference front end in place.
 //
-// Link-time stand-ins for the pieces of the reference that oracle/Makefile
+// Link-time stand-ins for the pieces of the reference that host/Makefile
 // does NOT compile because they need libraries absent from this image:
 //   * src/cameras/omni.cpp, src/cameras/realisticEye.cpp  (GSL)
 //   * src/textures/ptex.cpp                               (Ptex)
@@ -38,37 +38,37 @@ namespace pbrt {
 
 OmniCamera *CreateOmniCamera(const ParamSet &, const AnimatedTransform &,
                              Film *, const Medium *) {
-    Error("Camera \"omni\" needs GSL: not built into the oracle.");
+    Error("Camera \"omni\" needs GSL: not built into this in-place build.");
     return nullptr;
 }
 
 RealisticEye *CreateRealisticEye(const ParamSet &, const AnimatedTransform &,
                                  Film *, const Medium *) {
-    Error("Camera \"realisticEye\" needs GSL: not built into the oracle.");
+    Error("Camera \"realisticEye\" needs GSL: not built into this in-place build.");
     return nullptr;
 }
 
 PtexTexture<Float> *CreatePtexFloatTexture(const Transform &,
                                            const TextureParams &) {
-    Error("Ptex textures are not built into the oracle.");
+    Error("Ptex textures are not built into this in-place build.");
     return nullptr;
 }
 
 PtexTexture<Spectrum> *CreatePtexSpectrumTexture(const Transform &,
                                                  const TextureParams &) {
-    Error("Ptex textures are not built into the oracle.");
+    Error("Ptex textures are not built into this in-place build.");
     return nullptr;
 }
 
 std::unique_ptr<RGBSpectrum[]> ReadImage(const std::string &name, Point2i *) {
-    Error("ReadImage(\"%s\"): image reading is not built into the oracle.",
+    Error("ReadImage(\"%s\"): image reading is not built into this in-place build.",
           name.c_str());
     return nullptr;
 }
 
 RGBSpectrum *ReadImageEXR(const std::string &name, int *, int *, Bounds2i *,
                           Bounds2i *) {
-    Error("ReadImageEXR(\"%s\"): OpenEXR is not built into the oracle.",
+    Error("ReadImageEXR(\"%s\"): OpenEXR is not built into this in-place build.",
           name.c_str());
     return nullptr;
 }

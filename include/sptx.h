@@ -1,0 +1,360 @@
+/* sptx.h -- C ABI of the B200 spectral path-tracing core.
+ *
+ * This is the drop-in boundary for pbrt-v3-spectral's PathIntegrator hot path.
+ * The reference has no FFI: `pbrtWorldEnd` calls `Integrator::Render(scene)`
+ * in-process (reference src/core/api.cpp:1695-1707, src/core/integrator.h:53-58).
+ * The host C++ layer (host/gpu_path_integrator.cpp) implements that interface,
+ * flattens the reference's scene graph into the POD tables below and drives
+ * these entry points.  Every struct is plain data: no C++ types, no torch
+ * types, pointers + counts only.  All functions return 0 on success and a
+ * non-zero SPTX_E* code on failure; nothing throws across this boundary.
+ *
+ * Arithmetic conventions (needed for parity with the reference's x86-64 build,
+ * CMakeLists.txt:73-76: -O3, no FMA contraction): all device math is IEEE
+ * float32 with fused multiply-add DISABLED, double where the reference uses
+ * double (Cross, Quadratic, triangle edge fallback).
+ */
+#ifndef SPTX_H
+#define SPTX_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SPTX_NBINS 31          /* nSpectralSamples, src/core/spectrum.h:50 */
+#define SPTX_SPECTRUM_STRIDE 32 /* floats per row of the spectra table (128 B) */
+#define SPTX_FILTER_TABLE_WIDTH 16 /* Film::filterTableWidth, src/core/film.h:98 */
+#define SPTX_ABI_VERSION 1
+
+/* ---- error codes ------------------------------------------------------- */
+enum {
+    SPTX_OK = 0,
+    SPTX_EINVAL = 1,       /* bad argument / malformed scene tables          */
+    SPTX_ECUDA = 2,        /* CUDA runtime error (see sptx_last_error)       */
+    SPTX_EUNSUPPORTED = 3, /* scene uses a feature outside the hot path      */
+    SPTX_ENOMEM = 4,
+    SPTX_EIO = 5,
+    SPTX_ESTATE = 6        /* call order (e.g. render before upload)         */
+};
+
+/* ---- geometry tables ---------------------------------------------------- */
+
+/* Bit-identical to LinearBVHNode, src/accelerators/bvh.cpp:95-104 (32 B). */
+typedef struct sptx_bvh_node {
+    float bmin[3];
+    float bmax[3];
+    int32_t offset;   /* leaf: primitivesOffset; interior: secondChildOffset */
+    uint16_t n_prims; /* 0 -> interior                                        */
+    uint8_t axis;
+    uint8_t pad;
+} sptx_bvh_node;
+
+/* One BVHAccel.  bvhs[0] is the scene aggregate; the others are the nested
+ * aggregates object instances point at (src/core/api.cpp:1590-1613).
+ * Node and primitive offsets stored inside nodes are relative to the bases. */
+typedef struct sptx_bvh {
+    int32_t node_base;
+    int32_t n_nodes;
+    int32_t prim_base;
+    int32_t n_prims;
+} sptx_bvh;
+
+enum { SPTX_PRIM_TRIANGLE = 0, SPTX_PRIM_SPHERE = 1, SPTX_PRIM_INSTANCE = 2 };
+
+/* Entry of BVHAccel::primitives (post-build order).  GeometricPrimitive binds
+ * shape+material+areaLight (src/core/primitive.cpp:119-152);
+ * TransformedPrimitive is an instance (src/core/primitive.cpp:78-99). */
+typedef struct sptx_prim {
+    int32_t kind;     /* SPTX_PRIM_*                                         */
+    int32_t shape;    /* index into triangles / spheres / instances          */
+    int32_t material; /* index into materials, -1 = none                     */
+    int32_t light;    /* index into lights (area light), -1 = none           */
+} sptx_prim;
+
+/* TriangleMesh, src/shapes/triangle.h:51-69 (positions are world space). */
+typedef struct sptx_mesh {
+    int32_t p_base;  /* first vertex of this mesh in positions[]             */
+    int32_t n_base;  /* first normal in normals[], -1 if the mesh has none   */
+    int32_t s_base;  /* first tangent in tangents[], -1 if none              */
+    int32_t uv_base; /* first uv in uvs[], -1 if none                        */
+    int32_t flip;    /* reverseOrientation ^ transformSwapsHandedness        */
+    int32_t n_vertices;
+} sptx_mesh;
+
+typedef struct sptx_triangle {
+    int32_t v[3]; /* mesh-local vertex indices                               */
+    int32_t mesh;
+} sptx_triangle;
+
+/* Sphere, src/shapes/sphere.h.  Matrices are row-major m[r][c]. */
+typedef struct sptx_sphere {
+    float o2w[16];     /* ObjectToWorld->m                                   */
+    float w2o[16];     /* ObjectToWorld->mInv (== WorldToObject->m)          */
+    float radius, z_min, z_max, theta_min, theta_max, phi_max;
+    int32_t reverse_orientation;
+    int32_t swaps_handedness;
+} sptx_sphere;
+
+typedef struct sptx_instance {
+    float p2w[16]; /* PrimitiveToWorld.m (static transforms only)            */
+    float w2p[16]; /* its inverse (mInv)                                      */
+    int32_t bvh;   /* index into bvhs[]                                       */
+    int32_t instance_id;
+    int32_t is_identity;
+    int32_t pad;
+} sptx_instance;
+
+/* ---- shading tables ------------------------------------------------------ */
+
+enum {
+    SPTX_LOBE_LAMBERT = 0,         /* LambertianReflection                   */
+    SPTX_LOBE_OREN_NAYAR = 1,      /* OrenNayar (A, B precomputed)           */
+    SPTX_LOBE_SPECULAR_REFL = 2,   /* SpecularReflection                     */
+    SPTX_LOBE_SPECULAR_TRANS = 3,  /* SpecularTransmission                   */
+    SPTX_LOBE_FRESNEL_SPECULAR = 4,/* FresnelSpecular                        */
+    SPTX_LOBE_MICROFACET_REFL = 5  /* MicrofacetReflection + TrowbridgeReitz */
+};
+enum { SPTX_FRESNEL_NOOP = 0, SPTX_FRESNEL_DIELECTRIC = 1, SPTX_FRESNEL_CONDUCTOR = 2 };
+
+/* One BxDF of the BSDF a material builds for constant textures
+ * (src/materials/{matte,plastic,glass,metal,mirror}.cpp).  Spectra are row
+ * indices into spectra[] (already clamped the way the material clamps them). */
+typedef struct sptx_lobe {
+    int32_t type;    /* SPTX_LOBE_*                                          */
+    int32_t fresnel; /* SPTX_FRESNEL_* for SPECULAR_REFL / MICROFACET_REFL   */
+    int32_t R;       /* reflectance spectrum row, -1 if unused               */
+    int32_t T;       /* transmittance spectrum row, -1 if unused             */
+    int32_t fr_eta_i, fr_eta_t, fr_k; /* conductor Fresnel spectra rows      */
+    float eta_a, eta_b;   /* dielectric: Fresnel etaI/etaT or lobe etaA/etaB */
+    float alpha_x, alpha_y; /* Trowbridge-Reitz alphas (after remap)         */
+    float A, B;             /* Oren-Nayar                                    */
+    int32_t sample_visible; /* MicrofacetDistribution::sampleVisibleArea     */
+} sptx_lobe;
+
+typedef struct sptx_material {
+    int32_t first_lobe;
+    int32_t n_lobes; /* <= 8, BSDF::MaxBxDFs, src/core/reflection.h:199      */
+    float eta;       /* BSDF::eta                                            */
+    int32_t material_id;
+} sptx_material;
+
+enum { SPTX_LIGHT_DIFFUSE_AREA = 0, SPTX_LIGHT_POINT = 1 };
+
+/* DiffuseAreaLight (src/lights/diffuse.cpp) or PointLight (src/lights/point.cpp). */
+typedef struct sptx_light {
+    int32_t type;
+    int32_t shape_kind; /* SPTX_PRIM_TRIANGLE / SPTX_PRIM_SPHERE (area)      */
+    int32_t shape;      /* triangle / sphere index                           */
+    int32_t two_sided;
+    int32_t spectrum;   /* Lemit (area) or I (point) row in spectra[]        */
+    float area;         /* shape->Area() as the reference computed it        */
+    float pos[3];       /* point light position                              */
+} sptx_light;
+
+/* ---- sensor -------------------------------------------------------------- */
+
+enum { SPTX_CAMERA_PERSPECTIVE = 0, SPTX_CAMERA_REALISTIC = 1 };
+
+typedef struct sptx_camera {
+    int32_t type;
+    float raster_to_camera[16]; /* ProjectiveCamera::RasterToCamera.m         */
+    float camera_to_world[16];  /* CameraToWorld start transform .m           */
+    float lens_radius, focal_distance;
+    float shutter_open, shutter_close;
+    /* RealisticCamera (src/cameras/realistic.cpp) */
+    int32_t n_elements;      /* rows of lens_elements[] (4 floats each)       */
+    int32_t n_pupil_bounds;  /* rows of exit_pupil_bounds[] (4 floats each)   */
+    int32_t simple_weighting;
+    int32_t ca_flag;         /* chromaticAberrationEnabled                    */
+    float film_diagonal;     /* Film::diagonal (metres)                       */
+    float pad[3];
+} sptx_camera;
+
+enum { SPTX_SAMPLER_HALTON = 0, SPTX_SAMPLER_RANDOM = 1 };
+
+/* HaltonSampler state, src/samplers/halton.cpp:65-92. */
+typedef struct sptx_sampler {
+    int32_t type;
+    int32_t spp;
+    int32_t sample_at_center;
+    int32_t base_scales[2];
+    int32_t base_exponents[2];
+    int32_t sample_stride;
+    int32_t mult_inverse[2];
+    int32_t n_dims; /* dimensions covered by primes[]/prime_sums[]/perms[]    */
+    int32_t pad;
+} sptx_sampler;
+
+/* Film, src/core/film.cpp:50-92. Bounds are {x0, y0, x1, y1}. */
+typedef struct sptx_film {
+    int32_t full_res[2];
+    int32_t cropped[4];       /* croppedPixelBounds                           */
+    int32_t sample_bounds[4]; /* GetSampleBounds()                            */
+    float filter_radius[2];
+    float filter_table[SPTX_FILTER_TABLE_WIDTH * SPTX_FILTER_TABLE_WIDTH];
+    float max_sample_luminance;
+    float scale;
+    float diagonal;
+    int32_t spectral_flag;
+} sptx_film;
+
+enum { SPTX_LIGHTS_UNIFORM = 0, SPTX_LIGHTS_POWER = 1, SPTX_LIGHTS_SPATIAL = 2 };
+
+/* PathIntegrator parameters, src/integrators/path.cpp:190-213. */
+typedef struct sptx_integrator {
+    int32_t max_depth;
+    float rr_threshold;
+    int32_t pixel_bounds[4];
+    int32_t light_strategy; /* as named in the scene file; the 1-light       */
+                            /* fallback to uniform is applied by the core     */
+    int32_t pad;
+} sptx_integrator;
+
+/* Everything Render() needs, as flat host arrays.  The caller keeps ownership
+ * and may free the arrays once sptx_upload_scene returns. */
+typedef struct sptx_scene_desc {
+    uint32_t abi_version;
+    uint32_t reserved;
+    sptx_camera camera;
+    sptx_sampler sampler;
+    sptx_film film;
+    sptx_integrator integrator;
+    float cie_y[SPTX_SPECTRUM_STRIDE]; /* SampledSpectrum::Y                  */
+    float cie_y_integral;               /* CIE_Y_integral, spectrum.h:87       */
+    int32_t pad0;
+
+    int64_t n_nodes;      const sptx_bvh_node *nodes;
+    int64_t n_bvhs;       const sptx_bvh *bvhs;
+    int64_t n_prims;      const sptx_prim *prims;
+    int64_t n_meshes;     const sptx_mesh *meshes;
+    int64_t n_triangles;  const sptx_triangle *triangles;
+    int64_t n_positions;  const float *positions; /* xyz                      */
+    int64_t n_normals;    const float *normals;   /* xyz                      */
+    int64_t n_tangents;   const float *tangents;  /* xyz                      */
+    int64_t n_uvs;        const float *uvs;       /* uv                       */
+    int64_t n_spheres;    const sptx_sphere *spheres;
+    int64_t n_instances;  const sptx_instance *instances;
+    int64_t n_materials;  const sptx_material *materials;
+    int64_t n_lobes;      const sptx_lobe *lobes;
+    int64_t n_spectra;    const float *spectra;   /* rows of 32 floats        */
+    int64_t n_lights;     const sptx_light *lights;
+    int64_t n_lens_floats;  const float *lens_elements;     /* 4 per element  */
+    int64_t n_pupil_floats; const float *exit_pupil_bounds; /* 4 per bound    */
+    int64_t n_primes;     const int32_t *primes;     /* Primes[0..n_dims)     */
+    int64_t n_prime_sums; const int32_t *prime_sums; /* PrimeSums[0..n_dims)  */
+    int64_t n_perms;      const uint16_t *perms; /* radicalInversePermutations */
+} sptx_scene_desc;
+
+/* ---- ray batches (parity test #1 and the traversal benchmark) ----------- */
+
+typedef struct sptx_ray {
+    float o[3];
+    float t_max;
+    float d[3];
+    float time;
+} sptx_ray; /* 32 B */
+
+typedef struct sptx_hit {
+    int32_t prim;     /* global index into prims[] of the hit primitive, -1 = miss */
+    int32_t instance; /* index into instances[] of the enclosing instance, -1 = none */
+    float t;          /* ray.tMax after the traversal                         */
+    float b0, b1, b2; /* triangle barycentrics at the hit (0 for spheres)     */
+    int32_t n_nodes;  /* BVH nodes visited (only when counters are enabled)   */
+    int32_t n_tests;  /* primitive tests made (only when counters are enabled) */
+} sptx_hit; /* 32 B */
+
+typedef struct sptx_counters {
+    uint64_t camera_rays;
+    uint64_t closest_hit_rays; /* "Regular ray intersection tests"            */
+    uint64_t shadow_rays;      /* "Shadow ray intersection tests"             */
+    uint64_t path_vertices;
+    uint64_t kernel_launches;
+    double render_ms;          /* device time of the last sptx_render         */
+    double traverse_ms;        /* of which traversal kernels                  */
+    double shade_ms;
+    double film_ms;
+} sptx_counters;
+
+typedef struct sptx_ctx sptx_ctx;
+
+/* ---- entry points -------------------------------------------------------- */
+
+/* Creates a context on CUDA device `device`.  Replaces: construction of the
+ * integrator in RenderOptions::MakeIntegrator (src/core/api.cpp:1750-1771). */
+int sptx_create(int device, sptx_ctx **out);
+void sptx_destroy(sptx_ctx *ctx);
+/* Message of the last failure on ctx (or of the last failed sptx_create /
+ * scene-file call when ctx is NULL).  Replaces Error() (src/core/error.cpp:89-103). */
+const char *sptx_last_error(const sptx_ctx *ctx);
+
+/* Copies the scene tables to HBM and builds device-side derived tables
+ * (per-leaf triangle vertex blocks, Halton pixel offsets, light-selection
+ * tables).  Replaces Preprocess + the pointer graph Render walks
+ * (src/core/integrator.cpp:229, src/integrators/path.cpp:59-62). */
+int sptx_upload_scene(sptx_ctx *ctx, const sptx_scene_desc *scene);
+
+/* BVHAccel::Intersect (any_hit = 0, src/accelerators/bvh.cpp:662-700) or
+ * BVHAccel::IntersectP (any_hit = 1, :702-738) for n rays in HOST memory. */
+int sptx_intersect_batch(sptx_ctx *ctx, const sptx_ray *rays, int64_t n,
+                         sptx_hit *hits, int any_hit, int with_counters);
+/* Same with rays and hits already resident in device memory; *ms (optional)
+ * receives the CUDA-event time of the traversal kernel alone. */
+int sptx_intersect_batch_device(sptx_ctx *ctx, const void *d_rays, int64_t n,
+                                void *d_hits, int any_hit, int with_counters,
+                                float *ms);
+
+/* SamplerIntegrator::Render's pixel/sample loop (src/core/integrator.cpp:
+ * 228-334) for sample numbers [sample_begin, sample_end) of every pixel of
+ * `pixel_bounds` (NULL = the film's sample bounds), accumulated into the
+ * device film.  Does not clear the film and does not write files. */
+int sptx_render(sptx_ctx *ctx, const int32_t *pixel_bounds, int sample_begin,
+                int sample_end);
+/* Rank-interleaved variant for multi-GPU pixel partitioning: renders only the
+ * 16x16 tiles t with t % n_parts == part (tile order of integrator.cpp:235-249). */
+int sptx_render_tiles(sptx_ctx *ctx, int part, int n_parts, int sample_begin,
+                      int sample_end);
+
+/* Film::Clear (src/core/film.cpp:114-122). */
+int sptx_film_clear(sptx_ctx *ctx);
+/* Device film: contrib is float32 [H][W][32] (31 bins + filterWeightSum in
+ * slot 31) over croppedPixelBounds.  Exposed so the host can sum films across
+ * GPUs with NCCL (the reference's MergeFilmTile, src/core/film.cpp:124-142). */
+int sptx_film_device_ptr(sptx_ctx *ctx, void **d_film, int64_t *n_floats);
+/* Film pixels to host: contrib [H][W][31] float32, weight [H][W] float32. */
+int sptx_film_download(sptx_ctx *ctx, float *contrib, float *weight);
+/* Film::WriteImage's spectral branch (src/core/film.cpp:226-306) up to the
+ * file: L * scale as float64, bin-major [31][H][W], into host memory. */
+int sptx_film_pack_dat(sptx_ctx *ctx, double *planes);
+/* The .dat writer itself: header "W H 31\nv3 \n" + planes (film.cpp:267-306). */
+int sptx_write_dat(const char *path, int width, int height, const double *planes);
+
+int sptx_get_counters(sptx_ctx *ctx, sptx_counters *out);
+int sptx_reset_counters(sptx_ctx *ctx);
+/* Max paths in flight per wavefront pass (0 = default). */
+int sptx_set_wavefront_size(sptx_ctx *ctx, int64_t max_paths);
+
+/* Test hooks: the device sampler and camera evaluated stand-alone.
+ * values[i] = SampleDimension(index of (px[i],py[i],sample[i]), dim[i])
+ * (src/samplers/halton.cpp:96-127). */
+int sptx_sampler_eval(sptx_ctx *ctx, const int32_t *px, const int32_t *py,
+                      const int32_t *sample, const int32_t *dim, int64_t n,
+                      float *values);
+/* rays[i], weights[i] = Camera::GenerateRayDifferential's main ray for
+ * CameraSample{pFilm, time, pLens} = cs[5*i .. 5*i+4] at `wavelength`. */
+int sptx_camera_rays(sptx_ctx *ctx, const float *cs, int64_t n, float wavelength,
+                     sptx_ray *rays, float *weights);
+
+/* Flattened-scene files (what host/flatten.cpp writes). */
+int sptx_scene_save(const char *path, const sptx_scene_desc *scene);
+int sptx_scene_load(const char *path, sptx_scene_desc **out);
+void sptx_scene_free(sptx_scene_desc *scene);
+
+int sptx_abi_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SPTX_H */

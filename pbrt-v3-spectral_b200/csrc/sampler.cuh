@@ -1,0 +1,139 @@
+// sampler.cuh -- HaltonSampler reproduced on the device.
+//
+// A sample value is a pure function of (pixel, sample number, dimension):
+//   index = offsetForPixel + sampleNum * sampleStride   (samplers/halton.cpp:96-115)
+//   value = SampleDimension(index, dim)                 (samplers/halton.cpp:117-127)
+// so every path owns its own stream and streams match the reference bit for bit.
+#pragma once
+#include "scene.cuh"
+
+namespace sptx {
+
+SPTX_HD uint32_t reverse_bits32(uint32_t n) {
+    n = (n << 16) | (n >> 16);
+    n = ((n & 0x00ff00ffu) << 8) | ((n & 0xff00ff00u) >> 8);
+    n = ((n & 0x0f0f0f0fu) << 4) | ((n & 0xf0f0f0f0u) >> 4);
+    n = ((n & 0x33333333u) << 2) | ((n & 0xccccccccu) >> 2);
+    n = ((n & 0x55555555u) << 1) | ((n & 0xaaaaaaaau) >> 1);
+    return n;
+}
+SPTX_HD uint64_t reverse_bits64(uint64_t n) {
+    uint64_t n0 = reverse_bits32((uint32_t)n);
+    uint64_t n1 = reverse_bits32((uint32_t)(n >> 32));
+    return (n0 << 32) | n1;
+}
+
+// InverseRadicalInverse<base>, core/lowdiscrepancy.h:82-91.
+SPTX_HD uint64_t inverse_radical_inverse(uint64_t inverse, int base, int nDigits) {
+    uint64_t index = 0;
+    for (int i = 0; i < nDigits; ++i) {
+        uint64_t digit = inverse % (uint64_t)base;
+        inverse /= (uint64_t)base;
+        index = index * (uint64_t)base + digit;
+    }
+    return index;
+}
+
+// Mod for ints, core/pbrt.h:316-320.
+SPTX_HD int mod_i(int a, int b) {
+    int r = a - (a / b) * b;
+    return (r < 0) ? r + b : r;
+}
+
+// HaltonSampler::GetIndexForSample's per-pixel part (samplers/halton.cpp:96-112).
+SPTX_HD uint64_t halton_pixel_offset(const sptx_sampler &s, int px, int py) {
+    const int kMaxResolution = 128;
+    uint64_t off = 0;
+    if (s.sample_stride > 1) {
+        int pm0 = mod_i(px, kMaxResolution), pm1 = mod_i(py, kMaxResolution);
+        uint64_t d0 = inverse_radical_inverse((uint64_t)pm0, 2, s.base_exponents[0]);
+        off += d0 * (uint64_t)(s.sample_stride / s.base_scales[0]) * (uint64_t)s.mult_inverse[0];
+        uint64_t d1 = inverse_radical_inverse((uint64_t)pm1, 3, s.base_exponents[1]);
+        off += d1 * (uint64_t)(s.sample_stride / s.base_scales[1]) * (uint64_t)s.mult_inverse[1];
+        off %= (uint64_t)s.sample_stride;
+    }
+    return off;
+}
+
+// RadicalInverseSpecialized<base>, core/lowdiscrepancy.cpp:389-403.
+SPTX_HD float radical_inverse_base(uint64_t a, uint32_t base) {
+    const float invBase = 1.f / (float)base;
+    uint64_t reversed = 0;
+    float invBaseN = 1.f;
+    if (a >> 32) {
+        while (a >> 32) {
+            uint64_t next = a / base;
+            uint64_t digit = a - next * base;
+            reversed = reversed * base + digit;
+            invBaseN *= invBase;
+            a = next;
+        }
+    }
+    uint32_t a32 = (uint32_t)a;
+    while (a32) {
+        uint32_t next = a32 / base;
+        uint32_t digit = a32 - next * base;
+        reversed = reversed * base + digit;
+        invBaseN *= invBase;
+        a32 = next;
+    }
+    float r = (float)reversed * invBaseN;
+    return (kOneMinusEpsilon < r) ? kOneMinusEpsilon : r;
+}
+
+// ScrambledRadicalInverseSpecialized<base>, core/lowdiscrepancy.cpp:405-424.
+SPTX_DEV float scrambled_radical_inverse(const uint16_t *perm, uint64_t a, uint32_t base) {
+    const float invBase = 1.f / (float)base;
+    uint64_t reversed = 0;
+    float invBaseN = 1.f;
+    while (a >> 32) {
+        uint64_t next = a / base;
+        uint64_t digit = a - next * base;
+        reversed = reversed * base + __ldg(perm + digit);
+        invBaseN *= invBase;
+        a = next;
+    }
+    uint32_t a32 = (uint32_t)a;
+    while (a32) {
+        uint32_t next = a32 / base;
+        uint32_t digit = a32 - next * base;
+        reversed = reversed * base + __ldg(perm + digit);
+        invBaseN *= invBase;
+        a32 = next;
+    }
+    float r = invBaseN * ((float)reversed + invBase * (float)(int)__ldg(perm) / (1.f - invBase));
+    return (kOneMinusEpsilon < r) ? kOneMinusEpsilon : r;
+}
+
+// HaltonSampler::SampleDimension, samplers/halton.cpp:117-127.
+SPTX_DEV float halton_sample(const DSampler &H, uint64_t index, int dim) {
+    if (H.s.sample_at_center && (dim == 0 || dim == 1)) return 0.5f;
+    if (dim == 0) {
+        // RadicalInverse(0, a) = ReverseBits64(a) * 0x1p-64 in DOUBLE, rounded
+        // to float on return (core/lowdiscrepancy.cpp:430-437).
+        uint64_t a = index >> H.s.base_exponents[0];
+        return (float)((double)reverse_bits64(a) * 0x1p-64);
+    } else if (dim == 1) {
+        return radical_inverse_base(index / (uint64_t)H.s.base_scales[1], 3u);
+    }
+    int d = dim < H.s.n_dims ? dim : H.s.n_dims - 1;  // callers flag the overflow
+    return scrambled_radical_inverse(H.perms + __ldg(H.prime_sums + d), index,
+                                     (uint32_t)__ldg(H.primes + d));
+}
+
+// Per-path view of the sampler: GlobalSampler::Get1D/Get2D with no array
+// requests (core/sampler.cpp:180-195): dimensions are consumed sequentially.
+struct SampleStream {
+    uint64_t index;
+    int dim;
+};
+SPTX_DEV float get1d(const DSampler &H, SampleStream &st) { return halton_sample(H, st.index, st.dim++); }
+SPTX_DEV V2 get2d(const DSampler &H, SampleStream &st) {
+    V2 p;
+    p.x = halton_sample(H, st.index, st.dim);
+    p.y = halton_sample(H, st.index, st.dim + 1);
+    st.dim += 2;
+    return p;
+}
+
+}  // namespace sptx
