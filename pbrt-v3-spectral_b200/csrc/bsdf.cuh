@@ -1,0 +1,234 @@
+// bsdf.cuh -- BSDF::f / Sample_f / Pdf over 31-bin spectra.
+//
+// A material's BSDF is a short list of lobes (sptx_lobe).  Every lobe value is
+// "spectrum row x a few scalars", so instead of materialising 31-float arrays
+// per thread a BSDF evaluation returns an FSum: up to kMaxTerms terms, each a
+// formula id + spectrum rows + scalars.  Consumers stream over the 31 bins and
+// evaluate fsum_bin(), which reproduces the reference's per-bin operation
+// order (core/reflection.cpp, core/microfacet.cpp).
+#pragma once
+#include "camera.cuh"  // refract()
+#include "interaction.cuh"
+
+namespace sptx {
+
+enum {
+    BSDF_REFLECTION = 1 << 0,
+    BSDF_TRANSMISSION = 1 << 1,
+    BSDF_DIFFUSE = 1 << 2,
+    BSDF_GLOSSY = 1 << 3,
+    BSDF_SPECULAR = 1 << 4,
+    BSDF_ALL = 31
+};
+
+constexpr int kMaxTerms = 4;
+
+enum {
+    TERM_R_S = 0,        // R[b] * s0                       (Lambert: s0 = InvPi)
+    TERM_R_S_S = 1,      // R[b] * s0 * s1                  (Oren-Nayar)
+    TERM_MICRO_S = 2,    // R[b] * s0 * s1 * s2 / s3        (microfacet, scalar Fresnel s2)
+    TERM_MICRO_COND = 3, // R[b] * s0 * s1 * FrCond[b] / s3 (microfacet, conductor, cos = s2)
+    TERM_S_R_DIV = 4,    // s0 * R[b] / s1                  (specular reflection / FresnelSpecular R)
+    TERM_COND_R_DIV = 5, // FrCond[b](s0) * R[b] / s1       (specular reflection, conductor)
+    TERM_T_S_S_DIV = 6,  // (T[b] * s0) * s1 / s2           (specular transmission)
+};
+
+struct FTerm {
+    int kind;
+    int R;
+    int e0, e1, e2;  // conductor rows: etaI, etaT, k
+    float s0, s1, s2, s3;
+};
+struct FSum {
+    int n;
+    FTerm t[kMaxTerms];
+};
+
+SPTX_DEV float spec(const DScene &S, int row, int b) {
+    return __ldg(S.spectra + (size_t)row * SPTX_SPECTRUM_STRIDE + b);
+}
+
+// FrDielectric, core/reflection.cpp:47-68.
+SPTX_DEV float fr_dielectric(float cosThetaI, float etaI, float etaT) {
+    cosThetaI = clampf(cosThetaI, -1.f, 1.f);
+    bool entering = cosThetaI > 0.f;
+    if (!entering) {
+        float t = etaI;
+        etaI = etaT;
+        etaT = t;
+        cosThetaI = fabsf(cosThetaI);
+    }
+    float sinThetaI = sqrtf(fmaxf(0.f, 1.f - cosThetaI * cosThetaI));
+    float sinThetaT = etaI / etaT * sinThetaI;
+    if (sinThetaT >= 1) return 1.f;
+    float cosThetaT = sqrtf(fmaxf(0.f, 1.f - sinThetaT * sinThetaT));
+    float Rparl = ((etaT * cosThetaI) - (etaI * cosThetaT)) / ((etaT * cosThetaI) + (etaI * cosThetaT));
+    float Rperp = ((etaI * cosThetaI) - (etaT * cosThetaT)) / ((etaI * cosThetaI) + (etaT * cosThetaT));
+    return (Rparl * Rparl + Rperp * Rperp) / 2.f;
+}
+
+// FrConductor for one bin, core/reflection.cpp:71-94.
+SPTX_DEV float fr_conductor_bin(float cosThetaI, float etai, float etat, float k) {
+    cosThetaI = clampf(cosThetaI, -1.f, 1.f);
+    float eta = etat / etai;
+    float etak = k / etai;
+    float cosThetaI2 = cosThetaI * cosThetaI;
+    float sinThetaI2 = (float)(1. - (double)cosThetaI2);
+    float eta2 = eta * eta;
+    float etak2 = etak * etak;
+    float t0 = eta2 - etak2 - sinThetaI2;
+    float a2plusb2 = sqrtf(t0 * t0 + 4.f * eta2 * etak2);
+    float t1 = a2plusb2 + cosThetaI2;
+    float a = sqrtf(0.5f * (a2plusb2 + t0));
+    float t2 = 2.f * cosThetaI * a;
+    float Rs = (t1 - t2) / (t1 + t2);
+    float t3 = cosThetaI2 * a2plusb2 + sinThetaI2 * sinThetaI2;
+    float t4 = t2 * sinThetaI2;
+    float Rp = Rs * (t3 - t4) / (t3 + t4);
+    return 0.5f * (Rp + Rs);
+}
+
+SPTX_DEV float fterm_bin(const DScene &S, const FTerm &t, int b) {
+    switch (t.kind) {
+    case TERM_R_S:
+        return spec(S, t.R, b) * t.s0;
+    case TERM_R_S_S:
+        return spec(S, t.R, b) * t.s0 * t.s1;
+    case TERM_MICRO_S:
+        return spec(S, t.R, b) * t.s0 * t.s1 * t.s2 / t.s3;
+    case TERM_MICRO_COND: {
+        float F = fr_conductor_bin(t.s2, spec(S, t.e0, b), spec(S, t.e1, b), spec(S, t.e2, b));
+        return spec(S, t.R, b) * t.s0 * t.s1 * F / t.s3;
+    }
+    case TERM_S_R_DIV:
+        return t.s0 * spec(S, t.R, b) / t.s1;
+    case TERM_COND_R_DIV: {
+        float F = fr_conductor_bin(t.s0, spec(S, t.e0, b), spec(S, t.e1, b), spec(S, t.e2, b));
+        return F * spec(S, t.R, b) / t.s1;
+    }
+    default:  // TERM_T_S_S_DIV
+        return (spec(S, t.R, b) * t.s0) * t.s1 / t.s2;
+    }
+}
+// Sum of terms in lobe order, starting from Spectrum(0) as BSDF::f does.
+SPTX_DEV float fsum_bin(const DScene &S, const FSum &f, int b) {
+    float v = 0.f;
+    for (int i = 0; i < f.n; ++i) v += fterm_bin(S, f.t[i], b);
+    return v;
+}
+
+// ---- local shading frame trigonometry, core/reflection.h:55-100 ------------
+SPTX_DEV float cos_theta(V3 w) { return w.z; }
+SPTX_DEV float cos2_theta(V3 w) { return w.z * w.z; }
+SPTX_DEV float abs_cos_theta(V3 w) { return fabsf(w.z); }
+SPTX_DEV float sin2_theta(V3 w) { return fmaxf(0.f, 1.f - cos2_theta(w)); }
+SPTX_DEV float sin_theta(V3 w) { return sqrtf(sin2_theta(w)); }
+SPTX_DEV float tan_theta(V3 w) { return sin_theta(w) / cos_theta(w); }
+SPTX_DEV float tan2_theta(V3 w) { return sin2_theta(w) / cos2_theta(w); }
+SPTX_DEV float cos_phi(V3 w) {
+    float s = sin_theta(w);
+    return (s == 0) ? 1.f : clampf(w.x / s, -1.f, 1.f);
+}
+SPTX_DEV float sin_phi(V3 w) {
+    float s = sin_theta(w);
+    return (s == 0) ? 0.f : clampf(w.y / s, -1.f, 1.f);
+}
+SPTX_DEV float cos2_phi(V3 w) { return cos_phi(w) * cos_phi(w); }
+SPTX_DEV float sin2_phi(V3 w) { return sin_phi(w) * sin_phi(w); }
+SPTX_DEV bool same_hemisphere(V3 a, V3 b) { return a.z * b.z > 0; }
+
+// ---- Trowbridge-Reitz, core/microfacet.cpp:155-184, 238-344 -----------------
+SPTX_DEV float tr_D(float ax, float ay, V3 wh) {
+    float tan2Theta = tan2_theta(wh);
+    if (isinf(tan2Theta)) return 0.f;
+    const float cos4Theta = cos2_theta(wh) * cos2_theta(wh);
+    float e = (cos2_phi(wh) / (ax * ax) + sin2_phi(wh) / (ay * ay)) * tan2Theta;
+    return 1.f / (kPi * ax * ay * cos4Theta * (1.f + e) * (1.f + e));
+}
+SPTX_DEV float tr_lambda(float ax, float ay, V3 w) {
+    float absTanTheta = fabsf(tan_theta(w));
+    if (isinf(absTanTheta)) return 0.f;
+    float alpha = sqrtf(cos2_phi(w) * ax * ax + sin2_phi(w) * ay * ay);
+    float alpha2Tan2Theta = (alpha * absTanTheta) * (alpha * absTanTheta);
+    return (-1.f + sqrtf(1.f + alpha2Tan2Theta)) / 2.f;
+}
+SPTX_DEV float tr_G1(float ax, float ay, V3 w) { return 1.f / (1.f + tr_lambda(ax, ay, w)); }
+SPTX_DEV float tr_G(float ax, float ay, V3 wo, V3 wi) {
+    return 1.f / (1.f + tr_lambda(ax, ay, wo) + tr_lambda(ax, ay, wi));
+}
+SPTX_DEV float tr_pdf(const sptx_lobe &L, V3 wo, V3 wh) {
+    if (L.sample_visible)
+        return tr_D(L.alpha_x, L.alpha_y, wh) * tr_G1(L.alpha_x, L.alpha_y, wo) * absdot(wo, wh) /
+               abs_cos_theta(wo);
+    return tr_D(L.alpha_x, L.alpha_y, wh) * abs_cos_theta(wh);
+}
+SPTX_DEV void tr_sample11(float cosTheta, float U1, float U2, float *slope_x, float *slope_y) {
+    if ((double)cosTheta > .9999) {
+        float r = sqrtf(U1 / (1.f - U1));
+        float phi = (float)(6.28318530718 * (double)U2);
+        *slope_x = r * cosf(phi);
+        *slope_y = r * sinf(phi);
+        return;
+    }
+    float sinTheta = sqrtf(fmaxf(0.f, 1.f - cosTheta * cosTheta));
+    float tanTheta = sinTheta / cosTheta;
+    float a = 1.f / tanTheta;
+    float G1 = 2.f / (1.f + sqrtf(1.f + 1.f / (a * a)));
+    float A = 2.f * U1 / G1 - 1.f;
+    float tmp = 1.f / (A * A - 1.f);
+    if (tmp > 1e10f) tmp = 1e10f;
+    float B = tanTheta;
+    float D = sqrtf(fmaxf(B * B * tmp * tmp - (A * A - B * B) * tmp, 0.f));
+    float slope_x_1 = B * tmp - D;
+    float slope_x_2 = B * tmp + D;
+    *slope_x = (A < 0 || slope_x_2 > 1.f / tanTheta) ? slope_x_1 : slope_x_2;
+    float Sg;
+    if (U2 > 0.5f) {
+        Sg = 1.f;
+        U2 = 2.f * (U2 - .5f);
+    } else {
+        Sg = -1.f;
+        U2 = 2.f * (.5f - U2);
+    }
+    float z = (U2 * (U2 * (U2 * 0.27385f - 0.73369f) + 0.46341f)) /
+              (U2 * (U2 * (U2 * 0.093073f + 0.309420f) - 1.000000f) + 0.597999f);
+    *slope_y = Sg * z * sqrtf(1.f + *slope_x * *slope_x);
+}
+SPTX_DEV V3 tr_sample_wh(const sptx_lobe &L, V3 wo, V2 u) {
+    const float ax = L.alpha_x, ay = L.alpha_y;
+    V3 wh;
+    if (!L.sample_visible) {
+        float cosTheta = 0, phi = (2 * kPi) * u.y;
+        if (ax == ay) {
+            float tanTheta2 = ax * ax * u.x / (1.0f - u.x);
+            cosTheta = 1.f / sqrtf(1.f + tanTheta2);
+        } else {
+            phi = atanf(ay / ax * tanf(2 * kPi * u.y + .5f * kPi));
+            if (u.y > .5f) phi += kPi;
+            float sinPhi = sinf(phi), cosPhi = cosf(phi);
+            const float ax2 = ax * ax, ay2 = ay * ay;
+            const float alpha2 = 1.f / (cosPhi * cosPhi / ax2 + sinPhi * sinPhi / ay2);
+            float tanTheta2 = alpha2 * u.x / (1.f - u.x);
+            cosTheta = 1.f / sqrtf(1.f + tanTheta2);
+        }
+        float sinTheta = sqrtf(fmaxf(0.f, 1.f - cosTheta * cosTheta));
+        wh = mk(sinTheta * cosf(phi), sinTheta * sinf(phi), cosTheta);
+        if (!same_hemisphere(wo, wh)) wh = -wh;
+    } else {
+        bool flip = wo.z < 0;
+        V3 wi = flip ? -wo : wo;
+        V3 ws = normalize(mk(ax * wi.x, ay * wi.y, wi.z));
+        float sx, sy;
+        tr_sample11(cos_theta(ws), u.x, u.y, &sx, &sy);
+        float tmp = cos_phi(ws) * sx - sin_phi(ws) * sy;
+        sy = sin_phi(ws) * sx + cos_phi(ws) * sy;
+        sx = tmp;
+        sx = ax * sx;
+        sy = ay * sy;
+        wh = normalize(mk(-sx, -sy, 1.f));
+        if (flip) wh = -wh;
+    }
+    return wh;
+}
+
+}  // namespace sptx

@@ -1,0 +1,102 @@
+// kernels.cuh -- the wavefront kernels (K1 generate, K2 intersect, K3 shade,
+// K4 resolve, K5/K6 film) and the stand-alone ray-batch kernels.
+#pragma once
+#include "wavefront.cuh"
+
+namespace sptx {
+
+constexpr int kBlock = 128;
+
+// ---- K1: camera samples -> path state ---------------------------------------
+// Sampler::GetCameraSample (core/sampler.cpp:46-52) + GenerateRayDifferential +
+// the `if (rayWeight > 0) Li(...)` gate of SamplerIntegrator::Render
+// (core/integrator.cpp:279-292).
+__global__ void k_generate(DScene S, DCamera C, DSampler H, PathArrays A, RenderParams R,
+                           DeviceCounters *cnt) {
+    const int64_t nPaths = (int64_t)R.nPix * R.samplesInPass;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nPaths;
+         i += (int64_t)gridDim.x * blockDim.x) {
+        const int pix = (int)(i % R.nPix);
+        const int sampleNum = R.sampleBegin + (int)(i / R.nPix);
+        const int2 pxy = R.pixels[pix];
+        const int ox = pxy.x - H.sb[0], oy = pxy.y - H.sb[1];
+        const uint64_t off = H.pixel_offset[(size_t)oy * (H.sb[2] - H.sb[0]) + ox];
+        SampleStream st;
+        st.index = off + (uint64_t)sampleNum * (uint64_t)H.s.sample_stride;
+        st.dim = 0;
+        V2 u = get2d(H, st);
+        V2 pFilm{(float)pxy.x + u.x, (float)pxy.y + u.y};
+        (void)get1d(H, st);  // time
+        V2 pLens = get2d(H, st);
+        Ray ray;
+        ray.o = mk(0, 0, 0);
+        ray.d = mk(0, 0, 1);
+        ray.tMax = kInf;
+        float w = camera_ray(C, pFilm, pLens, R.wavelength, &ray);
+        A.rayA[i] = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.d.x);
+        A.rayB[i] = make_float4(ray.d.y, ray.d.z, 1.f, w);
+        A.sindex[i] = st.index;
+        A.info[i] = pack_info(0, 0, st.dim);
+        A.pfilm[i] = make_float2(pFilm.x, pFilm.y);
+        A.spill[i] = 0;
+        for (int b = 0; b < SPTX_NBINS; ++b) {
+            A.beta[0][(size_t)b * A.capacity + i] = 1.f;
+            A.L[(size_t)b * A.capacity + i] = 0.f;
+        }
+        queue_push(A.q[0], A.counters + 0, (int)i, w > 0);
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&cnt->cameraRays, (unsigned long long)nPaths);
+}
+
+// ---- K2: closest hit for the active queue ------------------------------------
+__global__ void k_intersect(DScene S, PathArrays A, int qi, DeviceCounters *cnt) {
+    const int n = A.counters[qi];
+    const int *queue = A.q[qi];
+    for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
+        const int i = queue[k];
+        float4 ra = A.rayA[i], rb = A.rayB[i];
+        Ray ray{mk(ra.x, ra.y, ra.z), mk(ra.w, rb.x, rb.y), kInf};
+        HitRec h;
+        scene_intersect<false>(S, ray, &h, nullptr);
+        A.hitA[i] = make_float4(__int_as_float(h.prim), __int_as_float(h.inst), h.b0, h.b1);
+        A.hitB[i] = make_float4(h.b2, ray.tMax, 0.f, 0.f);
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&cnt->closestRays, (unsigned long long)n);
+}
+
+// ---- stand-alone ray batches (sptx_intersect_batch) ---------------------------
+template <bool ANY, bool COUNT>
+__global__ void k_ray_batch(DScene S, const sptx_ray *rays, int64_t n, sptx_hit *hits) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+         i += (int64_t)gridDim.x * blockDim.x) {
+        const float4 *rp = reinterpret_cast<const float4 *>(rays + i);
+        float4 a = __ldg(rp), b = __ldg(rp + 1);
+        Ray ray{mk(a.x, a.y, a.z), mk(b.x, b.y, b.z), a.w};
+        TravCounters tc{0, 0};
+        sptx_hit out;
+        out.prim = -1;
+        out.instance = -1;
+        out.b0 = out.b1 = out.b2 = 0.f;
+        if (ANY) {
+            bool hit = scene_intersect_p<COUNT>(S, ray, &tc);
+            out.prim = hit ? 0 : -1;
+            out.t = ray.tMax;
+        } else {
+            HitRec h;
+            scene_intersect<COUNT>(S, ray, &h, &tc);
+            out.prim = h.prim;
+            out.instance = h.inst;
+            out.b0 = h.b0;
+            out.b1 = h.b1;
+            out.b2 = h.b2;
+            out.t = ray.tMax;
+        }
+        out.n_nodes = tc.nodes;
+        out.n_tests = tc.tests;
+        float4 *hp = reinterpret_cast<float4 *>(hits + i);
+        hp[0] = make_float4(__int_as_float(out.prim), __int_as_float(out.instance), out.t, out.b0);
+        hp[1] = make_float4(out.b1, out.b2, __int_as_float(out.n_nodes), __int_as_float(out.n_tests));
+    }
+}
+
+}  // namespace sptx

@@ -1,0 +1,245 @@
+// light.cuh -- DiffuseAreaLight / PointLight sampling and light selection.
+//
+// lights/diffuse.cpp:64-87, lights/point.cpp:44-54, core/shape.cpp:56-87,
+// shapes/triangle.cpp:575-608, shapes/sphere.cpp:219-306,
+// core/sampling.h:55-109 (Distribution1D), core/lightdistrib.cpp.
+#pragma once
+#include "bsdf_eval.cuh"
+
+namespace sptx {
+
+// Reference point of a light query: a surface point, or a bare point with
+// n = 0 (what SpatialLightDistribution::ComputeDistribution passes).
+struct RefPoint {
+    V3 p, pError, n;
+};
+
+struct LightPoint {  // Interaction returned by Shape::Sample
+    V3 p, pError, n;
+};
+
+SPTX_DEV V3 uniform_sample_sphere(V2 u) {
+    float z = 1.f - 2.f * u.x;
+    float r = sqrtf(fmaxf(0.f, 1.f - z * z));
+    float phi = 2.f * kPi * u.y;
+    return mk(r * cosf(phi), r * sinf(phi), z);
+}
+
+SPTX_DEV void tri_vertices(const DScene &S, int shape, V3 *p0, V3 *p1, V3 *p2, sptx_triangle *T,
+                           sptx_mesh *M) {
+    *T = S.triangles[shape];
+    *M = S.meshes[T->mesh];
+    *p0 = ld3(S.positions, (size_t)M->p_base + T->v[0]);
+    *p1 = ld3(S.positions, (size_t)M->p_base + T->v[1]);
+    *p2 = ld3(S.positions, (size_t)M->p_base + T->v[2]);
+}
+
+// Triangle::Sample(u, pdf), shapes/triangle.cpp:583-608.
+SPTX_DEV LightPoint triangle_sample(const DScene &S, int shape, V2 u, float area, float *pdf) {
+    float su0 = sqrtf(u.x);
+    float b0 = 1.f - su0, b1 = u.y * su0;
+    V3 p0, p1, p2;
+    sptx_triangle T;
+    sptx_mesh M;
+    tri_vertices(S, shape, &p0, &p1, &p2, &T, &M);
+    LightPoint it;
+    float b2 = (1.f - b0 - b1);
+    it.p = b0 * p0 + b1 * p1 + b2 * p2;
+    it.n = normalize(cross(p1 - p0, p2 - p0));
+    if (M.n_base >= 0) {
+        V3 n0 = ld3(S.normals, (size_t)M.n_base + T.v[0]);
+        V3 n1 = ld3(S.normals, (size_t)M.n_base + T.v[1]);
+        V3 n2 = ld3(S.normals, (size_t)M.n_base + T.v[2]);
+        V3 ns = b0 * n0 + b1 * n1 + b2 * n2;
+        it.n = faceforward(it.n, ns);
+    } else if (M.flip)
+        it.n = it.n * -1.f;
+    V3 pAbsSum = vabs(b0 * p0) + vabs(b1 * p1) + vabs(b2 * p2);
+    it.pError = gamma_n(6) * pAbsSum;
+    *pdf = 1.f / area;
+    return it;
+}
+
+// Sphere::Sample(u, pdf), shapes/sphere.cpp:219-230.
+SPTX_DEV LightPoint sphere_sample_area(const sptx_sphere &sp, V2 u, float area, float *pdf) {
+    V3 pObj = mk(0, 0, 0) + sp.radius * uniform_sample_sphere(u);
+    LightPoint it;
+    it.n = normalize(xf_normal(sp.w2o, pObj));
+    if (sp.reverse_orientation) it.n = it.n * -1.f;
+    pObj = pObj * (sp.radius / length(pObj));
+    V3 pObjError = gamma_n(5) * vabs(pObj);
+    it.p = xf_point_err2(sp.o2w, pObj, pObjError, &it.pError);
+    *pdf = 1.f / area;
+    return it;
+}
+
+// Shape::Sample(ref, u, pdf), core/shape.cpp:56-70 (area -> solid angle).
+SPTX_DEV void area_to_solid_angle(const RefPoint &ref, const LightPoint &lp, float *pdf,
+                                  bool checkInfAlways) {
+    V3 wi = lp.p - ref.p;
+    if (length_sq(wi) == 0)
+        *pdf = 0.f;
+    else {
+        wi = normalize(wi);
+        *pdf *= dist_sq(ref.p, lp.p) / absdot(lp.n, -wi);
+        if (!checkInfAlways && isinf(*pdf)) *pdf = 0.f;
+    }
+    if (checkInfAlways && isinf(*pdf)) *pdf = 0.f;
+}
+
+// Sphere::Sample(ref, u, pdf), shapes/sphere.cpp:232-292.
+SPTX_DEV LightPoint sphere_sample(const sptx_sphere &sp, const RefPoint &ref, V2 u, float area,
+                                  float *pdf) {
+    V3 pCenter = xf_point(sp.o2w, mk(0, 0, 0));
+    V3 pOrigin = offset_ray_origin(ref.p, ref.pError, ref.n, pCenter - ref.p);
+    const float radius = sp.radius;
+    if (dist_sq(pOrigin, pCenter) <= radius * radius) {
+        LightPoint lp = sphere_sample_area(sp, u, area, pdf);
+        area_to_solid_angle(ref, lp, pdf, true);
+        return lp;
+    }
+    V3 wc = normalize(pCenter - ref.p);
+    V3 wcX, wcY;
+    coordinate_system(wc, &wcX, &wcY);
+    float sinThetaMax2 = radius * radius / dist_sq(ref.p, pCenter);
+    float cosThetaMax = sqrtf(fmaxf(0.f, 1.f - sinThetaMax2));
+    float cosTheta = (1.f - u.x) + u.x * cosThetaMax;
+    float sinTheta = sqrtf(fmaxf(0.f, 1.f - cosTheta * cosTheta));
+    float phi = u.y * 2.f * kPi;
+    float dc = dist(ref.p, pCenter);
+    float ds = dc * cosTheta - sqrtf(fmaxf(0.f, radius * radius - dc * dc * sinTheta * sinTheta));
+    float cosAlpha = (dc * dc + radius * radius - ds * ds) / (2.f * dc * radius);
+    float sinAlpha = sqrtf(fmaxf(0.f, 1.f - cosAlpha * cosAlpha));
+    // SphericalDirection(sinAlpha, cosAlpha, phi, -wcX, -wcY, -wc), core/geometry.h:1478-1483
+    V3 nWorld = sinAlpha * cosf(phi) * (-wcX) + sinAlpha * sinf(phi) * (-wcY) + cosAlpha * (-wc);
+    V3 pWorld = pCenter + radius * nWorld;
+    LightPoint it;
+    it.p = pWorld;
+    it.pError = gamma_n(5) * vabs(pWorld);
+    it.n = nWorld;
+    if (sp.reverse_orientation) it.n = it.n * -1.f;
+    *pdf = 1.f / (2.f * kPi * (1.f - cosThetaMax));
+    return it;
+}
+
+// Shape::Pdf(ref, wi), core/shape.cpp:72-87, for one triangle / one sphere.
+SPTX_DEV float shape_pdf_generic(const DScene &S, int kind, int shape, const RefPoint &ref, V3 wi,
+                                 float area) {
+    Ray ray{offset_ray_origin(ref.p, ref.pError, ref.n, wi), wi, kInf};
+    V3 pHit, nHit;
+    if (kind == SPTX_PRIM_TRIANGLE) {
+        V3 p0, p1, p2;
+        sptx_triangle T;
+        sptx_mesh M;
+        tri_vertices(S, shape, &p0, &p1, &p2, &T, &M);
+        float t, b0, b1, b2;
+        if (!tri_test(ray.o, ray.d, ray.tMax, p0, p1, p2, &t, &b0, &b1, &b2)) return 0.f;
+        V2 uv[3];
+        tri_uvs(S, T, M, uv);
+        V3 du, dv;
+        if (!tri_partials(uv, p0, p1, p2, &du, &dv)) return 0.f;
+        Isect it;
+        triangle_interaction(S, shape, ray.d, b0, b1, b2, &it);
+        pHit = it.p;
+        nHit = it.n;
+    } else {
+        Isect it;
+        if (!sphere_interaction(S, shape, ray, &it)) return 0.f;
+        pHit = it.p;
+        nHit = it.n;
+    }
+    float pdf = dist_sq(ref.p, pHit) / (absdot(nHit, -wi) * area);
+    if (isinf(pdf)) pdf = 0.f;
+    return pdf;
+}
+
+// Sphere::Pdf(ref, wi), shapes/sphere.cpp:294-306.
+SPTX_DEV float sphere_pdf(const DScene &S, int shape, const RefPoint &ref, V3 wi, float area) {
+    const sptx_sphere &sp = S.spheres[shape];
+    V3 pCenter = xf_point(sp.o2w, mk(0, 0, 0));
+    V3 pOrigin = offset_ray_origin(ref.p, ref.pError, ref.n, pCenter - ref.p);
+    if (dist_sq(pOrigin, pCenter) <= sp.radius * sp.radius)
+        return shape_pdf_generic(S, SPTX_PRIM_SPHERE, shape, ref, wi, area);
+    float sinThetaMax2 = sp.radius * sp.radius / dist_sq(ref.p, pCenter);
+    float cosThetaMax = sqrtf(fmaxf(0.f, 1.f - sinThetaMax2));
+    return 1.f / (2.f * kPi * (1.f - cosThetaMax));
+}
+
+// Light::Pdf_Li (DiffuseAreaLight: shape->Pdf; PointLight: 0).
+SPTX_DEV float light_pdf_li(const DScene &S, const sptx_light &L, const RefPoint &ref, V3 wi) {
+    if (L.type != SPTX_LIGHT_DIFFUSE_AREA) return 0.f;
+    if (L.shape_kind == SPTX_PRIM_SPHERE) return sphere_pdf(S, L.shape, ref, wi, L.area);
+    return shape_pdf_generic(S, SPTX_PRIM_TRIANGLE, L.shape, ref, wi, L.area);
+}
+
+// Result of Light::Sample_Li.  The radiance is row `spectrum` scaled per bin:
+// area lights: Lemit[b] (emit != 0) ; point lights: I[b] / dist2.
+struct LiSample {
+    V3 wi;
+    float pdf;
+    bool black;     // Li is black (or pdf == 0)
+    int spectrum;   // row
+    float divisor;  // 0: Li[b] = row[b]; else Li[b] = row[b] / divisor
+    LightPoint lp;  // sampled point (shadow-ray target)
+};
+
+SPTX_DEV float li_bin(const DScene &S, const LiSample &ls, int b) {
+    float v = spec(S, ls.spectrum, b);
+    return ls.divisor != 0.f ? v / ls.divisor : v;
+}
+
+SPTX_DEV LiSample light_sample_li(const DScene &S, const sptx_light &L, const RefPoint &ref, V2 u) {
+    LiSample r;
+    r.spectrum = L.spectrum;
+    r.divisor = 0.f;
+    r.black = true;
+    r.pdf = 0.f;
+    r.wi = mk(0, 0, 0);
+    if (L.type == SPTX_LIGHT_POINT) {
+        V3 pl = mk(L.pos[0], L.pos[1], L.pos[2]);
+        r.wi = normalize(pl - ref.p);
+        r.pdf = 1.f;
+        r.lp.p = pl;
+        r.lp.pError = mk(0, 0, 0);
+        r.lp.n = mk(0, 0, 0);
+        r.divisor = dist_sq(pl, ref.p);
+        r.black = false;  // blackness of I/d^2 is checked per bin by the caller
+        return r;
+    }
+    float pdf;
+    LightPoint lp;
+    if (L.shape_kind == SPTX_PRIM_SPHERE)
+        lp = sphere_sample(S.spheres[L.shape], ref, u, L.area, &pdf);
+    else {
+        lp = triangle_sample(S, L.shape, u, L.area, &pdf);
+        area_to_solid_angle(ref, lp, &pdf, false);
+    }
+    r.lp = lp;
+    if (pdf == 0 || length_sq(lp.p - ref.p) == 0) return r;  // pdf = 0, black
+    r.wi = normalize(lp.p - ref.p);
+    r.pdf = pdf;
+    // DiffuseAreaLight::L(pShape, -wi), lights/diffuse.h:56-58
+    r.black = !(L.two_sided || dot(lp.n, -r.wi) > 0);
+    return r;
+}
+
+// Distribution1D::SampleDiscrete, core/sampling.h:90-100, on func[n] cdf[n+1].
+SPTX_DEV int sample_discrete(const float *func, const float *cdf, int n, float funcInt, float u,
+                             float *pdf) {
+    // FindInterval(size = n + 1, cdf[i] <= u), core/pbrt.h:398-416
+    int size = n + 1;
+    int first = 0, len = size;
+    while (len > 0) {
+        int half = len >> 1, middle = first + half;
+        if (__ldg(cdf + middle) <= u) {
+            first = middle + 1;
+            len -= half + 1;
+        } else
+            len = half;
+    }
+    int offset = min(max(first - 1, 0), size - 2);
+    *pdf = (funcInt > 0) ? __ldg(func + offset) / (funcInt * (float)n) : 0.f;
+    return offset;
+}
+
+}  // namespace sptx

@@ -1,0 +1,185 @@
+// resolve.cuh -- K4 (shadow / MIS rays of EstimateDirect) and K5/K6 (film).
+#pragma once
+#include "shade.cuh"
+
+namespace sptx {
+
+// ---- K4 ------------------------------------------------------------------------
+// VisibilityTester::Unoccluded (core/light.cpp:59-61) for the light sample and
+// the closest-hit test of the BSDF-sampled direction (core/integrator.cpp:
+// 190-212), then L += beta * (Ld / lightPdf) (integrator.cpp:104-105,
+// path.cpp:122-128).
+__global__ void __launch_bounds__(kBlock)
+k_resolve(DScene S, PathArrays A, int betaIn, DeviceCounters *cnt) {
+    const int n = A.counters[2];
+    const size_t P = (size_t)A.capacity;
+    const float *beta = A.beta[betaIn];
+    unsigned long long nShadow = 0, nClosest = 0;
+    for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
+        const int i = A.qNee[k];
+        const float4 sa = A.shA[i], sb = A.shB[i];
+        const float4 ma = A.misA[i], mb = A.misB[i];
+        const int flags = __float_as_int(mb.w);
+        const int lightNum = __float_as_int(mb.z);
+        const float lightPdfSel = sb.w;
+        bool useA = false, useB = false;
+        if (flags & NEE_HAS_SHADOW) {
+            Ray r{mk(sa.x, sa.y, sa.z), mk(sa.w, sb.x, sb.y), sb.z};
+            useA = !scene_intersect_p<false>(S, r, nullptr);
+            ++nShadow;
+        }
+        if (flags & NEE_HAS_MIS) {
+            Ray r{mk(ma.x, ma.y, ma.z), mk(ma.w, mb.x, mb.y), kInf};
+            HitRec h;
+            ++nClosest;
+            if (scene_intersect<false>(S, r, &h, nullptr)) {
+                if (S.prims[h.prim].light == lightNum) {
+                    const sptx_light &Lt = S.lights[lightNum];
+                    if (Lt.two_sided)
+                        useB = true;
+                    else {
+                        Isect it;
+                        if (build_interaction(S, r, h.prim, h.inst, h.b0, h.b1, h.b2, &it))
+                            useB = dot(it.n, -r.d) > 0;
+                    }
+                }
+            }
+        }
+        if (useA || useB) {
+            for (int b = 0; b < SPTX_NBINS; ++b) {
+                float Ld = 0.f;
+                if (useA) Ld += A.fa[b * P + i];
+                if (useB) Ld += A.fb[b * P + i];
+                A.L[b * P + i] += beta[b * P + i] * (Ld / lightPdfSel);
+            }
+        }
+    }
+    // one atomic per warp for the ray counters
+    for (int o = 16; o > 0; o >>= 1) {
+        nShadow += __shfl_down_sync(0xffffffffu, nShadow, o);
+        nClosest += __shfl_down_sync(0xffffffffu, nClosest, o);
+    }
+    if ((threadIdx.x & 31) == 0) {
+        if (nShadow) atomicAdd(&cnt->shadowRays, nShadow);
+        if (nClosest) atomicAdd(&cnt->closestRays, nClosest);
+    }
+}
+
+// ---- K5: film accumulation, one thread per pixel ------------------------------
+// The NaN / infinite-luminance guard of SamplerIntegrator::Render
+// (core/integrator.cpp:295-316) and FilmTile::AddSample (core/film.h:123-163).
+// Samples whose filter footprint is exactly their own pixel (always the case
+// for the default box filter of radius 0.5 unless the sample sits on a pixel
+// edge) are summed here in sample order, in registers, on top of the pixel's
+// current value -- the same float32 sequence as the reference.  Other samples
+// are marked for K6.
+SPTX_DEV bool sample_footprint(const DFilm &F, float2 pFilm, int *x0, int *y0, int *x1, int *y1) {
+    float dx = pFilm.x - 0.5f, dy = pFilm.y - 0.5f;
+    int p0x = (int)ceilf(dx - F.f.filter_radius[0]);
+    int p0y = (int)ceilf(dy - F.f.filter_radius[1]);
+    int p1x = (int)floorf(dx + F.f.filter_radius[0]) + 1;
+    int p1y = (int)floorf(dy + F.f.filter_radius[1]) + 1;
+    *x0 = max(p0x, F.f.cropped[0]);
+    *y0 = max(p0y, F.f.cropped[1]);
+    *x1 = min(p1x, F.f.cropped[2]);
+    *y1 = min(p1y, F.f.cropped[3]);
+    return *x0 < *x1 && *y0 < *y1;
+}
+SPTX_DEV float filter_weight(const DFilm &F, float2 pFilm, int x, int y) {
+    const int W = SPTX_FILTER_TABLE_WIDTH;
+    float dx = pFilm.x - 0.5f, dy = pFilm.y - 0.5f;
+    float fx = fabsf(((float)x - dx) * (1.f / F.f.filter_radius[0]) * (float)W);
+    float fy = fabsf(((float)y - dy) * (1.f / F.f.filter_radius[1]) * (float)W);
+    int ix = min((int)floorf(fx), W - 1), iy = min((int)floorf(fy), W - 1);
+    return F.f.filter_table[iy * W + ix];
+}
+
+// Applies the radiance guard and the luminance clamp; returns the scale to
+// apply to L (0 = black it out) -- y is computed once.
+SPTX_DEV float guard_scale(const DScene &S, const DFilm &F, const PathArrays &A, size_t i) {
+    const size_t P = (size_t)A.capacity;
+    float yy = 0.f;
+    bool nan = false;
+    for (int b = 0; b < SPTX_NBINS; ++b) {
+        float v = A.L[b * P + i];
+        if (isnan(v)) nan = true;
+        yy += S.cie_y[b] * v;
+    }
+    if (nan) return 0.f;
+    float y = y_finish(S, yy);
+    if (isinf(y)) return 0.f;
+    if (y > F.f.max_sample_luminance) return F.f.max_sample_luminance / y;
+    return 1.f;
+}
+
+__global__ void __launch_bounds__(kBlock)
+k_film(DScene S, DFilm F, PathArrays A, RenderParams R) {
+    const size_t P = (size_t)A.capacity;
+    for (int pix = blockIdx.x * blockDim.x + threadIdx.x; pix < R.nPix;
+         pix += gridDim.x * blockDim.x) {
+        const int2 pxy = R.pixels[pix];
+        const bool inFilm = pxy.x >= F.f.cropped[0] && pxy.x < F.f.cropped[2] &&
+                            pxy.y >= F.f.cropped[1] && pxy.y < F.f.cropped[3];
+        float acc[SPTX_NBINS + 1];
+        float *px = nullptr;
+        if (inFilm) {
+            px = F.pixels + ((size_t)(pxy.y - F.f.cropped[1]) * F.width + (pxy.x - F.f.cropped[0])) *
+                                SPTX_SPECTRUM_STRIDE;
+            for (int b = 0; b <= SPTX_NBINS; ++b) acc[b] = px[b];
+        }
+        bool touched = false;
+        for (int s = 0; s < R.samplesInPass; ++s) {
+            const size_t i = (size_t)s * R.nPix + pix;
+            const float2 pf = A.pfilm[i];
+            int x0, y0, x1, y1;
+            if (!sample_footprint(F, pf, &x0, &y0, &x1, &y1)) continue;
+            const bool own = inFilm && x0 == pxy.x && y0 == pxy.y && x1 == x0 + 1 && y1 == y0 + 1;
+            if (!own) {
+                A.spill[i] = 1;
+                continue;
+            }
+            const float g = guard_scale(S, F, A, i);
+            const float w = A.rayB[i].w;
+            const float fw = filter_weight(F, pf, x0, y0);
+            for (int b = 0; b < SPTX_NBINS; ++b) {
+                float v = A.L[b * P + i];
+                v = (g == 1.f) ? v : ((g == 0.f) ? 0.f : v * g);
+                acc[b] += v * w * fw;
+            }
+            acc[SPTX_NBINS] += fw;
+            touched = true;
+        }
+        if (touched)
+            for (int b = 0; b <= SPTX_NBINS; ++b) px[b] = acc[b];
+    }
+}
+
+// ---- K6: samples whose footprint covers other pixels (wide filters, pixel
+// edges): atomic splat, the device analogue of MergeFilmTile's overlap sums.
+__global__ void k_film_spill(DScene S, DFilm F, PathArrays A, RenderParams R) {
+    const size_t P = (size_t)A.capacity;
+    const int64_t nPaths = (int64_t)R.nPix * R.samplesInPass;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nPaths;
+         i += (int64_t)gridDim.x * blockDim.x) {
+        if (!A.spill[i]) continue;
+        const float2 pf = A.pfilm[i];
+        int x0, y0, x1, y1;
+        if (!sample_footprint(F, pf, &x0, &y0, &x1, &y1)) continue;
+        const float g = guard_scale(S, F, A, (size_t)i);
+        const float w = A.rayB[i].w;
+        for (int y = y0; y < y1; ++y)
+            for (int x = x0; x < x1; ++x) {
+                const float fw = filter_weight(F, pf, x, y);
+                float *px = F.pixels + ((size_t)(y - F.f.cropped[1]) * F.width + (x - F.f.cropped[0])) *
+                                           SPTX_SPECTRUM_STRIDE;
+                for (int b = 0; b < SPTX_NBINS; ++b) {
+                    float v = A.L[b * P + i];
+                    v = (g == 1.f) ? v : ((g == 0.f) ? 0.f : v * g);
+                    atomicAdd(px + b, v * w * fw);
+                }
+                atomicAdd(px + SPTX_NBINS, fw);
+            }
+    }
+}
+
+}  // namespace sptx

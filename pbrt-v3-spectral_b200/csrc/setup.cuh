@@ -1,0 +1,151 @@
+// setup.cuh -- one-time kernels run by sptx_upload_scene and the test hooks.
+#pragma once
+#include "resolve.cuh"
+
+namespace sptx {
+
+// Per-primitive 48-byte leaf block (see scene.cuh).
+__global__ void k_build_leafv(const sptx_prim *prims, int64_t nPrims, const sptx_triangle *tris,
+                              const sptx_mesh *meshes, const float *positions, float4 *leafv) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nPrims;
+         i += (int64_t)gridDim.x * blockDim.x) {
+        const sptx_prim P = prims[i];
+        float4 v0 = make_float4(0, 0, 0, 0), v1 = v0, v2 = v0;
+        if (P.kind == SPTX_PRIM_TRIANGLE) {
+            const sptx_triangle T = tris[P.shape];
+            const sptx_mesh M = meshes[T.mesh];
+            const float *p0 = positions + 3 * (size_t)(M.p_base + T.v[0]);
+            const float *p1 = positions + 3 * (size_t)(M.p_base + T.v[1]);
+            const float *p2 = positions + 3 * (size_t)(M.p_base + T.v[2]);
+            v0 = make_float4(p0[0], p0[1], p0[2], p1[0]);
+            v1 = make_float4(p1[1], p1[2], p2[0], p2[1]);
+            v2.x = p2[2];
+        }
+        v2.y = __int_as_float(P.shape);
+        v2.w = __int_as_float(P.kind);
+        leafv[3 * i] = v0;
+        leafv[3 * i + 1] = v1;
+        leafv[3 * i + 2] = v2;
+    }
+}
+
+// HaltonSampler::GetIndexForSample's per-pixel offset for every pixel of the
+// sample bounds (samplers/halton.cpp:96-112).
+__global__ void k_pixel_offsets(sptx_sampler s, int x0, int y0, int w, int h, uint64_t *out) {
+    const int64_t n = (int64_t)w * h;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+         i += (int64_t)gridDim.x * blockDim.x) {
+        int px = x0 + (int)(i % w), py = y0 + (int)(i / w);
+        out[i] = halton_pixel_offset(s, px, py);
+    }
+}
+
+// SpatialLightDistribution::ComputeDistribution for every voxel, eagerly
+// (core/lightdistrib.cpp:221-300).  halton5 holds RadicalInverse(d, i) for
+// d = 0..4, i = 0..127.  Row layout: func[n] | cdf[n+1] | funcInt.
+__global__ void k_voxel_tables(DScene S, const float *halton5, float *tables) {
+    const int n = S.n_lights;
+    const int64_t nVox = (int64_t)S.n_voxels[0] * S.n_voxels[1] * S.n_voxels[2];
+    const V3 wmin = mk(S.wb_min[0], S.wb_min[1], S.wb_min[2]);
+    const V3 wmax = mk(S.wb_max[0], S.wb_max[1], S.wb_max[2]);
+    for (int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; v < nVox;
+         v += (int64_t)gridDim.x * blockDim.x) {
+        int pz = (int)(v % S.n_voxels[2]);
+        int py = (int)((v / S.n_voxels[2]) % S.n_voxels[1]);
+        int px = (int)(v / ((int64_t)S.n_voxels[2] * S.n_voxels[1]));
+        V3 p0 = mk((float)px / (float)S.n_voxels[0], (float)py / (float)S.n_voxels[1],
+                   (float)pz / (float)S.n_voxels[2]);
+        V3 p1 = mk((float)(px + 1) / (float)S.n_voxels[0], (float)(py + 1) / (float)S.n_voxels[1],
+                   (float)(pz + 1) / (float)S.n_voxels[2]);
+        V3 a = mk(lerpf(p0.x, wmin.x, wmax.x), lerpf(p0.y, wmin.y, wmax.y), lerpf(p0.z, wmin.z, wmax.z));
+        V3 c = mk(lerpf(p1.x, wmin.x, wmax.x), lerpf(p1.y, wmin.y, wmax.y), lerpf(p1.z, wmin.z, wmax.z));
+        V3 vmin = mk(fminf(a.x, c.x), fminf(a.y, c.y), fminf(a.z, c.z));
+        V3 vmax = mk(fmaxf(a.x, c.x), fmaxf(a.y, c.y), fmaxf(a.z, c.z));
+        float *row = tables + v * (int64_t)(2 * n + 2);
+        for (int j = 0; j < n; ++j) row[j] = 0.f;
+        const int nSamples = 128;
+        for (int i = 0; i < nSamples; ++i) {
+            const float *h = halton5 + 5 * i;
+            RefPoint ref;
+            ref.p = mk(lerpf(h[0], vmin.x, vmax.x), lerpf(h[1], vmin.y, vmax.y), lerpf(h[2], vmin.z, vmax.z));
+            ref.pError = mk(0, 0, 0);
+            ref.n = mk(0, 0, 0);
+            V2 u{h[3], h[4]};
+            for (int j = 0; j < n; ++j) {
+                LiSample ls = light_sample_li(S, S.lights[j], ref, u);
+                if (ls.pdf > 0) {
+                    float yy = 0.f;
+                    if (!ls.black)
+                        for (int b = 0; b < SPTX_NBINS; ++b) yy += S.cie_y[b] * li_bin(S, ls, b);
+                    row[j] += y_finish(S, yy) / ls.pdf;
+                }
+            }
+        }
+        float sum = 0.f;
+        for (int j = 0; j < n; ++j) sum += row[j];
+        float avg = sum / (float)((size_t)nSamples * (size_t)n);
+        float minContrib = (avg > 0) ? (float)(.001 * (double)avg) : 1.f;
+        for (int j = 0; j < n; ++j) row[j] = (row[j] < minContrib) ? minContrib : row[j];
+        // Distribution1D, core/sampling.h:55-70
+        float *cdf = row + n;
+        cdf[0] = 0.f;
+        for (int j = 1; j < n + 1; ++j) cdf[j] = cdf[j - 1] + row[j - 1] / (float)n;
+        float funcInt = cdf[n];
+        if (funcInt == 0) {
+            for (int j = 1; j < n + 1; ++j) cdf[j] = (float)j / (float)n;
+        } else {
+            for (int j = 1; j < n + 1; ++j) cdf[j] /= funcInt;
+        }
+        row[2 * n + 1] = funcInt;
+    }
+}
+
+// Test hooks ---------------------------------------------------------------------
+__global__ void k_sampler_eval(DSampler H, const int *px, const int *py, const int *sample,
+                               const int *dim, int64_t n, float *out) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+         i += (int64_t)gridDim.x * blockDim.x) {
+        uint64_t off = halton_pixel_offset(H.s, px[i], py[i]);
+        uint64_t index = off + (uint64_t)sample[i] * (uint64_t)H.s.sample_stride;
+        out[i] = halton_sample(H, index, dim[i]);
+    }
+}
+
+__global__ void k_camera_rays(DCamera C, const float *cs, int64_t n, float wavelength,
+                              sptx_ray *rays, float *weights) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+         i += (int64_t)gridDim.x * blockDim.x) {
+        V2 pFilm{cs[5 * i], cs[5 * i + 1]};
+        V2 pLens{cs[5 * i + 3], cs[5 * i + 4]};
+        Ray r;
+        r.o = mk(0, 0, 0);
+        r.d = mk(0, 0, 1);
+        r.tMax = kInf;
+        float w = camera_ray(C, pFilm, pLens, wavelength, &r);
+        sptx_ray o;
+        o.o[0] = r.o.x; o.o[1] = r.o.y; o.o[2] = r.o.z;
+        o.d[0] = r.d.x; o.d[1] = r.d.y; o.d[2] = r.d.z;
+        o.t_max = r.tMax;
+        o.time = lerpf(cs[5 * i + 2], C.c.shutter_open, C.c.shutter_close);
+        rays[i] = o;
+        weights[i] = w;
+    }
+}
+
+// Film::WriteImage's spectral branch up to the file (core/film.cpp:226-306):
+// value * scale as float64, bin-major planes.
+__global__ void k_pack_dat(DFilm F, double *planes) {
+    const int64_t nPix = (int64_t)F.width * F.height;
+    const int64_t n = nPix * SPTX_NBINS;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+         i += (int64_t)gridDim.x * blockDim.x) {
+        int64_t b = i / nPix, p = i % nPix;
+        float v = F.pixels[p * SPTX_SPECTRUM_STRIDE + b];
+        // spectralData = L; += splatScale * splat (0); *= scale   (all float32)
+        v = v + 0.f;
+        v = v * F.f.scale;
+        planes[i] = (double)v;
+    }
+}
+
+}  // namespace sptx

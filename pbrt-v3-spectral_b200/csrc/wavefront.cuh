@@ -1,0 +1,78 @@
+// wavefront.cuh -- path state in HBM and the wavefront kernels' shared types.
+//
+// PathIntegrator::Li (integrators/path.cpp:64-188) restructured as a wavefront:
+//   generate -> [ intersect -> shade -> resolve ]* -> film
+// One "pass" carries nPix * S paths (S consecutive sample numbers of every
+// pixel of the render region); path id = s * nPix + pixel, so the film kernel
+// can add a pixel's samples in sample order, exactly like FilmTile::AddSample.
+// All per-path arrays are structure-of-arrays; spectra are bin-major
+// ([31][P]) so a warp reads 32 consecutive floats per bin.
+#pragma once
+#include "light.cuh"
+#include "sampler.cuh"
+
+namespace sptx {
+
+struct PathArrays {
+    int64_t capacity;  // P
+    // current path ray: {o.xyz, d.x} {d.y, d.z, etaScale, rayWeight}
+    float4 *rayA, *rayB;
+    // closest hit of the path ray: {prim, inst, b0, b1} {b2, t, -, -}
+    float4 *hitA, *hitB;
+    float *beta[2];  // [31][P], ping-pong per bounce
+    float *L;        // [31][P]
+    uint64_t *sindex;  // Halton index of the path's sample
+    uint32_t *info;    // bounces | specularBounce << 8 | dim << 16
+    float2 *pfilm;
+    // next-event estimation, pending until the resolve kernel
+    float4 *shA, *shB;    // shadow ray {o.xyz, d.x} {d.y, d.z, tMax, lightPdfSel}
+    float4 *misA, *misB;  // MIS ray {o.xyz, d.x} {d.y, d.z, bits(light), bits(flags)}
+    float *fa, *fb;       // [31][P] contributions of the two MIS strategies
+    // queues of path ids
+    int *q[2];
+    int *qNee;
+    int *counters;  // [0],[1]: sizes of q[0], q[1]; [2]: qNee size; [3]: error flags
+    uint8_t *spill;  // per path: film sample needs the atomic (wide filter) pass
+};
+
+enum { NEE_HAS_SHADOW = 1, NEE_HAS_MIS = 2 };
+enum { ERR_DIM_OVERFLOW = 1, ERR_INTERACTION = 2, ERR_TERMS = 4 };
+
+struct RenderParams {
+    int nPix;          // pixels in the render region
+    int samplesInPass; // S
+    int sampleBegin;   // first sample number of this pass
+    int maxDepth;
+    float rrThreshold;
+    const int2 *pixels;  // [nPix] pixel coordinates
+    float wavelength;    // ray.wavelength (550 for PathIntegrator)
+};
+
+struct DeviceCounters {
+    unsigned long long cameraRays, closestRays, shadowRays, vertices;
+};
+
+SPTX_DEV uint32_t pack_info(int bounces, int specular, int dim) {
+    return (uint32_t)bounces | ((uint32_t)specular << 8) | ((uint32_t)dim << 16);
+}
+
+// SampledSpectrum::y() tail, core/spectrum.h:415-421.
+SPTX_DEV float y_finish(const DScene &S, float yy) {
+    yy = (yy < 0) ? 0.f : yy;
+    return yy * S.y_scale_num / S.y_scale_den;
+}
+
+// Warp-aggregated append: one atomicAdd per warp (ballot + popc prefix).
+SPTX_DEV void queue_push(int *queue, int *counter, int value, bool pred) {
+    unsigned active = __activemask();
+    unsigned mask = __ballot_sync(active, pred);
+    if (mask == 0) return;
+    int leader = __ffs(mask) - 1;
+    int lane = threadIdx.x & 31;
+    int base = 0;
+    if (lane == leader) base = atomicAdd(counter, __popc(mask));
+    base = __shfl_sync(active, base, leader);
+    if (pred) queue[base + __popc(mask & ((1u << lane) - 1u))] = value;
+}
+
+}  // namespace sptx
