@@ -1,0 +1,881 @@
+// sptx_api.cu -- the C ABI of include/sptx.h: context, scene upload, render
+// driver, film access.  The only translation unit with device code; the
+// kernels live in the .cuh files it includes.
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "setup.cuh"
+
+using namespace sptx;
+
+static std::string g_last_error;
+
+struct sptx_ctx {
+    int device = 0;
+    std::string err;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr, ev3 = nullptr;
+    bool haveScene = false;
+    std::vector<void *> sceneAllocs;
+    std::vector<void *> pathAllocs;
+    DScene S;
+    DCamera C;
+    DSampler H;
+    DFilm F;
+    PathArrays A;
+    sptx_integrator integ;
+    int64_t maxPaths = 0;       // requested wavefront size
+    int64_t allocatedPaths = 0; // capacity of A
+    DeviceCounters *dCnt = nullptr;
+    sptx_counters counters;
+    bool profileKernels = false;
+    int smCount = 148;
+};
+
+static int fail(sptx_ctx *ctx, int code, const char *fmt, ...) {
+    char buf[1024];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    if (ctx)
+        ctx->err = buf;
+    else
+        g_last_error = buf;
+    return code;
+}
+
+#define CK(call)                                                                      \
+    do {                                                                              \
+        cudaError_t e_ = (call);                                                      \
+        if (e_ != cudaSuccess)                                                        \
+            return fail(ctx, SPTX_ECUDA, "%s: %s (%s:%d)", #call, cudaGetErrorString(e_), \
+                        __FILE__, __LINE__);                                          \
+    } while (0)
+
+static int grid_for(const sptx_ctx *ctx, int64_t n, int block = kBlock) {
+    int64_t blocks = (n + block - 1) / block;
+    int64_t cap = (int64_t)ctx->smCount * 16;  // a multiple of the SM count
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    return (int)blocks;
+}
+
+template <typename T>
+static int upload(sptx_ctx *ctx, std::vector<void *> &pool, const T *src, int64_t n, const T **out) {
+    *out = nullptr;
+    if (n <= 0) {
+        // keep kernels safe: a 1-element dummy so pointers are never null
+        void *p = nullptr;
+        CK(cudaMalloc(&p, sizeof(T) > 16 ? sizeof(T) : 16));
+        CK(cudaMemsetAsync(p, 0, sizeof(T) > 16 ? sizeof(T) : 16, ctx->stream));
+        pool.push_back(p);
+        *out = (const T *)p;
+        return SPTX_OK;
+    }
+    void *p = nullptr;
+    CK(cudaMalloc(&p, (size_t)n * sizeof(T)));
+    pool.push_back(p);
+    CK(cudaMemcpyAsync(p, src, (size_t)n * sizeof(T), cudaMemcpyHostToDevice, ctx->stream));
+    *out = (const T *)p;
+    return SPTX_OK;
+}
+
+template <typename T>
+static int dalloc(sptx_ctx *ctx, std::vector<void *> &pool, int64_t n, T **out) {
+    void *p = nullptr;
+    if (n < 1) n = 1;
+    CK(cudaMalloc(&p, (size_t)n * sizeof(T)));
+    pool.push_back(p);
+    *out = (T *)p;
+    return SPTX_OK;
+}
+
+static void free_pool(std::vector<void *> &pool) {
+    for (void *p : pool) cudaFree(p);
+    pool.clear();
+}
+
+extern "C" int sptx_abi_version(void) { return SPTX_ABI_VERSION; }
+
+extern "C" const char *sptx_last_error(const sptx_ctx *ctx) {
+    return ctx ? ctx->err.c_str() : g_last_error.c_str();
+}
+
+extern "C" int sptx_create(int device, sptx_ctx **out) {
+    sptx_ctx *ctx = nullptr;
+    if (!out) return fail(nullptr, SPTX_EINVAL, "sptx_create: out is NULL");
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0)
+        return fail(nullptr, SPTX_ECUDA,
+                    "sptx_create: no CUDA device (%s); there is no CPU fallback",
+                    e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
+    if (device < 0 || device >= count)
+        return fail(nullptr, SPTX_EINVAL, "sptx_create: device %d out of range [0,%d)", device, count);
+    ctx = new sptx_ctx();
+    ctx->device = device;
+    memset(&ctx->S, 0, sizeof(ctx->S));
+    memset(&ctx->C, 0, sizeof(ctx->C));
+    memset(&ctx->H, 0, sizeof(ctx->H));
+    memset(&ctx->F, 0, sizeof(ctx->F));
+    memset(&ctx->A, 0, sizeof(ctx->A));
+    memset(&ctx->counters, 0, sizeof(ctx->counters));
+    auto bail = [&](cudaError_t ce, const char *what) {
+        int rc = fail(nullptr, SPTX_ECUDA, "sptx_create: %s: %s", what, cudaGetErrorString(ce));
+        delete ctx;
+        return rc;
+    };
+    if ((e = cudaSetDevice(device)) != cudaSuccess) return bail(e, "cudaSetDevice");
+    cudaDeviceProp prop;
+    if ((e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess) return bail(e, "props");
+    ctx->smCount = prop.multiProcessorCount;
+    if ((e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess)
+        return bail(e, "cudaStreamCreate");
+    cudaEventCreate(&ctx->ev0);
+    cudaEventCreate(&ctx->ev1);
+    cudaEventCreate(&ctx->ev2);
+    cudaEventCreate(&ctx->ev3);
+    if ((e = cudaMalloc((void **)&ctx->dCnt, sizeof(DeviceCounters))) != cudaSuccess)
+        return bail(e, "cudaMalloc");
+    cudaMemset(ctx->dCnt, 0, sizeof(DeviceCounters));
+    // Traversal keeps a 64-entry stack per thread in local memory.
+    cudaDeviceSetLimit(cudaLimitStackSize, 2048);
+    ctx->profileKernels = getenv("SPTX_PROFILE_KERNELS") != nullptr;
+    *out = ctx;
+    return SPTX_OK;
+}
+
+extern "C" void sptx_destroy(sptx_ctx *ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    free_pool(ctx->sceneAllocs);
+    free_pool(ctx->pathAllocs);
+    if (ctx->dCnt) cudaFree(ctx->dCnt);
+    cudaEventDestroy(ctx->ev0);
+    cudaEventDestroy(ctx->ev1);
+    cudaEventDestroy(ctx->ev2);
+    cudaEventDestroy(ctx->ev3);
+    cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+extern "C" int sptx_set_wavefront_size(sptx_ctx *ctx, int64_t max_paths) {
+    if (!ctx) return fail(nullptr, SPTX_EINVAL, "ctx is NULL");
+    if (max_paths < 0) return fail(ctx, SPTX_EINVAL, "wavefront size must be >= 0");
+    ctx->maxPaths = max_paths;
+    return SPTX_OK;
+}
+
+// ---- scene upload ---------------------------------------------------------------
+
+static int validate_scene(sptx_ctx *ctx, const sptx_scene_desc *sc) {
+#define REQ(cond, msg)                                                        \
+    do {                                                                      \
+        if (!(cond)) return fail(ctx, SPTX_EINVAL, "sptx_upload_scene: %s", msg); \
+    } while (0)
+    REQ(sc->abi_version == SPTX_ABI_VERSION, "ABI version mismatch");
+    REQ(sc->n_bvhs >= 1 && sc->bvhs, "no aggregate");
+    REQ(sc->n_prims == 0 || sc->prims, "prims missing");
+    REQ(sc->n_nodes == 0 || sc->nodes, "nodes missing");
+    for (int64_t i = 0; i < sc->n_bvhs; ++i) {
+        const sptx_bvh &b = sc->bvhs[i];
+        REQ(b.node_base >= 0 && b.n_nodes >= 0 && (int64_t)b.node_base + b.n_nodes <= sc->n_nodes,
+            "bvh node range out of bounds");
+        REQ(b.prim_base >= 0 && b.n_prims >= 0 && (int64_t)b.prim_base + b.n_prims <= sc->n_prims,
+            "bvh primitive range out of bounds");
+        for (int k = 0; k < b.n_nodes; ++k) {
+            const sptx_bvh_node &n = sc->nodes[b.node_base + k];
+            if (n.n_prims > 0)
+                REQ(n.offset >= 0 && n.offset + (int)n.n_prims <= b.n_prims, "leaf range out of bounds");
+            else
+                REQ(n.offset > k && n.offset < b.n_nodes && k + 1 < b.n_nodes && n.axis < 3,
+                    "interior node malformed");
+        }
+    }
+    for (int64_t i = 0; i < sc->n_prims; ++i) {
+        const sptx_prim &p = sc->prims[i];
+        REQ(p.material >= -1 && p.material < sc->n_materials, "material index out of range");
+        REQ(p.light >= -1 && p.light < sc->n_lights, "light index out of range");
+        if (p.kind == SPTX_PRIM_TRIANGLE)
+            REQ(p.shape >= 0 && p.shape < sc->n_triangles, "triangle index out of range");
+        else if (p.kind == SPTX_PRIM_SPHERE)
+            REQ(p.shape >= 0 && p.shape < sc->n_spheres, "sphere index out of range");
+        else if (p.kind == SPTX_PRIM_INSTANCE)
+            REQ(p.shape >= 0 && p.shape < sc->n_instances, "instance index out of range");
+        else
+            return fail(ctx, SPTX_EUNSUPPORTED, "sptx_upload_scene: primitive kind %d", p.kind);
+    }
+    for (int64_t i = 0; i < sc->n_instances; ++i)
+        REQ(sc->instances[i].bvh > 0 && sc->instances[i].bvh < sc->n_bvhs, "instance bvh out of range");
+    for (int64_t i = 0; i < sc->n_triangles; ++i) {
+        const sptx_triangle &t = sc->triangles[i];
+        REQ(t.mesh >= 0 && t.mesh < sc->n_meshes, "mesh index out of range");
+        const sptx_mesh &m = sc->meshes[t.mesh];
+        for (int k = 0; k < 3; ++k) REQ(t.v[k] >= 0 && t.v[k] < m.n_vertices, "vertex index out of range");
+    }
+    for (int64_t i = 0; i < sc->n_meshes; ++i) {
+        const sptx_mesh &m = sc->meshes[i];
+        REQ(m.p_base >= 0 && (int64_t)m.p_base + m.n_vertices <= sc->n_positions, "mesh positions");
+        REQ(m.n_base < 0 || (int64_t)m.n_base + m.n_vertices <= sc->n_normals, "mesh normals");
+        REQ(m.s_base < 0 || (int64_t)m.s_base + m.n_vertices <= sc->n_tangents, "mesh tangents");
+        REQ(m.uv_base < 0 || (int64_t)m.uv_base + m.n_vertices <= sc->n_uvs, "mesh uvs");
+    }
+    for (int64_t i = 0; i < sc->n_materials; ++i) {
+        const sptx_material &m = sc->materials[i];
+        REQ(m.n_lobes >= 0 && m.n_lobes <= 8 && m.first_lobe >= 0 &&
+                (int64_t)m.first_lobe + m.n_lobes <= sc->n_lobes,
+            "material lobe range");
+        if (m.n_lobes > kMaxTerms)
+            return fail(ctx, SPTX_EUNSUPPORTED, "sptx_upload_scene: material with %d lobes (max %d)",
+                        m.n_lobes, kMaxTerms);
+    }
+    for (int64_t i = 0; i < sc->n_lobes; ++i) {
+        const sptx_lobe &l = sc->lobes[i];
+        REQ(l.type >= SPTX_LOBE_LAMBERT && l.type <= SPTX_LOBE_MICROFACET_REFL, "lobe type");
+        REQ(l.R < sc->n_spectra && l.T < sc->n_spectra && l.fr_eta_i < sc->n_spectra &&
+                l.fr_eta_t < sc->n_spectra && l.fr_k < sc->n_spectra,
+            "lobe spectrum row out of range");
+    }
+    for (int64_t i = 0; i < sc->n_lights; ++i) {
+        const sptx_light &l = sc->lights[i];
+        REQ(l.spectrum >= 0 && l.spectrum < sc->n_spectra, "light spectrum row out of range");
+        if (l.type == SPTX_LIGHT_DIFFUSE_AREA) {
+            if (l.shape_kind == SPTX_PRIM_TRIANGLE)
+                REQ(l.shape >= 0 && l.shape < sc->n_triangles, "light triangle out of range");
+            else if (l.shape_kind == SPTX_PRIM_SPHERE)
+                REQ(l.shape >= 0 && l.shape < sc->n_spheres, "light sphere out of range");
+            else
+                return fail(ctx, SPTX_EUNSUPPORTED, "sptx_upload_scene: area light shape kind");
+        } else if (l.type != SPTX_LIGHT_POINT)
+            return fail(ctx, SPTX_EUNSUPPORTED, "sptx_upload_scene: light type %d", l.type);
+    }
+    const sptx_film &f = sc->film;
+    REQ(f.cropped[2] >= f.cropped[0] && f.cropped[3] >= f.cropped[1], "film bounds");
+    REQ(f.filter_radius[0] > 0 && f.filter_radius[1] > 0, "filter radius");
+    if (sc->sampler.type == SPTX_SAMPLER_HALTON) {
+        REQ(sc->sampler.n_dims >= 5 && sc->n_primes >= sc->sampler.n_dims &&
+                sc->n_prime_sums >= sc->sampler.n_dims && sc->perms,
+            "Halton tables missing");
+        const int last = sc->sampler.n_dims - 1;
+        REQ((int64_t)sc->prime_sums[last] + sc->primes[last] <= sc->n_perms, "Halton permutations short");
+    } else
+        return fail(ctx, SPTX_EUNSUPPORTED,
+                    "sptx_upload_scene: only the Halton sampler is reproduced on the device "
+                    "(RandomSampler is one serial PCG32 stream per tile, SURVEY.md 0.5)");
+    if (sc->camera.type == SPTX_CAMERA_REALISTIC)
+        REQ(sc->camera.n_elements > 0 && sc->n_lens_floats >= 4 * sc->camera.n_elements &&
+                sc->camera.n_pupil_bounds > 0 && sc->n_pupil_floats >= 4 * sc->camera.n_pupil_bounds,
+            "realistic camera tables missing");
+    else if (sc->camera.type != SPTX_CAMERA_PERSPECTIVE)
+        return fail(ctx, SPTX_EUNSUPPORTED, "sptx_upload_scene: camera type %d", sc->camera.type);
+#undef REQ
+    return SPTX_OK;
+}
+
+// SampledSpectrum::y() on the host (core/spectrum.h:415-421).
+static float host_y(const sptx_scene_desc *sc, const float *row, float scale) {
+    float yy = 0.f;
+    for (int i = 0; i < SPTX_NBINS; ++i) yy += sc->cie_y[i] * (row[i] * scale);
+    yy = (yy < 0) ? 0 : yy;
+    float num = (float)(705 - 395);
+    float den = (float)(sc->cie_y_integral * (float)SPTX_NBINS);
+    return yy * num / den;
+}
+
+extern "C" int sptx_upload_scene(sptx_ctx *ctx, const sptx_scene_desc *sc) {
+    if (!ctx) return fail(nullptr, SPTX_EINVAL, "sptx_upload_scene: ctx is NULL");
+    if (!sc) return fail(ctx, SPTX_EINVAL, "sptx_upload_scene: scene is NULL");
+    int rc = validate_scene(ctx, sc);
+    if (rc) return rc;
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(ctx->stream));
+    free_pool(ctx->sceneAllocs);
+    ctx->haveScene = false;
+    std::vector<void *> &pool = ctx->sceneAllocs;
+    DScene &S = ctx->S;
+    memset(&S, 0, sizeof(S));
+
+    const sptx_bvh_node *dNodes;
+    if ((rc = upload(ctx, pool, sc->nodes, sc->n_nodes, &dNodes))) return rc;
+    S.nodes = reinterpret_cast<const float4 *>(dNodes);
+    if ((rc = upload(ctx, pool, sc->bvhs, sc->n_bvhs, &S.bvhs))) return rc;
+    if ((rc = upload(ctx, pool, sc->prims, sc->n_prims, &S.prims))) return rc;
+    if ((rc = upload(ctx, pool, sc->meshes, sc->n_meshes, &S.meshes))) return rc;
+    if ((rc = upload(ctx, pool, sc->triangles, sc->n_triangles, &S.triangles))) return rc;
+    if ((rc = upload(ctx, pool, sc->positions, 3 * sc->n_positions, &S.positions))) return rc;
+    if ((rc = upload(ctx, pool, sc->normals, 3 * sc->n_normals, &S.normals))) return rc;
+    if ((rc = upload(ctx, pool, sc->tangents, 3 * sc->n_tangents, &S.tangents))) return rc;
+    if ((rc = upload(ctx, pool, sc->uvs, 2 * sc->n_uvs, &S.uvs))) return rc;
+    if ((rc = upload(ctx, pool, sc->spheres, sc->n_spheres, &S.spheres))) return rc;
+    if ((rc = upload(ctx, pool, sc->instances, sc->n_instances, &S.instances))) return rc;
+    if ((rc = upload(ctx, pool, sc->materials, sc->n_materials, &S.materials))) return rc;
+    if ((rc = upload(ctx, pool, sc->lobes, sc->n_lobes, &S.lobes))) return rc;
+    if ((rc = upload(ctx, pool, sc->spectra, SPTX_SPECTRUM_STRIDE * sc->n_spectra, &S.spectra))) return rc;
+    if ((rc = upload(ctx, pool, sc->lights, sc->n_lights, &S.lights))) return rc;
+    S.n_lights = (int)sc->n_lights;
+    S.n_bvhs = (int)sc->n_bvhs;
+    for (int i = 0; i < SPTX_SPECTRUM_STRIDE; ++i) S.cie_y[i] = i < SPTX_NBINS ? sc->cie_y[i] : 0.f;
+    S.y_scale_num = (float)(705 - 395);  // sampledLambdaEnd - sampledLambdaStart
+    S.y_scale_den = (float)(sc->cie_y_integral * (float)SPTX_NBINS);
+
+    // leaf blocks
+    float4 *leafv;
+    if ((rc = dalloc(ctx, pool, 3 * std::max<int64_t>(sc->n_prims, 1), &leafv))) return rc;
+    if (sc->n_prims > 0)
+        k_build_leafv<<<grid_for(ctx, sc->n_prims), kBlock, 0, ctx->stream>>>(
+            S.prims, sc->n_prims, S.triangles, S.meshes, S.positions, leafv);
+    S.leafv = leafv;
+
+    // scene.WorldBound() == the root node's bounds (accelerators/bvh.cpp:227-229)
+    if (sc->bvhs[0].n_nodes > 0) {
+        const sptx_bvh_node &root = sc->nodes[sc->bvhs[0].node_base];
+        for (int i = 0; i < 3; ++i) {
+            S.wb_min[i] = root.bmin[i];
+            S.wb_max[i] = root.bmax[i];
+        }
+    }
+
+    // ---- light selection (core/lightdistrib.cpp:48-66) ----
+    ctx->integ = sc->integrator;
+    const int nL = S.n_lights;
+    int strategy = sc->integrator.light_strategy;
+    if (nL == 1) strategy = SPTX_LIGHTS_UNIFORM;
+    S.light_strategy = strategy;
+    S.n_voxels[0] = S.n_voxels[1] = S.n_voxels[2] = 1;
+    {
+        // Uniform: func = 1; Power: func = light->Power().y()
+        std::vector<float> tab((size_t)2 * nL + 1, 0.f);
+        for (int j = 0; j < nL; ++j) {
+            float v = 1.f;
+            if (strategy == SPTX_LIGHTS_POWER) {
+                const sptx_light &l = sc->lights[j];
+                const float *row = sc->spectra + (size_t)l.spectrum * SPTX_SPECTRUM_STRIDE;
+                float tmp[SPTX_NBINS];
+                for (int b = 0; b < SPTX_NBINS; ++b) {
+                    if (l.type == SPTX_LIGHT_DIFFUSE_AREA)  // (twoSided ? 2 : 1) * Lemit * area * Pi
+                        tmp[b] = row[b] * (l.two_sided ? 2.f : 1.f) * l.area * kPi;
+                    else  // 4 * Pi * I
+                        tmp[b] = row[b] * (4.f * kPi);
+                }
+                v = host_y(sc, tmp, 1.f);
+            }
+            tab[j] = v;
+        }
+        float funcInt = 0.f;
+        if (nL > 0) {
+            float *cdf = tab.data() + nL;
+            cdf[0] = 0.f;
+            for (int j = 1; j < nL + 1; ++j) cdf[j] = cdf[j - 1] + tab[j - 1] / (float)nL;
+            funcInt = cdf[nL];
+            if (funcInt == 0)
+                for (int j = 1; j < nL + 1; ++j) cdf[j] = (float)j / (float)nL;
+            else
+                for (int j = 1; j < nL + 1; ++j) cdf[j] /= funcInt;
+        }
+        S.light_func_int = funcInt;
+        if ((rc = upload(ctx, pool, tab.data(), (int64_t)tab.size(), &S.light_func))) return rc;
+    }
+    S.voxel_tables = S.light_func;
+    if (strategy == SPTX_LIGHTS_SPATIAL && nL > 0) {
+        // SpatialLightDistribution::SpatialLightDistribution, lightdistrib.cpp:91-111
+        float diag[3] = {S.wb_max[0] - S.wb_min[0], S.wb_max[1] - S.wb_min[1], S.wb_max[2] - S.wb_min[2]};
+        int me = (diag[0] > diag[1] && diag[0] > diag[2]) ? 0 : ((diag[1] > diag[2]) ? 1 : 2);
+        float bmax = diag[me];
+        const int maxVoxels = 64;
+        int64_t nVox = 1;
+        for (int i = 0; i < 3; ++i) {
+            S.n_voxels[i] = std::max(1, (int)std::round(diag[i] / bmax * (float)maxVoxels));
+            nVox *= S.n_voxels[i];
+        }
+        const int64_t rowFloats = 2 * (int64_t)nL + 2;
+        const double bytes = (double)nVox * rowFloats * 4.0;
+        if (bytes > 16e9)
+            return fail(ctx, SPTX_EUNSUPPORTED,
+                        "sptx_upload_scene: spatial light distribution for %d lights needs %.1f GB "
+                        "when built eagerly; use lightsamplestrategy \"power\" or \"uniform\"",
+                        nL, bytes * 1e-9);
+        // RadicalInverse(d, i), d = 0..4, i = 0..127 (bases 2, 3, 5, 7, 11)
+        std::vector<float> h5(5 * 128);
+        const uint32_t bases[5] = {2, 3, 5, 7, 11};
+        for (int i = 0; i < 128; ++i) {
+            h5[5 * i] = (float)((double)reverse_bits64((uint64_t)i) * 0x1p-64);
+            for (int d = 1; d < 5; ++d) h5[5 * i + d] = radical_inverse_base((uint64_t)i, bases[d]);
+        }
+        const float *dH5;
+        if ((rc = upload(ctx, pool, h5.data(), (int64_t)h5.size(), &dH5))) return rc;
+        float *tables;
+        if ((rc = dalloc(ctx, pool, nVox * rowFloats, &tables))) return rc;
+        S.voxel_tables = tables;
+        k_voxel_tables<<<grid_for(ctx, nVox, 64), 64, 0, ctx->stream>>>(S, dH5, tables);
+    }
+
+    // ---- camera ----
+    DCamera &C = ctx->C;
+    memset(&C, 0, sizeof(C));
+    C.c = sc->camera;
+    C.full_res[0] = sc->film.full_res[0];
+    C.full_res[1] = sc->film.full_res[1];
+    if ((rc = upload(ctx, pool, sc->lens_elements, sc->n_lens_floats, &C.lens))) return rc;
+    if ((rc = upload(ctx, pool, sc->exit_pupil_bounds, sc->n_pupil_floats, &C.pupil))) return rc;
+    {
+        // Film::GetPhysicalExtent, core/film.cpp:94-99
+        float aspect = (float)sc->film.full_res[1] / (float)sc->film.full_res[0];
+        float d = sc->film.diagonal;
+        float x = std::sqrt(d * d / (1 + aspect * aspect));
+        float y = aspect * x;
+        C.film_extent[0] = -x / 2;
+        C.film_extent[1] = -y / 2;
+        C.film_extent[2] = x / 2;
+        C.film_extent[3] = y / 2;
+    }
+
+    // ---- sampler ----
+    DSampler &H = ctx->H;
+    memset(&H, 0, sizeof(H));
+    H.s = sc->sampler;
+    for (int i = 0; i < 4; ++i) H.sb[i] = sc->film.sample_bounds[i];
+    if ((rc = upload(ctx, pool, sc->primes, (int64_t)sc->sampler.n_dims, &H.primes))) return rc;
+    if ((rc = upload(ctx, pool, sc->prime_sums, (int64_t)sc->sampler.n_dims, &H.prime_sums))) return rc;
+    if ((rc = upload(ctx, pool, sc->perms, sc->n_perms, &H.perms))) return rc;
+    {
+        int w = std::max(0, H.sb[2] - H.sb[0]), h = std::max(0, H.sb[3] - H.sb[1]);
+        uint64_t *off;
+        if ((rc = dalloc(ctx, pool, (int64_t)w * h, &off))) return rc;
+        if ((int64_t)w * h > 0)
+            k_pixel_offsets<<<grid_for(ctx, (int64_t)w * h), kBlock, 0, ctx->stream>>>(
+                H.s, H.sb[0], H.sb[1], w, h, off);
+        H.pixel_offset = off;
+    }
+
+    // ---- film ----
+    DFilm &F = ctx->F;
+    memset(&F, 0, sizeof(F));
+    F.f = sc->film;
+    F.width = std::max(0, sc->film.cropped[2] - sc->film.cropped[0]);
+    F.height = std::max(0, sc->film.cropped[3] - sc->film.cropped[1]);
+    if ((rc = dalloc(ctx, pool, (int64_t)F.width * F.height * SPTX_SPECTRUM_STRIDE, &F.pixels))) return rc;
+    CK(cudaMemsetAsync(F.pixels, 0, (size_t)std::max<int64_t>(1, (int64_t)F.width * F.height) *
+                                        SPTX_SPECTRUM_STRIDE * sizeof(float), ctx->stream));
+    CK(cudaGetLastError());
+    CK(cudaStreamSynchronize(ctx->stream));
+    ctx->haveScene = true;
+    return SPTX_OK;
+}
+
+// ---- render driver ------------------------------------------------------------------
+
+__global__ void k_set_counters(int *counters, int a, int va, int b, int vb) {
+    if (a >= 0) counters[a] = va;
+    if (b >= 0) counters[b] = vb;
+}
+
+static int ensure_paths(sptx_ctx *ctx, int64_t P) {
+    if (ctx->allocatedPaths >= P) return SPTX_OK;
+    CK(cudaStreamSynchronize(ctx->stream));
+    free_pool(ctx->pathAllocs);
+    ctx->allocatedPaths = 0;
+    std::vector<void *> &pool = ctx->pathAllocs;
+    PathArrays &A = ctx->A;
+    memset(&A, 0, sizeof(A));
+    A.capacity = P;
+    int rc;
+#define DA(field, count) \
+    if ((rc = dalloc(ctx, pool, (int64_t)(count), &A.field))) return rc
+    DA(rayA, P);
+    DA(rayB, P);
+    DA(hitA, P);
+    DA(hitB, P);
+    DA(beta[0], P * SPTX_NBINS);
+    DA(beta[1], P * SPTX_NBINS);
+    DA(L, P * SPTX_NBINS);
+    DA(sindex, P);
+    DA(info, P);
+    DA(pfilm, P);
+    DA(shA, P);
+    DA(shB, P);
+    DA(misA, P);
+    DA(misB, P);
+    DA(fa, P * SPTX_NBINS);
+    DA(fb, P * SPTX_NBINS);
+    DA(q[0], P);
+    DA(q[1], P);
+    DA(qNee, P);
+    DA(counters, 8);
+    DA(spill, P);
+#undef DA
+    CK(cudaMemsetAsync(A.counters, 0, 8 * sizeof(int), ctx->stream));
+    ctx->allocatedPaths = P;
+    return SPTX_OK;
+}
+
+// Renders `pixels` (host list) for sample numbers [s0, s1).
+static int render_pixels(sptx_ctx *ctx, const std::vector<int2> &pixels, int s0, int s1) {
+    if (pixels.empty() || s1 <= s0) return SPTX_OK;
+    int rc;
+    const int64_t want = ctx->maxPaths > 0 ? ctx->maxPaths : ((int64_t)1 << 22);
+    const int64_t nPixAll = (int64_t)pixels.size();
+    const int64_t chunkPix = std::min<int64_t>(nPixAll, want);
+    int S_pass = (int)std::max<int64_t>(1, std::min<int64_t>(s1 - s0, want / chunkPix));
+    if ((rc = ensure_paths(ctx, chunkPix * S_pass))) return rc;
+    int2 *dPixels = nullptr;
+    CK(cudaMalloc((void **)&dPixels, (size_t)nPixAll * sizeof(int2)));
+    cudaError_t ce = cudaMemcpyAsync(dPixels, pixels.data(), (size_t)nPixAll * sizeof(int2),
+                                     cudaMemcpyHostToDevice, ctx->stream);
+    if (ce != cudaSuccess) {
+        cudaFree(dPixels);
+        return fail(ctx, SPTX_ECUDA, "pixel list upload: %s", cudaGetErrorString(ce));
+    }
+    PathArrays &A = ctx->A;
+    const int maxDepth = ctx->integ.max_depth;
+    uint64_t launches = 0;
+    const bool prof = ctx->profileKernels;
+    float msTrav = 0.f, msShade = 0.f, msFilm = 0.f;
+    auto tic = [&]() { if (prof) cudaEventRecord(ctx->ev2, ctx->stream); };
+    auto toc = [&](float &acc) {
+        if (prof) {
+            cudaEventRecord(ctx->ev3, ctx->stream);
+            cudaEventSynchronize(ctx->ev3);
+            float ms = 0.f;
+            cudaEventElapsedTime(&ms, ctx->ev2, ctx->ev3);
+            acc += ms;
+        }
+    };
+    cudaEventRecord(ctx->ev0, ctx->stream);
+    for (int64_t p0 = 0; p0 < nPixAll; p0 += chunkPix) {
+        const int nPix = (int)std::min<int64_t>(chunkPix, nPixAll - p0);
+        for (int s = s0; s < s1; s += S_pass) {
+            RenderParams R;
+            R.nPix = nPix;
+            R.samplesInPass = std::min(S_pass, s1 - s);
+            R.sampleBegin = s;
+            R.maxDepth = maxDepth;
+            R.rrThreshold = ctx->integ.rr_threshold;
+            R.pixels = dPixels + p0;
+            R.wavelength = 550.f;
+            const int64_t nPaths = (int64_t)nPix * R.samplesInPass;
+            const int g = grid_for(ctx, nPaths);
+            k_set_counters<<<1, 1, 0, ctx->stream>>>(A.counters, 0, 0, 1, 0);
+            tic();
+            k_generate<<<g, kBlock, 0, ctx->stream>>>(ctx->S, ctx->C, ctx->H, A, R, ctx->dCnt);
+            toc(msShade);
+            launches += 2;
+            int qi = 0, betaIn = 0;
+            for (int bounce = 0; bounce <= maxDepth; ++bounce) {
+                tic();
+                k_intersect<<<g, kBlock, 0, ctx->stream>>>(ctx->S, A, qi, ctx->dCnt);
+                toc(msTrav);
+                k_set_counters<<<1, 1, 0, ctx->stream>>>(A.counters, qi ^ 1, 0, 2, 0);
+                tic();
+                k_shade<<<g, kBlock, 0, ctx->stream>>>(ctx->S, ctx->H, A, R, qi, betaIn, ctx->dCnt);
+                toc(msShade);
+                launches += 3;
+                if (bounce < maxDepth) {
+                    tic();
+                    k_resolve<<<g, kBlock, 0, ctx->stream>>>(ctx->S, A, betaIn, ctx->dCnt);
+                    toc(msTrav);
+                    ++launches;
+                }
+                qi ^= 1;
+                betaIn ^= 1;
+            }
+            tic();
+            k_film<<<grid_for(ctx, nPix), kBlock, 0, ctx->stream>>>(ctx->S, ctx->F, A, R);
+            k_film_spill<<<g, kBlock, 0, ctx->stream>>>(ctx->S, ctx->F, A, R);
+            toc(msFilm);
+            launches += 2;
+        }
+    }
+    cudaEventRecord(ctx->ev1, ctx->stream);
+    ce = cudaStreamSynchronize(ctx->stream);
+    cudaFree(dPixels);
+    if (ce != cudaSuccess) return fail(ctx, SPTX_ECUDA, "render: %s", cudaGetErrorString(ce));
+    CK(cudaGetLastError());
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
+    ctx->counters.render_ms += ms;
+    ctx->counters.traverse_ms += msTrav;
+    ctx->counters.shade_ms += msShade;
+    ctx->counters.film_ms += msFilm;
+    ctx->counters.kernel_launches += launches;
+    int flags[8];
+    CK(cudaMemcpy(flags, A.counters, sizeof(flags), cudaMemcpyDeviceToHost));
+    if (flags[3]) {
+        int f = flags[3];
+        cudaMemset(A.counters + 3, 0, sizeof(int));
+        if (f & ERR_DIM_OVERFLOW)
+            return fail(ctx, SPTX_EINVAL,
+                        "render: a path ran past the %d Halton dimensions uploaded "
+                        "(the reference aborts at 1000, samplers/halton.h:71-76)", ctx->H.s.n_dims);
+        return fail(ctx, SPTX_EINVAL, "render: device error flags 0x%x", f);
+    }
+    return SPTX_OK;
+}
+
+static void region_pixels(const sptx_ctx *ctx, const int32_t *bounds, std::vector<int2> *out) {
+    int b[4];
+    for (int i = 0; i < 4; ++i) b[i] = ctx->F.f.sample_bounds[i];
+    auto clip = [&](const int32_t *o) {
+        b[0] = std::max(b[0], o[0]);
+        b[1] = std::max(b[1], o[1]);
+        b[2] = std::min(b[2], o[2]);
+        b[3] = std::min(b[3], o[3]);
+    };
+    clip(ctx->integ.pixel_bounds);  // the InsideExclusive(pixel, pixelBounds) test
+    if (bounds) clip(bounds);
+    for (int y = b[1]; y < b[3]; ++y)
+        for (int x = b[0]; x < b[2]; ++x) out->push_back(make_int2(x, y));
+}
+
+extern "C" int sptx_render(sptx_ctx *ctx, const int32_t *pixel_bounds, int sample_begin,
+                           int sample_end) {
+    if (!ctx) return fail(nullptr, SPTX_EINVAL, "sptx_render: ctx is NULL");
+    if (!ctx->haveScene) return fail(ctx, SPTX_ESTATE, "sptx_render: no scene uploaded");
+    if (sample_begin < 0 || sample_end < sample_begin)
+        return fail(ctx, SPTX_EINVAL, "sptx_render: bad sample range [%d,%d)", sample_begin, sample_end);
+    CK(cudaSetDevice(ctx->device));
+    std::vector<int2> pixels;
+    region_pixels(ctx, pixel_bounds, &pixels);
+    return render_pixels(ctx, pixels, sample_begin, sample_end);
+}
+
+extern "C" int sptx_render_tiles(sptx_ctx *ctx, int part, int n_parts, int sample_begin,
+                                 int sample_end) {
+    if (!ctx) return fail(nullptr, SPTX_EINVAL, "sptx_render_tiles: ctx is NULL");
+    if (!ctx->haveScene) return fail(ctx, SPTX_ESTATE, "sptx_render_tiles: no scene uploaded");
+    if (n_parts < 1 || part < 0 || part >= n_parts)
+        return fail(ctx, SPTX_EINVAL, "sptx_render_tiles: part %d of %d", part, n_parts);
+    CK(cudaSetDevice(ctx->device));
+    // Tiles as SamplerIntegrator::Render cuts them (core/integrator.cpp:232-257).
+    const int *sb = ctx->F.f.sample_bounds;
+    const int *pb = ctx->integ.pixel_bounds;
+    const int tileSize = 16;
+    const int ntx = (sb[2] - sb[0] + tileSize - 1) / tileSize;
+    const int nty = (sb[3] - sb[1] + tileSize - 1) / tileSize;
+    std::vector<int2> pixels;
+    for (int ty = 0; ty < nty; ++ty)
+        for (int tx = 0; tx < ntx; ++tx) {
+            if ((ty * ntx + tx) % n_parts != part) continue;
+            int x0 = sb[0] + tx * tileSize, x1 = std::min(x0 + tileSize, sb[2]);
+            int y0 = sb[1] + ty * tileSize, y1 = std::min(y0 + tileSize, sb[3]);
+            for (int y = y0; y < y1; ++y)
+                for (int x = x0; x < x1; ++x)
+                    if (x >= pb[0] && x < pb[2] && y >= pb[1] && y < pb[3])
+                        pixels.push_back(make_int2(x, y));
+        }
+    return render_pixels(ctx, pixels, sample_begin, sample_end);
+}
+
+// ---- film -----------------------------------------------------------------------------
+
+extern "C" int sptx_film_clear(sptx_ctx *ctx) {
+    if (!ctx) return fail(nullptr, SPTX_EINVAL, "sptx_film_clear: ctx is NULL");
+    if (!ctx->haveScene) return fail(ctx, SPTX_ESTATE, "sptx_film_clear: no scene uploaded");
+    CK(cudaSetDevice(ctx->device));
+    size_t n = (size_t)ctx->F.width * ctx->F.height * SPTX_SPECTRUM_STRIDE;
+    if (n) CK(cudaMemsetAsync(ctx->F.pixels, 0, n * sizeof(float), ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return SPTX_OK;
+}
+
+extern "C" int sptx_film_device_ptr(sptx_ctx *ctx, void **d_film, int64_t *n_floats) {
+    if (!ctx) return fail(nullptr, SPTX_EINVAL, "sptx_film_device_ptr: ctx is NULL");
+    if (!ctx->haveScene) return fail(ctx, SPTX_ESTATE, "sptx_film_device_ptr: no scene uploaded");
+    if (d_film) *d_film = ctx->F.pixels;
+    if (n_floats) *n_floats = (int64_t)ctx->F.width * ctx->F.height * SPTX_SPECTRUM_STRIDE;
+    return SPTX_OK;
+}
+
+extern "C" int sptx_film_download(sptx_ctx *ctx, float *contrib, float *weight) {
+    if (!ctx) return fail(nullptr, SPTX_EINVAL, "sptx_film_download: ctx is NULL");
+    if (!ctx->haveScene) return fail(ctx, SPTX_ESTATE, "sptx_film_download: no scene uploaded");
+    CK(cudaSetDevice(ctx->device));
+    const size_t nPix = (size_t)ctx->F.width * ctx->F.height;
+    std::vector<float> tmp(nPix * SPTX_SPECTRUM_STRIDE);
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (nPix) CK(cudaMemcpy(tmp.data(), ctx->F.pixels, tmp.size() * sizeof(float), cudaMemcpyDeviceToHost));
+    for (size_t p = 0; p < nPix; ++p) {
+        if (contrib)
+            memcpy(contrib + p * SPTX_NBINS, tmp.data() + p * SPTX_SPECTRUM_STRIDE, SPTX_NBINS * sizeof(float));
+        if (weight) weight[p] = tmp[p * SPTX_SPECTRUM_STRIDE + SPTX_NBINS];
+    }
+    return SPTX_OK;
+}
+
+extern "C" int sptx_film_pack_dat(sptx_ctx *ctx, double *planes) {
+    if (!ctx) return fail(nullptr, SPTX_EINVAL, "sptx_film_pack_dat: ctx is NULL");
+    if (!ctx->haveScene) return fail(ctx, SPTX_ESTATE, "sptx_film_pack_dat: no scene uploaded");
+    if (!planes) return fail(ctx, SPTX_EINVAL, "sptx_film_pack_dat: planes is NULL");
+    CK(cudaSetDevice(ctx->device));
+    const int64_t n = (int64_t)ctx->F.width * ctx->F.height * SPTX_NBINS;
+    if (n == 0) return SPTX_OK;
+    double *d = nullptr;
+    CK(cudaMalloc((void **)&d, (size_t)n * sizeof(double)));
+    k_pack_dat<<<grid_for(ctx, n), kBlock, 0, ctx->stream>>>(ctx->F, d);
+    cudaError_t e = cudaMemcpyAsync(planes, d, (size_t)n * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    cudaFree(d);
+    if (e != cudaSuccess) return fail(ctx, SPTX_ECUDA, "sptx_film_pack_dat: %s", cudaGetErrorString(e));
+    return SPTX_OK;
+}
+
+extern "C" int sptx_write_dat(const char *path, int width, int height, const double *planes) {
+    // Film::WriteImage, core/film.cpp:267-306: text header, then binary planes.
+    FILE *f = fopen(path, "wb");
+    if (!f) return fail(nullptr, SPTX_EIO, "sptx_write_dat: cannot open %s", path);
+    fprintf(f, "%d %d %d\n", width, height, SPTX_NBINS);
+    fprintf(f, "v3 \n");
+    size_t n = (size_t)width * height * SPTX_NBINS;
+    size_t w = fwrite(planes, sizeof(double), n, f);
+    fclose(f);
+    if (w != n) return fail(nullptr, SPTX_EIO, "sptx_write_dat: short write to %s", path);
+    return SPTX_OK;
+}
+
+// ---- counters ----------------------------------------------------------------------------
+
+extern "C" int sptx_get_counters(sptx_ctx *ctx, sptx_counters *out) {
+    if (!ctx || !out) return fail(ctx, SPTX_EINVAL, "sptx_get_counters: NULL argument");
+    CK(cudaSetDevice(ctx->device));
+    DeviceCounters dc;
+    CK(cudaStreamSynchronize(ctx->stream));
+    CK(cudaMemcpy(&dc, ctx->dCnt, sizeof(dc), cudaMemcpyDeviceToHost));
+    ctx->counters.camera_rays = dc.cameraRays;
+    ctx->counters.closest_hit_rays = dc.closestRays;
+    ctx->counters.shadow_rays = dc.shadowRays;
+    ctx->counters.path_vertices = dc.vertices;
+    *out = ctx->counters;
+    return SPTX_OK;
+}
+
+extern "C" int sptx_reset_counters(sptx_ctx *ctx) {
+    if (!ctx) return fail(nullptr, SPTX_EINVAL, "sptx_reset_counters: ctx is NULL");
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(ctx->stream));
+    CK(cudaMemset(ctx->dCnt, 0, sizeof(DeviceCounters)));
+    memset(&ctx->counters, 0, sizeof(ctx->counters));
+    return SPTX_OK;
+}
+
+// ---- ray batches ----------------------------------------------------------------------------
+
+extern "C" int sptx_intersect_batch_device(sptx_ctx *ctx, const void *d_rays, int64_t n, void *d_hits,
+                                           int any_hit, int with_counters, float *ms) {
+    if (!ctx) return fail(nullptr, SPTX_EINVAL, "sptx_intersect_batch: ctx is NULL");
+    if (!ctx->haveScene) return fail(ctx, SPTX_ESTATE, "sptx_intersect_batch: no scene uploaded");
+    if (n < 0 || (n > 0 && (!d_rays || !d_hits))) return fail(ctx, SPTX_EINVAL, "sptx_intersect_batch: bad arguments");
+    CK(cudaSetDevice(ctx->device));
+    if (n == 0) {
+        if (ms) *ms = 0.f;
+        return SPTX_OK;
+    }
+    const sptx_ray *r = (const sptx_ray *)d_rays;
+    sptx_hit *h = (sptx_hit *)d_hits;
+    const int g = grid_for(ctx, n);
+    cudaEventRecord(ctx->ev0, ctx->stream);
+    if (any_hit) {
+        if (with_counters)
+            k_ray_batch<true, true><<<g, kBlock, 0, ctx->stream>>>(ctx->S, r, n, h);
+        else
+            k_ray_batch<true, false><<<g, kBlock, 0, ctx->stream>>>(ctx->S, r, n, h);
+    } else {
+        if (with_counters)
+            k_ray_batch<false, true><<<g, kBlock, 0, ctx->stream>>>(ctx->S, r, n, h);
+        else
+            k_ray_batch<false, false><<<g, kBlock, 0, ctx->stream>>>(ctx->S, r, n, h);
+    }
+    cudaEventRecord(ctx->ev1, ctx->stream);
+    CK(cudaStreamSynchronize(ctx->stream));
+    CK(cudaGetLastError());
+    float t = 0.f;
+    cudaEventElapsedTime(&t, ctx->ev0, ctx->ev1);
+    if (ms) *ms = t;
+    ctx->counters.kernel_launches += 1;
+    ctx->counters.traverse_ms += t;
+    return SPTX_OK;
+}
+
+extern "C" int sptx_intersect_batch(sptx_ctx *ctx, const sptx_ray *rays, int64_t n, sptx_hit *hits,
+                                    int any_hit, int with_counters) {
+    if (!ctx) return fail(nullptr, SPTX_EINVAL, "sptx_intersect_batch: ctx is NULL");
+    if (!ctx->haveScene) return fail(ctx, SPTX_ESTATE, "sptx_intersect_batch: no scene uploaded");
+    if (n < 0 || (n > 0 && (!rays || !hits))) return fail(ctx, SPTX_EINVAL, "sptx_intersect_batch: bad arguments");
+    if (n == 0) return SPTX_OK;
+    CK(cudaSetDevice(ctx->device));
+    void *dR = nullptr, *dH = nullptr;
+    CK(cudaMalloc(&dR, (size_t)n * sizeof(sptx_ray)));
+    cudaError_t e = cudaMalloc(&dH, (size_t)n * sizeof(sptx_hit));
+    if (e != cudaSuccess) {
+        cudaFree(dR);
+        return fail(ctx, SPTX_ECUDA, "sptx_intersect_batch: %s", cudaGetErrorString(e));
+    }
+    int rc = SPTX_OK;
+    e = cudaMemcpyAsync(dR, rays, (size_t)n * sizeof(sptx_ray), cudaMemcpyHostToDevice, ctx->stream);
+    if (e == cudaSuccess) rc = sptx_intersect_batch_device(ctx, dR, n, dH, any_hit, with_counters, nullptr);
+    if (e == cudaSuccess && rc == SPTX_OK)
+        e = cudaMemcpy(hits, dH, (size_t)n * sizeof(sptx_hit), cudaMemcpyDeviceToHost);
+    cudaFree(dR);
+    cudaFree(dH);
+    if (e != cudaSuccess) return fail(ctx, SPTX_ECUDA, "sptx_intersect_batch: %s", cudaGetErrorString(e));
+    return rc;
+}
+
+// ---- test hooks --------------------------------------------------------------------------------
+
+extern "C" int sptx_sampler_eval(sptx_ctx *ctx, const int32_t *px, const int32_t *py, const int32_t *sample,
+                                 const int32_t *dim, int64_t n, float *values) {
+    if (!ctx) return fail(nullptr, SPTX_EINVAL, "sptx_sampler_eval: ctx is NULL");
+    if (!ctx->haveScene) return fail(ctx, SPTX_ESTATE, "sptx_sampler_eval: no scene uploaded");
+    if (n <= 0) return SPTX_OK;
+    CK(cudaSetDevice(ctx->device));
+    std::vector<void *> pool;
+    const int32_t *dpx, *dpy, *ds, *dd;
+    float *dv;
+    int rc;
+    if ((rc = upload(ctx, pool, px, n, &dpx)) || (rc = upload(ctx, pool, py, n, &dpy)) ||
+        (rc = upload(ctx, pool, sample, n, &ds)) || (rc = upload(ctx, pool, dim, n, &dd)) ||
+        (rc = dalloc(ctx, pool, n, &dv))) {
+        free_pool(pool);
+        return rc;
+    }
+    k_sampler_eval<<<grid_for(ctx, n), kBlock, 0, ctx->stream>>>(ctx->H, dpx, dpy, ds, dd, n, dv);
+    cudaError_t e = cudaMemcpyAsync(values, dv, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    free_pool(pool);
+    if (e != cudaSuccess) return fail(ctx, SPTX_ECUDA, "sptx_sampler_eval: %s", cudaGetErrorString(e));
+    return SPTX_OK;
+}
+
+extern "C" int sptx_camera_rays(sptx_ctx *ctx, const float *cs, int64_t n, float wavelength,
+                                sptx_ray *rays, float *weights) {
+    if (!ctx) return fail(nullptr, SPTX_EINVAL, "sptx_camera_rays: ctx is NULL");
+    if (!ctx->haveScene) return fail(ctx, SPTX_ESTATE, "sptx_camera_rays: no scene uploaded");
+    if (n <= 0) return SPTX_OK;
+    CK(cudaSetDevice(ctx->device));
+    std::vector<void *> pool;
+    const float *dcs;
+    sptx_ray *dr;
+    float *dw;
+    int rc;
+    if ((rc = upload(ctx, pool, cs, 5 * n, &dcs)) || (rc = dalloc(ctx, pool, n, &dr)) ||
+        (rc = dalloc(ctx, pool, n, &dw))) {
+        free_pool(pool);
+        return rc;
+    }
+    k_camera_rays<<<grid_for(ctx, n), kBlock, 0, ctx->stream>>>(ctx->C, dcs, n, wavelength, dr, dw);
+    cudaError_t e = cudaMemcpyAsync(rays, dr, (size_t)n * sizeof(sptx_ray), cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess)
+        e = cudaMemcpyAsync(weights, dw, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    free_pool(pool);
+    if (e != cudaSuccess) return fail(ctx, SPTX_ECUDA, "sptx_camera_rays: %s", cudaGetErrorString(e));
+    return SPTX_OK;
+}
