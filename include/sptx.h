@@ -347,10 +347,18 @@ int sptx_sampler_eval(sptx_ctx *ctx, const int32_t *px, const int32_t *py,
 int sptx_camera_rays(sptx_ctx *ctx, const float *cs, int64_t n, float wavelength,
                      sptx_ray *rays, float *weights);
 
+/* L[i][31] = PathIntegrator::Li (src/integrators/path.cpp:64-188) of sample
+ * number sample[i] of pixel (px[i], py[i]), following the per-sample sequence
+ * of SamplerIntegrator::Render (src/core/integrator.cpp:264-292); nothing is
+ * added to the film.  pfilm_weight[i] = {pFilm.x, pFilm.y, rayWeight} (optional). */
+int sptx_debug_radiance(sptx_ctx *ctx, const int32_t *px, const int32_t *py,
+                        const int32_t *sample, int64_t n, float *L, float *pfilm_weight);
+
 /* Flattened-scene files (what host/flatten.cpp writes). */
 int sptx_scene_save(const char *path, const sptx_scene_desc *scene);
 int sptx_scene_load(const char *path, sptx_scene_desc **out);
 void sptx_scene_free(sptx_scene_desc *scene);
+const char *sptx_io_last_error(void);
 
 int sptx_abi_version(void);
 

@@ -1,0 +1,237 @@
+"""ctypes binding of include/sptx.h (the C ABI of libsptx.so).
+
+This is harness glue for tests and benchmarks: it loads the in-tree
+``libsptx.so`` and exposes the entry points one-to-one.  There is no Python or
+CPU implementation behind it -- if the library is missing, or no CUDA device is
+present, calls fail loudly (north star: "no CPU fallback").
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libsptx.so")
+
+NBINS = 31
+STRIDE = 32
+
+# Every symbol include/sptx.h declares (tests check the library exports them all).
+SYMBOLS = [
+    "sptx_abi_version", "sptx_create", "sptx_destroy", "sptx_last_error",
+    "sptx_upload_scene", "sptx_intersect_batch", "sptx_intersect_batch_device",
+    "sptx_render", "sptx_render_tiles", "sptx_film_clear", "sptx_film_device_ptr",
+    "sptx_film_download", "sptx_film_pack_dat", "sptx_write_dat",
+    "sptx_get_counters", "sptx_reset_counters", "sptx_set_wavefront_size",
+    "sptx_sampler_eval", "sptx_camera_rays", "sptx_debug_radiance",
+    "sptx_scene_save", "sptx_scene_load", "sptx_scene_free", "sptx_io_last_error",
+]
+
+RAY_DTYPE = np.dtype([("o", "<f4", 3), ("t_max", "<f4"), ("d", "<f4", 3), ("time", "<f4")])
+HIT_DTYPE = np.dtype([("prim", "<i4"), ("instance", "<i4"), ("t", "<f4"), ("b0", "<f4"),
+                      ("b1", "<f4"), ("b2", "<f4"), ("n_nodes", "<i4"), ("n_tests", "<i4")])
+assert RAY_DTYPE.itemsize == 32 and HIT_DTYPE.itemsize == 32
+
+
+class Counters(C.Structure):
+    _fields_ = [("camera_rays", C.c_uint64), ("closest_hit_rays", C.c_uint64),
+                ("shadow_rays", C.c_uint64), ("path_vertices", C.c_uint64),
+                ("kernel_launches", C.c_uint64), ("render_ms", C.c_double),
+                ("traverse_ms", C.c_double), ("shade_ms", C.c_double), ("film_ms", C.c_double)]
+
+
+class SptxError(RuntimeError):
+    pass
+
+
+_lib = None
+
+
+def lib():
+    """Loads libsptx.so (once).  Raises if it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise SptxError(
+            f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(there is no fallback implementation)")
+    L = C.CDLL(LIB_PATH)
+    vp, i32, i64, f32p = C.c_void_p, C.c_int, C.c_int64, C.POINTER(C.c_float)
+    i32p = C.POINTER(C.c_int32)
+    L.sptx_abi_version.restype = i32
+    L.sptx_create.argtypes = [i32, C.POINTER(vp)]
+    L.sptx_destroy.argtypes = [vp]
+    L.sptx_destroy.restype = None
+    L.sptx_last_error.argtypes = [vp]
+    L.sptx_last_error.restype = C.c_char_p
+    L.sptx_io_last_error.restype = C.c_char_p
+    L.sptx_upload_scene.argtypes = [vp, vp]
+    L.sptx_intersect_batch.argtypes = [vp, vp, i64, vp, i32, i32]
+    L.sptx_intersect_batch_device.argtypes = [vp, vp, i64, vp, i32, i32, f32p]
+    L.sptx_render.argtypes = [vp, i32p, i32, i32]
+    L.sptx_render_tiles.argtypes = [vp, i32, i32, i32, i32]
+    L.sptx_film_clear.argtypes = [vp]
+    L.sptx_film_device_ptr.argtypes = [vp, C.POINTER(vp), C.POINTER(i64)]
+    L.sptx_film_download.argtypes = [vp, vp, vp]
+    L.sptx_film_pack_dat.argtypes = [vp, vp]
+    L.sptx_write_dat.argtypes = [C.c_char_p, i32, i32, vp]
+    L.sptx_get_counters.argtypes = [vp, C.POINTER(Counters)]
+    L.sptx_reset_counters.argtypes = [vp]
+    L.sptx_set_wavefront_size.argtypes = [vp, i64]
+    L.sptx_sampler_eval.argtypes = [vp, vp, vp, vp, vp, i64, vp]
+    L.sptx_camera_rays.argtypes = [vp, vp, i64, C.c_float, vp, vp]
+    L.sptx_debug_radiance.argtypes = [vp, vp, vp, vp, i64, vp, vp]
+    L.sptx_scene_save.argtypes = [C.c_char_p, vp]
+    L.sptx_scene_load.argtypes = [C.c_char_p, C.POINTER(vp)]
+    L.sptx_scene_free.argtypes = [vp]
+    L.sptx_scene_free.restype = None
+    _lib = L
+    return L
+
+
+def _ptr(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+class SceneFile:
+    """A flattened scene (host arrays) loaded from a file host/flatten.cpp wrote."""
+
+    def __init__(self, path):
+        self.path = path
+        self.handle = C.c_void_p()
+        rc = lib().sptx_scene_load(path.encode(), C.byref(self.handle))
+        if rc != 0:
+            raise SptxError(f"sptx_scene_load({path}) -> {rc}: {lib().sptx_io_last_error().decode()}")
+
+    def close(self):
+        if self.handle:
+            lib().sptx_scene_free(self.handle)
+            self.handle = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class Context:
+    """One GPU context (sptx_ctx).  Mirrors the call sequence of GpuPathIntegrator::Render."""
+
+    def __init__(self, device=0):
+        self.h = C.c_void_p()
+        rc = lib().sptx_create(int(device), C.byref(self.h))
+        if rc != 0:
+            raise SptxError(f"sptx_create -> {rc}: {lib().sptx_last_error(None).decode()}")
+        self.film_shape = None
+
+    def _ck(self, rc, what):
+        if rc != 0:
+            raise SptxError(f"{what} -> {rc}: {lib().sptx_last_error(self.h).decode()}")
+
+    def close(self):
+        if self.h:
+            lib().sptx_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def upload(self, scene):
+        self._ck(lib().sptx_upload_scene(self.h, scene.handle), "sptx_upload_scene")
+        ptr, n = C.c_void_p(), C.c_int64()
+        self._ck(lib().sptx_film_device_ptr(self.h, C.byref(ptr), C.byref(n)), "sptx_film_device_ptr")
+        self.film_ptr, self.film_floats = ptr.value, n.value
+
+    def set_wavefront_size(self, n):
+        self._ck(lib().sptx_set_wavefront_size(self.h, int(n)), "sptx_set_wavefront_size")
+
+    def intersect(self, rays, any_hit=False, counters=False):
+        rays = np.ascontiguousarray(rays, dtype=RAY_DTYPE)
+        hits = np.zeros(rays.shape[0], dtype=HIT_DTYPE)
+        self._ck(lib().sptx_intersect_batch(self.h, _ptr(rays), rays.shape[0], _ptr(hits),
+                                            int(any_hit), int(counters)), "sptx_intersect_batch")
+        return hits
+
+    def intersect_device(self, d_rays, n, d_hits, any_hit=False, counters=False):
+        ms = C.c_float()
+        self._ck(lib().sptx_intersect_batch_device(self.h, d_rays, int(n), d_hits, int(any_hit),
+                                                   int(counters), C.byref(ms)),
+                 "sptx_intersect_batch_device")
+        return ms.value
+
+    def render(self, sample_begin, sample_end, pixel_bounds=None):
+        pb = None
+        if pixel_bounds is not None:
+            pb = (C.c_int32 * 4)(*[int(v) for v in pixel_bounds])
+        self._ck(lib().sptx_render(self.h, pb, int(sample_begin), int(sample_end)), "sptx_render")
+
+    def render_tiles(self, part, n_parts, sample_begin, sample_end):
+        self._ck(lib().sptx_render_tiles(self.h, int(part), int(n_parts), int(sample_begin),
+                                         int(sample_end)), "sptx_render_tiles")
+
+    def film_clear(self):
+        self._ck(lib().sptx_film_clear(self.h), "sptx_film_clear")
+
+    def film_download(self, width, height):
+        contrib = np.zeros((height, width, NBINS), dtype=np.float32)
+        weight = np.zeros((height, width), dtype=np.float32)
+        self._ck(lib().sptx_film_download(self.h, _ptr(contrib), _ptr(weight)), "sptx_film_download")
+        return contrib, weight
+
+    def film_pack_dat(self, width, height):
+        planes = np.zeros((NBINS, height, width), dtype=np.float64)
+        self._ck(lib().sptx_film_pack_dat(self.h, _ptr(planes)), "sptx_film_pack_dat")
+        return planes
+
+    def counters(self):
+        c = Counters()
+        self._ck(lib().sptx_get_counters(self.h, C.byref(c)), "sptx_get_counters")
+        return {k: getattr(c, k) for k, _ in Counters._fields_}
+
+    def reset_counters(self):
+        self._ck(lib().sptx_reset_counters(self.h), "sptx_reset_counters")
+
+    def sampler_eval(self, px, py, sample, dim):
+        px, py, sample, dim = [np.ascontiguousarray(a, dtype=np.int32) for a in (px, py, sample, dim)]
+        out = np.zeros(px.shape[0], dtype=np.float32)
+        self._ck(lib().sptx_sampler_eval(self.h, _ptr(px), _ptr(py), _ptr(sample), _ptr(dim),
+                                         px.shape[0], _ptr(out)), "sptx_sampler_eval")
+        return out
+
+    def camera_rays(self, cs, wavelength=550.0):
+        cs = np.ascontiguousarray(cs, dtype=np.float32).reshape(-1, 5)
+        rays = np.zeros(cs.shape[0], dtype=RAY_DTYPE)
+        w = np.zeros(cs.shape[0], dtype=np.float32)
+        self._ck(lib().sptx_camera_rays(self.h, _ptr(cs), cs.shape[0], float(wavelength), _ptr(rays),
+                                        _ptr(w)), "sptx_camera_rays")
+        return rays, w
+
+    def debug_radiance(self, px, py, sample):
+        px, py, sample = [np.ascontiguousarray(a, dtype=np.int32) for a in (px, py, sample)]
+        L = np.zeros((px.shape[0], NBINS), dtype=np.float32)
+        pw = np.zeros((px.shape[0], 3), dtype=np.float32)
+        self._ck(lib().sptx_debug_radiance(self.h, _ptr(px), _ptr(py), _ptr(sample), px.shape[0],
+                                           _ptr(L), _ptr(pw)), "sptx_debug_radiance")
+        return L, pw
+
+
+def write_dat(path, planes):
+    planes = np.ascontiguousarray(planes, dtype=np.float64)
+    rc = lib().sptx_write_dat(path.encode(), planes.shape[2], planes.shape[1], _ptr(planes))
+    if rc != 0:
+        raise SptxError(f"sptx_write_dat -> {rc}")
+
+
+def read_dat(path):
+    """Reads a spectral .dat as Film::WriteImage writes it (reference src/core/film.cpp:267-306)."""
+    with open(path, "rb") as f:
+        header = f.readline().split()
+        w, h, nb = int(header[0]), int(header[1]), int(header[2])
+        f.readline()  # "v3 \n"
+        data = np.frombuffer(f.read(), dtype="<f8")
+    return data.reshape(nb, h, w)

@@ -17,7 +17,7 @@ __global__ void k_generate(DScene S, DCamera C, DSampler H, PathArrays A, Render
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nPaths;
          i += (int64_t)gridDim.x * blockDim.x) {
         const int pix = (int)(i % R.nPix);
-        const int sampleNum = R.sampleBegin + (int)(i / R.nPix);
+        const int sampleNum = R.sampleList ? R.sampleList[i] : R.sampleBegin + (int)(i / R.nPix);
         const int2 pxy = R.pixels[pix];
         const int ox = pxy.x - H.sb[0], oy = pxy.y - H.sb[1];
         const uint64_t off = H.pixel_offset[(size_t)oy * (H.sb[2] - H.sb[0]) + ox];

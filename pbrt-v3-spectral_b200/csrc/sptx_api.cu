@@ -518,12 +518,13 @@ static int ensure_paths(sptx_ctx *ctx, int64_t P) {
 }
 
 // Renders `pixels` (host list) for sample numbers [s0, s1).
-static int render_pixels(sptx_ctx *ctx, const std::vector<int2> &pixels, int s0, int s1) {
+static int render_pixels(sptx_ctx *ctx, const std::vector<int2> &pixels, int s0, int s1,
+                         const int *dSampleList = nullptr) {
     if (pixels.empty() || s1 <= s0) return SPTX_OK;
     int rc;
     const int64_t want = ctx->maxPaths > 0 ? ctx->maxPaths : ((int64_t)1 << 22);
     const int64_t nPixAll = (int64_t)pixels.size();
-    const int64_t chunkPix = std::min<int64_t>(nPixAll, want);
+    const int64_t chunkPix = dSampleList ? nPixAll : std::min<int64_t>(nPixAll, want);
     int S_pass = (int)std::max<int64_t>(1, std::min<int64_t>(s1 - s0, want / chunkPix));
     if ((rc = ensure_paths(ctx, chunkPix * S_pass))) return rc;
     int2 *dPixels = nullptr;
@@ -561,6 +562,7 @@ static int render_pixels(sptx_ctx *ctx, const std::vector<int2> &pixels, int s0,
             R.rrThreshold = ctx->integ.rr_threshold;
             R.pixels = dPixels + p0;
             R.wavelength = 550.f;
+            R.sampleList = dSampleList;
             const int64_t nPaths = (int64_t)nPix * R.samplesInPass;
             const int g = grid_for(ctx, nPaths);
             k_set_counters<<<1, 1, 0, ctx->stream>>>(A.counters, 0, 0, 1, 0);
@@ -587,11 +589,13 @@ static int render_pixels(sptx_ctx *ctx, const std::vector<int2> &pixels, int s0,
                 qi ^= 1;
                 betaIn ^= 1;
             }
-            tic();
-            k_film<<<grid_for(ctx, nPix), kBlock, 0, ctx->stream>>>(ctx->S, ctx->F, A, R);
-            k_film_spill<<<g, kBlock, 0, ctx->stream>>>(ctx->S, ctx->F, A, R);
-            toc(msFilm);
-            launches += 2;
+            if (!dSampleList) {
+                tic();
+                k_film<<<grid_for(ctx, nPix), kBlock, 0, ctx->stream>>>(ctx->S, ctx->F, A, R);
+                k_film_spill<<<g, kBlock, 0, ctx->stream>>>(ctx->S, ctx->F, A, R);
+                toc(msFilm);
+                launches += 2;
+            }
         }
     }
     cudaEventRecord(ctx->ev1, ctx->stream);
@@ -877,5 +881,41 @@ extern "C" int sptx_camera_rays(sptx_ctx *ctx, const float *cs, int64_t n, float
     if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
     free_pool(pool);
     if (e != cudaSuccess) return fail(ctx, SPTX_ECUDA, "sptx_camera_rays: %s", cudaGetErrorString(e));
+    return SPTX_OK;
+}
+
+// Debug / parity hook: PathIntegrator::Li for explicit (pixel, sample) pairs,
+// returned per sample instead of being added to the film.
+extern "C" int sptx_debug_radiance(sptx_ctx *ctx, const int32_t *px, const int32_t *py,
+                                   const int32_t *sample, int64_t n, float *L, float *pfilm_weight) {
+    if (!ctx) return fail(nullptr, SPTX_EINVAL, "sptx_debug_radiance: ctx is NULL");
+    if (!ctx->haveScene) return fail(ctx, SPTX_ESTATE, "sptx_debug_radiance: no scene uploaded");
+    if (n <= 0) return SPTX_OK;
+    CK(cudaSetDevice(ctx->device));
+    std::vector<int2> pixels((size_t)n);
+    for (int64_t i = 0; i < n; ++i) pixels[i] = make_int2(px[i], py[i]);
+    std::vector<void *> pool;
+    const int32_t *dS;
+    int rc = upload(ctx, pool, sample, n, &dS);
+    if (rc == SPTX_OK) rc = render_pixels(ctx, pixels, 0, 1, dS);
+    free_pool(pool);
+    if (rc) return rc;
+    const PathArrays &A = ctx->A;
+    std::vector<float> tmp((size_t)n);
+    for (int b = 0; b < SPTX_NBINS; ++b) {
+        CK(cudaMemcpy(tmp.data(), A.L + (size_t)b * A.capacity, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost));
+        for (int64_t i = 0; i < n; ++i) L[i * SPTX_NBINS + b] = tmp[i];
+    }
+    if (pfilm_weight) {
+        std::vector<float2> pf((size_t)n);
+        std::vector<float4> rb((size_t)n);
+        CK(cudaMemcpy(pf.data(), A.pfilm, (size_t)n * sizeof(float2), cudaMemcpyDeviceToHost));
+        CK(cudaMemcpy(rb.data(), A.rayB, (size_t)n * sizeof(float4), cudaMemcpyDeviceToHost));
+        for (int64_t i = 0; i < n; ++i) {
+            pfilm_weight[3 * i] = pf[i].x;
+            pfilm_weight[3 * i + 1] = pf[i].y;
+            pfilm_weight[3 * i + 2] = rb[i].w;
+        }
+    }
     return SPTX_OK;
 }

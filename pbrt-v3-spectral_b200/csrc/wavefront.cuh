@@ -46,6 +46,7 @@ struct RenderParams {
     float rrThreshold;
     const int2 *pixels;  // [nPix] pixel coordinates
     float wavelength;    // ray.wavelength (550 for PathIntegrator)
+    const int *sampleList;  // debug: explicit sample number per path (or NULL)
 };
 
 struct DeviceCounters {

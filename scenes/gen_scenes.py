@@ -1,0 +1,183 @@
+#!/usr/bin/env python3
+"""Procedural .pbrt scenes for the configs of BASELINE.json.
+
+    python scenes/gen_scenes.py <name> <out.pbrt> [key=value ...]
+
+names:  cornell       C2: spectral Cornell box (diffuse + glass + metal), perspective camera
+        cornell_lens  C3: the same scene through Camera "realistic" (double-Gauss lens)
+        instanced     C4: N x N displaced grid mesh, instanced on a lattice
+        furnace_point / furnace_area   the known-answer scenes of the reference's
+                      src/tests/analytic_scenes.cpp:68-165 written as scene files
+keys:   res=<w>[x<h>] spp=<n> maxdepth=<n> strategy=<uniform|power|spatial>
+        grid=<N> inst=<k> (instanced: k x k instances)
+The files only use directives the reference's parser accepts, so the same file
+feeds the reference CLI (oracle/_ref/pbrt) and the GPU host binary
+(host/_build/pbrt_b200).
+"""
+import math
+import os
+import sys
+
+import numpy as np
+
+# 11-interface double-Gauss, 50 mm (curvature radius, thickness, eta, aperture
+# diameter; mm).  The table of pbrt-v3-scenes' dgauss.50mm.dat as recalled in
+# SURVEY.md 8d; oracle and GPU read the same file, so any consistent table works.
+DGAUSS_50MM = """# D-GAUSS F/2 22deg HFOV (50 mm)
+29.475 3.76 1.67 25.2
+84.83 0.12 1 25.2
+19.275 4.025 1.67 23
+40.77 3.275 1.699 23
+12.75 5.705 1 18
+0 4.5 0 17.1
+-14.495 1.18 1.603 17
+40.77 6.065 1.658 20
+-20.385 0.19 1 20
+437.065 3.22 1.717 20
+-39.73 5.0 1 20
+"""
+
+WHITE = "[400 .73 700 .73]"
+RED = "[400 .05 580 .05 600 .65 700 .65]"
+GREEN = "[400 .1 500 .1 520 .45 560 .45 580 .1 700 .1]"
+
+
+def parse_res(v):
+    if "x" in v:
+        a, b = v.split("x")
+        return int(a), int(b)
+    return int(v), int(v)
+
+
+def header(opts, camera, name):
+    w, h = opts["res"]
+    s = []
+    s.append(camera)
+    s.append(f'Film "image" "integer xresolution" [{w}] "integer yresolution" [{h}] '
+             f'"string filename" "{name}.exr"')
+    s.append(f'Sampler "halton" "integer pixelsamples" [{opts["spp"]}]')
+    s.append(f'Integrator "path" "integer maxdepth" [{opts["maxdepth"]}] '
+             f'"string lightsamplestrategy" "{opts["strategy"]}"')
+    return "\n".join(s) + "\n"
+
+
+def quad(p0, p1, p2, p3):
+    pts = " ".join(f"{c:g}" for p in (p0, p1, p2, p3) for c in p)
+    return f'Shape "trianglemesh" "integer indices" [0 1 2 0 2 3] "point P" [{pts}]\n'
+
+
+def cornell_world():
+    s = "WorldBegin\n"
+    # emitter: two triangles facing -y, just below the ceiling -> 2 area lights
+    s += 'AttributeBegin\n  Material "matte" "spectrum Kd" [400 0 700 0]\n'
+    s += '  AreaLightSource "diffuse" "blackbody L" [6500 15]\n'
+    s += "  " + quad((-.25, .99, -.25), (.25, .99, -.25), (.25, .99, .25), (-.25, .99, .25))
+    s += "AttributeEnd\n"
+    s += f'AttributeBegin\n  Material "matte" "spectrum Kd" {WHITE}\n'
+    s += "  " + quad((-1, -1, -1), (1, -1, -1), (1, 1, -1), (-1, 1, -1))      # back
+    s += "  " + quad((-1, -1, 1), (1, -1, 1), (1, -1, -1), (-1, -1, -1))      # floor
+    s += "  " + quad((-1, 1, -1), (1, 1, -1), (1, 1, 1), (-1, 1, 1))          # ceiling
+    s += "AttributeEnd\n"
+    s += f'AttributeBegin\n  Material "matte" "spectrum Kd" {RED}\n'
+    s += "  " + quad((-1, -1, 1), (-1, -1, -1), (-1, 1, -1), (-1, 1, 1)) + "AttributeEnd\n"
+    s += f'AttributeBegin\n  Material "matte" "spectrum Kd" {GREEN}\n'
+    s += "  " + quad((1, -1, -1), (1, -1, 1), (1, 1, 1), (1, 1, -1)) + "AttributeEnd\n"
+    s += ('AttributeBegin\n  Material "glass" "float index" [1.5]\n  Translate .45 -.65 .3\n'
+          '  Shape "sphere" "float radius" [.35]\nAttributeEnd\n')
+    s += ('AttributeBegin\n  Material "metal" "float roughness" [.01]\n  Translate -.45 -.6 -.3\n'
+          '  Shape "sphere" "float radius" [.4]\nAttributeEnd\n')
+    s += "WorldEnd\n"
+    return s
+
+
+def cornell(opts, out):
+    cam = 'LookAt 0 0 3.8  0 0 0  0 1 0\nCamera "perspective" "float fov" [39]'
+    return header(opts, cam, os.path.splitext(os.path.basename(out))[0]) + cornell_world()
+
+
+def cornell_lens(opts, out):
+    lens = os.path.join(os.path.dirname(os.path.abspath(out)), "dgauss.50mm.dat")
+    with open(lens, "w") as f:
+        f.write(DGAUSS_50MM)
+    cam = ('LookAt 0 0 3.8  0 0 0  0 1 0\nCamera "realistic" "string lensfile" "dgauss.50mm.dat" '
+           '"float aperturediameter" [8] "float focusdistance" [3.8] "bool simpleweighting" "true"')
+    return header(opts, cam, os.path.splitext(os.path.basename(out))[0]) + cornell_world()
+
+
+def instanced(opts, out):
+    n, k = opts["grid"], opts["inst"]
+    xs = np.linspace(-0.5, 0.5, n)
+    X, Y = np.meshgrid(xs, xs, indexing="xy")
+    Z = 0.08 * np.sin(9 * X) * np.cos(7 * Y) + 0.03 * np.sin(31 * X * Y)
+    P = np.stack([X, Y, Z], -1).reshape(-1, 3).astype(np.float32)
+    idx = []
+    ii = np.arange(n - 1)
+    a = (ii[None, :] + n * ii[:, None]).reshape(-1)
+    tri = np.stack([a, a + 1, a + n + 1, a, a + n + 1, a + n], -1).reshape(-1)
+    cam = f'LookAt 0 {-0.9 * k} {0.55 * k}  0 0 0  0 0 1\nCamera "perspective" "float fov" [45]'
+    s = header(opts, cam, os.path.splitext(os.path.basename(out))[0]) + "WorldBegin\n"
+    s += 'LightSource "point" "point from" [0 0 %g] "blackbody I" [6500 %g]\n' % (1.5 * k, 40.0 * k * k)
+    s += 'Material "matte" "spectrum Kd" [400 .6 700 .5]\n'
+    s += 'ObjectBegin "tile"\n  Shape "trianglemesh" "integer indices" [\n'
+    s += " ".join(str(int(v)) for v in tri) + ' ]\n  "point P" [\n'
+    s += " ".join(f"{v:.6g}" for v in P.reshape(-1)) + " ]\nObjectEnd\n"
+    rng = np.random.RandomState(7)
+    for j in range(k):
+        for i in range(k):
+            ang = rng.uniform(-8, 8)
+            s += (f"AttributeBegin\n  Translate {i - (k - 1) / 2:g} {j - (k - 1) / 2:g} "
+                  f"{rng.uniform(-.05, .05):.4f}\n  Rotate {ang:.3f} 0 0 1\n"
+                  f'  ObjectInstance "tile"\nAttributeEnd\n')
+    s += "WorldEnd\n"
+    return s
+
+
+def furnace(opts, out, area):
+    # src/tests/analytic_scenes.cpp:71-98 (point light, Kd = 0.5) and :135-165
+    # (Kd = 0.5 sphere that also emits Le = 0.5): a camera inside a unit
+    # sphere; every pixel's converged radiance is 1.
+    cam = 'LookAt 0 0 0  0 0 1  0 1 0\nCamera "perspective" "float fov" [45]'
+    s = header(opts, cam, os.path.splitext(os.path.basename(out))[0]) + "WorldBegin\n"
+    if area:
+        s += 'AreaLightSource "diffuse" "spectrum L" [400 .5 700 .5]\n'
+    else:
+        s += f'LightSource "point" "point from" [0 0 0] "spectrum I" [400 {math.pi:.9g} 700 {math.pi:.9g}]\n'
+    s += 'Material "matte" "spectrum Kd" [400 .5 700 .5]\n'
+    s += 'ReverseOrientation\nShape "sphere" "float radius" [1]\nWorldEnd\n'
+    return s
+
+
+def main(argv):
+    if len(argv) < 3:
+        print(__doc__)
+        return 2
+    name, out = argv[1], argv[2]
+    opts = {"res": (64, 64), "spp": 16, "maxdepth": 5, "strategy": "spatial", "grid": 64, "inst": 4}
+    for kv in argv[3:]:
+        k, v = kv.split("=", 1)
+        if k == "res":
+            opts[k] = parse_res(v)
+        elif k in ("spp", "maxdepth", "grid", "inst"):
+            opts[k] = int(v)
+        else:
+            opts[k] = v
+    if name == "cornell":
+        text = cornell(opts, out)
+    elif name == "cornell_lens":
+        text = cornell_lens(opts, out)
+    elif name == "instanced":
+        text = instanced(opts, out)
+    elif name == "furnace_point":
+        text = furnace(opts, out, False)
+    elif name == "furnace_area":
+        text = furnace(opts, out, True)
+    else:
+        print("unknown scene", name)
+        return 2
+    with open(out, "w") as f:
+        f.write(text)
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main(sys.argv))
