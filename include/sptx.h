@@ -276,6 +276,14 @@ typedef struct sptx_counters {
     double traverse_ms;        /* of which traversal kernels                  */
     double shade_ms;
     double film_ms;
+    /* per kernel type, CUDA-event time and launches since the last reset:
+     * 0 generate, 1 intersect, 2 shade, 3 resolve, 4 film, 5 film spill, 6 ray batch */
+    double kernel_ms[8];
+    uint64_t kernel_count[8];
+    /* visit counts of the wavefront traversal kernels (only when enabled with
+     * sptx_set_option("count_visits", 1)): BVH nodes fetched / primitive tests */
+    uint64_t nodes_visited[2]; /* [0] intersect kernel, [1] resolve kernel    */
+    uint64_t prims_tested[2];
 } sptx_counters;
 
 typedef struct sptx_ctx sptx_ctx;
@@ -333,6 +341,8 @@ int sptx_write_dat(const char *path, int width, int height, const double *planes
 
 int sptx_get_counters(sptx_ctx *ctx, sptx_counters *out);
 int sptx_reset_counters(sptx_ctx *ctx);
+/* Named integer options: "count_visits" (0/1). */
+int sptx_set_option(sptx_ctx *ctx, const char *name, int64_t value);
 /* Max paths in flight per wavefront pass (0 = default). */
 int sptx_set_wavefront_size(sptx_ctx *ctx, int64_t max_paths);
 

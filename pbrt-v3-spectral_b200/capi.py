@@ -22,7 +22,7 @@ SYMBOLS = [
     "sptx_upload_scene", "sptx_intersect_batch", "sptx_intersect_batch_device",
     "sptx_render", "sptx_render_tiles", "sptx_film_clear", "sptx_film_device_ptr",
     "sptx_film_download", "sptx_film_pack_dat", "sptx_write_dat",
-    "sptx_get_counters", "sptx_reset_counters", "sptx_set_wavefront_size",
+    "sptx_get_counters", "sptx_reset_counters", "sptx_set_wavefront_size", "sptx_set_option",
     "sptx_sampler_eval", "sptx_camera_rays", "sptx_debug_radiance",
     "sptx_scene_save", "sptx_scene_load", "sptx_scene_free", "sptx_io_last_error",
 ]
@@ -37,7 +37,11 @@ class Counters(C.Structure):
     _fields_ = [("camera_rays", C.c_uint64), ("closest_hit_rays", C.c_uint64),
                 ("shadow_rays", C.c_uint64), ("path_vertices", C.c_uint64),
                 ("kernel_launches", C.c_uint64), ("render_ms", C.c_double),
-                ("traverse_ms", C.c_double), ("shade_ms", C.c_double), ("film_ms", C.c_double)]
+                ("traverse_ms", C.c_double), ("shade_ms", C.c_double), ("film_ms", C.c_double),
+                ("kernel_ms", C.c_double * 8), ("kernel_count", C.c_uint64 * 8),
+                ("nodes_visited", C.c_uint64 * 2), ("prims_tested", C.c_uint64 * 2)]
+
+KERNEL_NAMES = ["generate", "intersect", "shade", "resolve", "film", "film_spill", "ray_batch"]
 
 
 class SptxError(RuntimeError):
@@ -79,6 +83,7 @@ def lib():
     L.sptx_get_counters.argtypes = [vp, C.POINTER(Counters)]
     L.sptx_reset_counters.argtypes = [vp]
     L.sptx_set_wavefront_size.argtypes = [vp, i64]
+    L.sptx_set_option.argtypes = [vp, C.c_char_p, i64]
     L.sptx_sampler_eval.argtypes = [vp, vp, vp, vp, vp, i64, vp]
     L.sptx_camera_rays.argtypes = [vp, vp, i64, C.c_float, vp, vp]
     L.sptx_debug_radiance.argtypes = [vp, vp, vp, vp, i64, vp, vp]
@@ -150,6 +155,9 @@ class Context:
     def set_wavefront_size(self, n):
         self._ck(lib().sptx_set_wavefront_size(self.h, int(n)), "sptx_set_wavefront_size")
 
+    def set_option(self, name, value):
+        self._ck(lib().sptx_set_option(self.h, name.encode(), int(value)), "sptx_set_option")
+
     def intersect(self, rays, any_hit=False, counters=False):
         rays = np.ascontiguousarray(rays, dtype=RAY_DTYPE)
         hits = np.zeros(rays.shape[0], dtype=HIT_DTYPE)
@@ -191,7 +199,11 @@ class Context:
     def counters(self):
         c = Counters()
         self._ck(lib().sptx_get_counters(self.h, C.byref(c)), "sptx_get_counters")
-        return {k: getattr(c, k) for k, _ in Counters._fields_}
+        out = {}
+        for k, _ in Counters._fields_:
+            v = getattr(c, k)
+            out[k] = list(v) if hasattr(v, "__len__") else v
+        return out
 
     def reset_counters(self):
         self._ck(lib().sptx_reset_counters(self.h), "sptx_reset_counters")

@@ -49,17 +49,23 @@ __global__ void k_generate(DScene S, DCamera C, DSampler H, PathArrays A, Render
 }
 
 // ---- K2: closest hit for the active queue ------------------------------------
+template <bool COUNT>
 __global__ void k_intersect(DScene S, PathArrays A, int qi, DeviceCounters *cnt) {
     const int n = A.counters[qi];
     const int *queue = A.q[qi];
+    TravCounters tc{0, 0};
     for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
         const int i = queue[k];
         float4 ra = A.rayA[i], rb = A.rayB[i];
         Ray ray{mk(ra.x, ra.y, ra.z), mk(ra.w, rb.x, rb.y), kInf};
         HitRec h;
-        scene_intersect<false>(S, ray, &h, nullptr);
+        scene_intersect<COUNT>(S, ray, &h, &tc);
         A.hitA[i] = make_float4(__int_as_float(h.prim), __int_as_float(h.inst), h.b0, h.b1);
         A.hitB[i] = make_float4(h.b2, ray.tMax, 0.f, 0.f);
+    }
+    if (COUNT) {
+        atomicAdd(&cnt->nodes[0], (unsigned long long)tc.nodes);
+        atomicAdd(&cnt->tests[0], (unsigned long long)tc.tests);
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&cnt->closestRays, (unsigned long long)n);
 }

@@ -9,8 +9,10 @@ namespace sptx {
 // the closest-hit test of the BSDF-sampled direction (core/integrator.cpp:
 // 190-212), then L += beta * (Ld / lightPdf) (integrator.cpp:104-105,
 // path.cpp:122-128).
+template <bool COUNT>
 __global__ void __launch_bounds__(kBlock)
 k_resolve(DScene S, PathArrays A, int betaIn, DeviceCounters *cnt) {
+    TravCounters tc{0, 0};
     const int n = A.counters[2];
     const size_t P = (size_t)A.capacity;
     const float *beta = A.beta[betaIn];
@@ -25,14 +27,14 @@ k_resolve(DScene S, PathArrays A, int betaIn, DeviceCounters *cnt) {
         bool useA = false, useB = false;
         if (flags & NEE_HAS_SHADOW) {
             Ray r{mk(sa.x, sa.y, sa.z), mk(sa.w, sb.x, sb.y), sb.z};
-            useA = !scene_intersect_p<false>(S, r, nullptr);
+            useA = !scene_intersect_p<COUNT>(S, r, &tc);
             ++nShadow;
         }
         if (flags & NEE_HAS_MIS) {
             Ray r{mk(ma.x, ma.y, ma.z), mk(ma.w, mb.x, mb.y), kInf};
             HitRec h;
             ++nClosest;
-            if (scene_intersect<false>(S, r, &h, nullptr)) {
+            if (scene_intersect<COUNT>(S, r, &h, &tc)) {
                 if (S.prims[h.prim].light == lightNum) {
                     const sptx_light &Lt = S.lights[lightNum];
                     if (Lt.two_sided)
@@ -53,6 +55,10 @@ k_resolve(DScene S, PathArrays A, int betaIn, DeviceCounters *cnt) {
                 A.L[b * P + i] += beta[b * P + i] * (Ld / lightPdfSel);
             }
         }
+    }
+    if (COUNT) {
+        atomicAdd(&cnt->nodes[1], (unsigned long long)tc.nodes);
+        atomicAdd(&cnt->tests[1], (unsigned long long)tc.tests);
     }
     // one atomic per warp for the ray counters
     for (int o = 16; o > 0; o >>= 1) {

@@ -35,6 +35,8 @@ struct sptx_ctx {
     DeviceCounters *dCnt = nullptr;
     sptx_counters counters;
     bool profileKernels = false;
+    bool countVisits = false;
+    std::vector<cudaEvent_t> evPool;
     int smCount = 148;
 };
 
@@ -164,8 +166,18 @@ extern "C" void sptx_destroy(sptx_ctx *ctx) {
     cudaEventDestroy(ctx->ev1);
     cudaEventDestroy(ctx->ev2);
     cudaEventDestroy(ctx->ev3);
+    for (cudaEvent_t e : ctx->evPool) cudaEventDestroy(e);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
+}
+
+extern "C" int sptx_set_option(sptx_ctx *ctx, const char *name, int64_t value) {
+    if (!ctx || !name) return fail(ctx, SPTX_EINVAL, "sptx_set_option: NULL argument");
+    if (!strcmp(name, "count_visits")) {
+        ctx->countVisits = value != 0;
+        return SPTX_OK;
+    }
+    return fail(ctx, SPTX_EINVAL, "sptx_set_option: unknown option %s", name);
 }
 
 extern "C" int sptx_set_wavefront_size(sptx_ctx *ctx, int64_t max_paths) {
@@ -538,18 +550,26 @@ static int render_pixels(sptx_ctx *ctx, const std::vector<int2> &pixels, int s0,
     PathArrays &A = ctx->A;
     const int maxDepth = ctx->integ.max_depth;
     uint64_t launches = 0;
-    const bool prof = ctx->profileKernels;
-    float msTrav = 0.f, msShade = 0.f, msFilm = 0.f;
-    auto tic = [&]() { if (prof) cudaEventRecord(ctx->ev2, ctx->stream); };
-    auto toc = [&](float &acc) {
-        if (prof) {
-            cudaEventRecord(ctx->ev3, ctx->stream);
-            cudaEventSynchronize(ctx->ev3);
-            float ms = 0.f;
-            cudaEventElapsedTime(&ms, ctx->ev2, ctx->ev3);
-            acc += ms;
+    // Per-launch CUDA events on the launching stream, read back after the sync.
+    size_t evUsed = 0;
+    std::vector<int> evKind;
+    auto tic = [&](int kind) {
+        if (evUsed + 2 > ctx->evPool.size()) {
+            cudaEvent_t a, b;
+            cudaEventCreate(&a);
+            cudaEventCreate(&b);
+            ctx->evPool.push_back(a);
+            ctx->evPool.push_back(b);
         }
+        evKind.push_back(kind);
+        cudaEventRecord(ctx->evPool[evUsed], ctx->stream);
     };
+    auto toc = [&]() {
+        cudaEventRecord(ctx->evPool[evUsed + 1], ctx->stream);
+        evUsed += 2;
+        ++launches;
+    };
+    const bool cv = ctx->countVisits;
     cudaEventRecord(ctx->ev0, ctx->stream);
     for (int64_t p0 = 0; p0 < nPixAll; p0 += chunkPix) {
         const int nPix = (int)std::min<int64_t>(chunkPix, nPixAll - p0);
@@ -566,35 +586,41 @@ static int render_pixels(sptx_ctx *ctx, const std::vector<int2> &pixels, int s0,
             const int64_t nPaths = (int64_t)nPix * R.samplesInPass;
             const int g = grid_for(ctx, nPaths);
             k_set_counters<<<1, 1, 0, ctx->stream>>>(A.counters, 0, 0, 1, 0);
-            tic();
+            ++launches;
+            tic(0);
             k_generate<<<g, kBlock, 0, ctx->stream>>>(ctx->S, ctx->C, ctx->H, A, R, ctx->dCnt);
-            toc(msShade);
-            launches += 2;
+            toc();
             int qi = 0, betaIn = 0;
             for (int bounce = 0; bounce <= maxDepth; ++bounce) {
-                tic();
-                k_intersect<<<g, kBlock, 0, ctx->stream>>>(ctx->S, A, qi, ctx->dCnt);
-                toc(msTrav);
+                tic(1);
+                if (cv)
+                    k_intersect<true><<<g, kBlock, 0, ctx->stream>>>(ctx->S, A, qi, ctx->dCnt);
+                else
+                    k_intersect<false><<<g, kBlock, 0, ctx->stream>>>(ctx->S, A, qi, ctx->dCnt);
+                toc();
                 k_set_counters<<<1, 1, 0, ctx->stream>>>(A.counters, qi ^ 1, 0, 2, 0);
-                tic();
+                ++launches;
+                tic(2);
                 k_shade<<<g, kBlock, 0, ctx->stream>>>(ctx->S, ctx->H, A, R, qi, betaIn, ctx->dCnt);
-                toc(msShade);
-                launches += 3;
+                toc();
                 if (bounce < maxDepth) {
-                    tic();
-                    k_resolve<<<g, kBlock, 0, ctx->stream>>>(ctx->S, A, betaIn, ctx->dCnt);
-                    toc(msTrav);
-                    ++launches;
+                    tic(3);
+                    if (cv)
+                        k_resolve<true><<<g, kBlock, 0, ctx->stream>>>(ctx->S, A, betaIn, ctx->dCnt);
+                    else
+                        k_resolve<false><<<g, kBlock, 0, ctx->stream>>>(ctx->S, A, betaIn, ctx->dCnt);
+                    toc();
                 }
                 qi ^= 1;
                 betaIn ^= 1;
             }
             if (!dSampleList) {
-                tic();
+                tic(4);
                 k_film<<<grid_for(ctx, nPix), kBlock, 0, ctx->stream>>>(ctx->S, ctx->F, A, R);
+                toc();
+                tic(5);
                 k_film_spill<<<g, kBlock, 0, ctx->stream>>>(ctx->S, ctx->F, A, R);
-                toc(msFilm);
-                launches += 2;
+                toc();
             }
         }
     }
@@ -606,9 +632,16 @@ static int render_pixels(sptx_ctx *ctx, const std::vector<int2> &pixels, int s0,
     float ms = 0.f;
     cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
     ctx->counters.render_ms += ms;
-    ctx->counters.traverse_ms += msTrav;
-    ctx->counters.shade_ms += msShade;
-    ctx->counters.film_ms += msFilm;
+    for (size_t e = 0; e < evKind.size(); ++e) {
+        float t = 0.f;
+        cudaEventElapsedTime(&t, ctx->evPool[2 * e], ctx->evPool[2 * e + 1]);
+        const int k = evKind[e];
+        ctx->counters.kernel_ms[k] += t;
+        ctx->counters.kernel_count[k] += 1;
+        if (k == 1 || k == 3) ctx->counters.traverse_ms += t;
+        else if (k == 0 || k == 2) ctx->counters.shade_ms += t;
+        else ctx->counters.film_ms += t;
+    }
     ctx->counters.kernel_launches += launches;
     int flags[8];
     CK(cudaMemcpy(flags, A.counters, sizeof(flags), cudaMemcpyDeviceToHost));
@@ -756,6 +789,10 @@ extern "C" int sptx_get_counters(sptx_ctx *ctx, sptx_counters *out) {
     ctx->counters.closest_hit_rays = dc.closestRays;
     ctx->counters.shadow_rays = dc.shadowRays;
     ctx->counters.path_vertices = dc.vertices;
+    for (int k = 0; k < 2; ++k) {
+        ctx->counters.nodes_visited[k] = dc.nodes[k];
+        ctx->counters.prims_tested[k] = dc.tests[k];
+    }
     *out = ctx->counters;
     return SPTX_OK;
 }
@@ -804,6 +841,8 @@ extern "C" int sptx_intersect_batch_device(sptx_ctx *ctx, const void *d_rays, in
     if (ms) *ms = t;
     ctx->counters.kernel_launches += 1;
     ctx->counters.traverse_ms += t;
+    ctx->counters.kernel_ms[6] += t;
+    ctx->counters.kernel_count[6] += 1;
     return SPTX_OK;
 }
 

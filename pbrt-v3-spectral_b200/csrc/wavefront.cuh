@@ -50,7 +50,7 @@ struct RenderParams {
 };
 
 struct DeviceCounters {
-    unsigned long long cameraRays, closestRays, shadowRays, vertices;
+    unsigned long long cameraRays, closestRays, shadowRays, vertices, nodes[2], tests[2];
 };
 
 SPTX_DEV uint32_t pack_info(int bounces, int specular, int dim) {
