@@ -53,7 +53,7 @@ SPTX_DEV int bsdf_num_components(const DScene &S, const Bsdf &b, int flags) {
 
 // BxDF::f for the non-specular lobes; appends one term (or nothing when the
 // lobe evaluates to zero).
-SPTX_DEV void lobe_f(const sptx_lobe &L, V3 wo, V3 wi, FSum *out) {
+SPTX_NOINL void lobe_f(const sptx_lobe &L, V3 wo, V3 wi, FSum *out) {
     FTerm t;
     t.R = L.R;
     t.e0 = L.fr_eta_i;
@@ -108,7 +108,7 @@ SPTX_DEV void lobe_f(const sptx_lobe &L, V3 wo, V3 wi, FSum *out) {
 }
 
 // BxDF::Pdf, core/reflection.cpp:386-388 and MicrofacetReflection::Pdf :418-422.
-SPTX_DEV float lobe_pdf(const sptx_lobe &L, V3 wo, V3 wi) {
+SPTX_NOINL float lobe_pdf(const sptx_lobe &L, V3 wo, V3 wi) {
     if (L.type == SPTX_LOBE_LAMBERT || L.type == SPTX_LOBE_OREN_NAYAR)
         return same_hemisphere(wo, wi) ? abs_cos_theta(wi) * kInvPi : 0.f;
     if (L.type == SPTX_LOBE_MICROFACET_REFL) {
@@ -120,7 +120,7 @@ SPTX_DEV float lobe_pdf(const sptx_lobe &L, V3 wo, V3 wi) {
 }
 
 // BSDF::f, core/reflection.cpp:670-683.
-SPTX_DEV void bsdf_f(const DScene &S, const Bsdf &b, V3 woW, V3 wiW, int flags, FSum *f) {
+SPTX_NOINL void bsdf_f(const DScene &S, const Bsdf &b, V3 woW, V3 wiW, int flags, FSum *f) {
     f->n = 0;
     V3 wi = to_local(b, wiW), wo = to_local(b, woW);
     if (wo.z == 0) return;
@@ -135,7 +135,7 @@ SPTX_DEV void bsdf_f(const DScene &S, const Bsdf &b, V3 woW, V3 wiW, int flags, 
 }
 
 // BSDF::Pdf, core/reflection.cpp:770-785.
-SPTX_DEV float bsdf_pdf(const DScene &S, const Bsdf &b, V3 woW, V3 wiW, int flags) {
+SPTX_NOINL float bsdf_pdf(const DScene &S, const Bsdf &b, V3 woW, V3 wiW, int flags) {
     if (b.n == 0) return 0.f;
     V3 wo = to_local(b, woW), wi = to_local(b, wiW);
     if (wo.z == 0) return 0.f;
@@ -160,7 +160,7 @@ SPTX_DEV V3 cosine_sample_hemisphere(V2 u) {
 
 // BSDF::Sample_f, core/reflection.cpp:703-768.  Returns false when the
 // reference returns a black spectrum with pdf == 0 (f->n == 0, *pdf == 0).
-SPTX_DEV void bsdf_sample_f(const DScene &S, const Bsdf &b, V3 woW, V2 u, int type, V3 *wiW,
+SPTX_NOINL void bsdf_sample_f(const DScene &S, const Bsdf &b, V3 woW, V2 u, int type, V3 *wiW,
                             float *pdf, int *sampledType, FSum *f) {
     f->n = 0;
     *pdf = 0.f;

@@ -12,6 +12,7 @@
 
 #define SPTX_DEV __device__ __forceinline__
 #define SPTX_HD __host__ __device__ __forceinline__
+#define SPTX_NOINL __device__ __noinline__
 
 namespace sptx {
 

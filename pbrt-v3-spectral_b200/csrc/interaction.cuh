@@ -24,7 +24,7 @@ SPTX_DEV V3 ld3(const float *base, size_t i) {
 }
 
 // Interaction in the space the shape lives in (world for top-level triangles).
-SPTX_DEV void triangle_interaction(const DScene &S, int shape, V3 rayD, float b0, float b1,
+SPTX_NOINL void triangle_interaction(const DScene &S, int shape, V3 rayD, float b0, float b1,
                                    float b2, Isect *it) {
     const sptx_triangle T = S.triangles[shape];
     const sptx_mesh M = S.meshes[T.mesh];
@@ -93,7 +93,7 @@ SPTX_DEV void triangle_interaction(const DScene &S, int shape, V3 rayD, float b0
 }
 
 // Object-space sphere interaction moved to the sphere's parent space.
-SPTX_DEV bool sphere_interaction(const DScene &S, int shape, const Ray &ray, Isect *it) {
+SPTX_NOINL bool sphere_interaction(const DScene &S, int shape, const Ray &ray, Isect *it) {
     const sptx_sphere &sp = S.spheres[shape];
     Ray r = ray;
     r.tMax = kInf;  // the accepted root does not depend on tMax
@@ -126,7 +126,7 @@ SPTX_DEV bool sphere_interaction(const DScene &S, int shape, const Ray &ray, Ise
 }
 
 // Scene-level interaction for a closest-hit record of world ray `ray`.
-SPTX_DEV bool build_interaction(const DScene &S, const Ray &ray, int prim, int inst, float b0,
+SPTX_NOINL bool build_interaction(const DScene &S, const Ray &ray, int prim, int inst, float b0,
                                 float b1, float b2, Isect *it) {
     const sptx_prim P = S.prims[prim];
     it->material = P.material;

@@ -192,7 +192,7 @@ struct SphereHit {
 
 // Sphere::Intersect / IntersectP up to the clipping tests,
 // shapes/sphere.cpp:49-107 (== :158-215).
-SPTX_DEV bool sphere_test(const sptx_sphere &sp, const Ray &wr, SphereHit *h) {
+SPTX_NOINL bool sphere_test(const sptx_sphere &sp, const Ray &wr, SphereHit *h) {
     V3 oErr, dErr;
     Ray ray = xf_ray_err(sp.w2o, wr, &oErr, &dErr);
     EF ox = ef(ray.o.x, oErr.x), oy = ef(ray.o.y, oErr.y), oz = ef(ray.o.z, oErr.z);

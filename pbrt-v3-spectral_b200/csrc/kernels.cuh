@@ -39,9 +39,12 @@ __global__ void k_generate(DScene S, DCamera C, DSampler H, PathArrays A, Render
         A.info[i] = pack_info(0, 0, st.dim);
         A.pfilm[i] = make_float2(pFilm.x, pFilm.y);
         A.spill[i] = 0;
-        for (int b = 0; b < SPTX_NBINS; ++b) {
-            A.beta[0][(size_t)b * A.capacity + i] = 1.f;
-            A.L[(size_t)b * A.capacity + i] = 0.f;
+        // path-major spectra: 32 floats (one 128-byte line) per path
+        float4 *b4 = reinterpret_cast<float4 *>(A.beta[0] + (size_t)i * SPTX_SPECTRUM_STRIDE);
+        float4 *l4 = reinterpret_cast<float4 *>(A.L + (size_t)i * SPTX_SPECTRUM_STRIDE);
+        for (int q = 0; q < SPTX_SPECTRUM_STRIDE / 4; ++q) {
+            b4[q] = make_float4(1.f, 1.f, 1.f, 1.f);
+            l4[q] = make_float4(0.f, 0.f, 0.f, 0.f);
         }
         queue_push(A.q[0], A.counters + 0, (int)i, w > 0);
     }

@@ -123,7 +123,7 @@ SPTX_DEV LightPoint sphere_sample(const sptx_sphere &sp, const RefPoint &ref, V2
 }
 
 // Shape::Pdf(ref, wi), core/shape.cpp:72-87, for one triangle / one sphere.
-SPTX_DEV float shape_pdf_generic(const DScene &S, int kind, int shape, const RefPoint &ref, V3 wi,
+SPTX_NOINL float shape_pdf_generic(const DScene &S, int kind, int shape, const RefPoint &ref, V3 wi,
                                  float area) {
     Ray ray{offset_ray_origin(ref.p, ref.pError, ref.n, wi), wi, kInf};
     V3 pHit, nHit;
@@ -166,7 +166,7 @@ SPTX_DEV float sphere_pdf(const DScene &S, int shape, const RefPoint &ref, V3 wi
 }
 
 // Light::Pdf_Li (DiffuseAreaLight: shape->Pdf; PointLight: 0).
-SPTX_DEV float light_pdf_li(const DScene &S, const sptx_light &L, const RefPoint &ref, V3 wi) {
+SPTX_NOINL float light_pdf_li(const DScene &S, const sptx_light &L, const RefPoint &ref, V3 wi) {
     if (L.type != SPTX_LIGHT_DIFFUSE_AREA) return 0.f;
     if (L.shape_kind == SPTX_PRIM_SPHERE) return sphere_pdf(S, L.shape, ref, wi, L.area);
     return shape_pdf_generic(S, SPTX_PRIM_TRIANGLE, L.shape, ref, wi, L.area);
@@ -188,7 +188,7 @@ SPTX_DEV float li_bin(const DScene &S, const LiSample &ls, int b) {
     return ls.divisor != 0.f ? v / ls.divisor : v;
 }
 
-SPTX_DEV LiSample light_sample_li(const DScene &S, const sptx_light &L, const RefPoint &ref, V2 u) {
+SPTX_NOINL LiSample light_sample_li(const DScene &S, const sptx_light &L, const RefPoint &ref, V2 u) {
     LiSample r;
     r.spectrum = L.spectrum;
     r.divisor = 0.f;

@@ -14,17 +14,21 @@ __global__ void __launch_bounds__(kBlock)
 k_resolve(DScene S, PathArrays A, int betaIn, DeviceCounters *cnt) {
     TravCounters tc{0, 0};
     const int n = A.counters[2];
-    const size_t P = (size_t)A.capacity;
     const float *beta = A.beta[betaIn];
+    const int lane = threadIdx.x & 31;
     unsigned long long nShadow = 0, nClosest = 0;
-    for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
-        const int i = A.qNee[k];
+    for (int k0 = blockIdx.x * blockDim.x; k0 < n; k0 += gridDim.x * blockDim.x) {
+        const int k = k0 + threadIdx.x;
+        bool useA = false, useB = false;
+        int i = 0;
+        float lightPdfSel = 1.f;
+        if (k < n) {
+        i = A.qNee[k];
         const float4 sa = A.shA[i], sb = A.shB[i];
         const float4 ma = A.misA[i], mb = A.misB[i];
         const int flags = __float_as_int(mb.w);
         const int lightNum = __float_as_int(mb.z);
-        const float lightPdfSel = sb.w;
-        bool useA = false, useB = false;
+        lightPdfSel = sb.w;
         if (flags & NEE_HAS_SHADOW) {
             Ray r{mk(sa.x, sa.y, sa.z), mk(sa.w, sb.x, sb.y), sb.z};
             useA = !scene_intersect_p<COUNT>(S, r, &tc);
@@ -47,13 +51,19 @@ k_resolve(DScene S, PathArrays A, int betaIn, DeviceCounters *cnt) {
                 }
             }
         }
-        if (useA || useB) {
-            for (int b = 0; b < SPTX_NBINS; ++b) {
-                float Ld = 0.f;
-                if (useA) Ld += A.fa[b * P + i];
-                if (useB) Ld += A.fb[b * P + i];
-                A.L[b * P + i] += beta[b * P + i] * (Ld / lightPdfSel);
-            }
+        }
+        // bin phase: the warp walks its paths, lane = bin
+        const unsigned mA = __ballot_sync(0xffffffffu, useA);
+        const unsigned mB = __ballot_sync(0xffffffffu, useB);
+        for (unsigned m = mA | mB; m; m &= m - 1) {
+            const int p = __ffs(m) - 1;
+            const int ip = __shfl_sync(0xffffffffu, i, p);
+            const float sel = __shfl_sync(0xffffffffu, lightPdfSel, p);
+            const size_t at = (size_t)ip * SPTX_SPECTRUM_STRIDE + lane;
+            float Ld = 0.f;
+            if ((mA >> p) & 1u) Ld += A.fa[at];
+            if ((mB >> p) & 1u) Ld += A.fb[at];
+            A.L[at] += beta[at] * (Ld / sel);
         }
     }
     if (COUNT) {
@@ -103,11 +113,11 @@ SPTX_DEV float filter_weight(const DFilm &F, float2 pFilm, int x, int y) {
 // Applies the radiance guard and the luminance clamp; returns the scale to
 // apply to L (0 = black it out) -- y is computed once.
 SPTX_DEV float guard_scale(const DScene &S, const DFilm &F, const PathArrays &A, size_t i) {
-    const size_t P = (size_t)A.capacity;
+    const float *Lp = A.L + i * SPTX_SPECTRUM_STRIDE;
     float yy = 0.f;
     bool nan = false;
     for (int b = 0; b < SPTX_NBINS; ++b) {
-        float v = A.L[b * P + i];
+        float v = Lp[b];
         if (isnan(v)) nan = true;
         yy += S.cie_y[b] * v;
     }
@@ -120,7 +130,6 @@ SPTX_DEV float guard_scale(const DScene &S, const DFilm &F, const PathArrays &A,
 
 __global__ void __launch_bounds__(kBlock)
 k_film(DScene S, DFilm F, PathArrays A, RenderParams R) {
-    const size_t P = (size_t)A.capacity;
     for (int pix = blockIdx.x * blockDim.x + threadIdx.x; pix < R.nPix;
          pix += gridDim.x * blockDim.x) {
         const int2 pxy = R.pixels[pix];
@@ -147,8 +156,9 @@ k_film(DScene S, DFilm F, PathArrays A, RenderParams R) {
             const float g = guard_scale(S, F, A, i);
             const float w = A.rayB[i].w;
             const float fw = filter_weight(F, pf, x0, y0);
+            const float *Lp = A.L + i * SPTX_SPECTRUM_STRIDE;
             for (int b = 0; b < SPTX_NBINS; ++b) {
-                float v = A.L[b * P + i];
+                float v = Lp[b];
                 v = (g == 1.f) ? v : ((g == 0.f) ? 0.f : v * g);
                 acc[b] += v * w * fw;
             }
@@ -163,7 +173,6 @@ k_film(DScene S, DFilm F, PathArrays A, RenderParams R) {
 // ---- K6: samples whose footprint covers other pixels (wide filters, pixel
 // edges): atomic splat, the device analogue of MergeFilmTile's overlap sums.
 __global__ void k_film_spill(DScene S, DFilm F, PathArrays A, RenderParams R) {
-    const size_t P = (size_t)A.capacity;
     const int64_t nPaths = (int64_t)R.nPix * R.samplesInPass;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nPaths;
          i += (int64_t)gridDim.x * blockDim.x) {
@@ -179,7 +188,7 @@ __global__ void k_film_spill(DScene S, DFilm F, PathArrays A, RenderParams R) {
                 float *px = F.pixels + ((size_t)(y - F.f.cropped[1]) * F.width + (x - F.f.cropped[0])) *
                                            SPTX_SPECTRUM_STRIDE;
                 for (int b = 0; b < SPTX_NBINS; ++b) {
-                    float v = A.L[b * P + i];
+                    float v = A.L[(size_t)i * SPTX_SPECTRUM_STRIDE + b];
                     v = (g == 1.f) ? v : ((g == 0.f) ? 0.f : v * g);
                     atomicAdd(px + b, v * w * fw);
                 }

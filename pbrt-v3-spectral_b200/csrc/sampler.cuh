@@ -82,6 +82,9 @@ SPTX_HD float radical_inverse_base(uint64_t a, uint32_t base) {
 }
 
 // ScrambledRadicalInverseSpecialized<base>, core/lowdiscrepancy.cpp:405-424.
+// Same integer digits and the same float operations; the 32-bit quotient is
+// found with a reciprocal multiply (magic = floor(2^32 / base), one fix-up)
+// instead of a hardware-emulated division.
 SPTX_DEV float scrambled_radical_inverse(const uint16_t *perm, uint64_t a, uint32_t base) {
     const float invBase = 1.f / (float)base;
     uint64_t reversed = 0;
@@ -94,9 +97,18 @@ SPTX_DEV float scrambled_radical_inverse(const uint16_t *perm, uint64_t a, uint3
         a = next;
     }
     uint32_t a32 = (uint32_t)a;
+    const uint32_t magic = 0xffffffffu / base;  // floor((2^32 - 1) / base) <= 2^32 / base
     while (a32) {
-        uint32_t next = a32 / base;
+        uint32_t next = __umulhi(a32, magic);    // in {q - 1, q}  (a32 * (1/base - magic/2^32) < 2)
         uint32_t digit = a32 - next * base;
+        if (digit >= base) {
+            ++next;
+            digit -= base;
+        }
+        if (digit >= base) {  // magic may undershoot twice when base divides 2^32 - 1 oddly
+            ++next;
+            digit -= base;
+        }
         reversed = reversed * base + __ldg(perm + digit);
         invBaseN *= invBase;
         a32 = next;
@@ -106,7 +118,7 @@ SPTX_DEV float scrambled_radical_inverse(const uint16_t *perm, uint64_t a, uint3
 }
 
 // HaltonSampler::SampleDimension, samplers/halton.cpp:117-127.
-SPTX_DEV float halton_sample(const DSampler &H, uint64_t index, int dim) {
+SPTX_NOINL float halton_sample(const DSampler &H, uint64_t index, int dim) {
     if (H.s.sample_at_center && (dim == 0 || dim == 1)) return 0.5f;
     if (dim == 0) {
         // RadicalInverse(0, a) = ReverseBits64(a) * 0x1p-64 in DOUBLE, rounded

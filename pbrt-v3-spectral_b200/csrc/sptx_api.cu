@@ -141,6 +141,10 @@ extern "C" int sptx_create(int device, sptx_ctx **out) {
     ctx->smCount = prop.multiProcessorCount;
     if ((e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess)
         return bail(e, "cudaStreamCreate");
+    // k_shade keeps one recipe per thread in shared memory (more than 48 KB per block)
+    if ((e = cudaFuncSetAttribute(k_shade, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)(kBlock * sizeof(Recipe)))) != cudaSuccess)
+        return bail(e, "cudaFuncSetAttribute(k_shade)");
     cudaEventCreate(&ctx->ev0);
     cudaEventCreate(&ctx->ev1);
     cudaEventCreate(&ctx->ev2);
@@ -506,9 +510,9 @@ static int ensure_paths(sptx_ctx *ctx, int64_t P) {
     DA(rayB, P);
     DA(hitA, P);
     DA(hitB, P);
-    DA(beta[0], P * SPTX_NBINS);
-    DA(beta[1], P * SPTX_NBINS);
-    DA(L, P * SPTX_NBINS);
+    DA(beta[0], P * SPTX_SPECTRUM_STRIDE);
+    DA(beta[1], P * SPTX_SPECTRUM_STRIDE);
+    DA(L, P * SPTX_SPECTRUM_STRIDE);
     DA(sindex, P);
     DA(info, P);
     DA(pfilm, P);
@@ -516,8 +520,8 @@ static int ensure_paths(sptx_ctx *ctx, int64_t P) {
     DA(shB, P);
     DA(misA, P);
     DA(misB, P);
-    DA(fa, P * SPTX_NBINS);
-    DA(fb, P * SPTX_NBINS);
+    DA(fa, P * SPTX_SPECTRUM_STRIDE);
+    DA(fb, P * SPTX_SPECTRUM_STRIDE);
     DA(q[0], P);
     DA(q[1], P);
     DA(qNee, P);
@@ -601,7 +605,7 @@ static int render_pixels(sptx_ctx *ctx, const std::vector<int2> &pixels, int s0,
                 k_set_counters<<<1, 1, 0, ctx->stream>>>(A.counters, qi ^ 1, 0, 2, 0);
                 ++launches;
                 tic(2);
-                k_shade<<<g, kBlock, 0, ctx->stream>>>(ctx->S, ctx->H, A, R, qi, betaIn, ctx->dCnt);
+                k_shade<<<g, kBlock, kBlock * sizeof(Recipe), ctx->stream>>>(ctx->S, ctx->H, A, R, qi, betaIn, ctx->dCnt);
                 toc();
                 if (bounce < maxDepth) {
                     tic(3);
@@ -940,11 +944,10 @@ extern "C" int sptx_debug_radiance(sptx_ctx *ctx, const int32_t *px, const int32
     free_pool(pool);
     if (rc) return rc;
     const PathArrays &A = ctx->A;
-    std::vector<float> tmp((size_t)n);
-    for (int b = 0; b < SPTX_NBINS; ++b) {
-        CK(cudaMemcpy(tmp.data(), A.L + (size_t)b * A.capacity, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost));
-        for (int64_t i = 0; i < n; ++i) L[i * SPTX_NBINS + b] = tmp[i];
-    }
+    std::vector<float> tmp((size_t)n * SPTX_SPECTRUM_STRIDE);
+    CK(cudaMemcpy(tmp.data(), A.L, tmp.size() * sizeof(float), cudaMemcpyDeviceToHost));
+    for (int64_t i = 0; i < n; ++i)
+        for (int b = 0; b < SPTX_NBINS; ++b) L[i * SPTX_NBINS + b] = tmp[i * SPTX_SPECTRUM_STRIDE + b];
     if (pfilm_weight) {
         std::vector<float2> pf((size_t)n);
         std::vector<float4> rb((size_t)n);
