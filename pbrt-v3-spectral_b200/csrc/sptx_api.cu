@@ -143,7 +143,7 @@ extern "C" int sptx_create(int device, sptx_ctx **out) {
         return bail(e, "cudaStreamCreate");
     // k_shade keeps one recipe per thread in shared memory (more than 48 KB per block)
     if ((e = cudaFuncSetAttribute(k_shade, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  (int)(kBlock * sizeof(Recipe)))) != cudaSuccess)
+                                  (int)(kShadeBlock * sizeof(Recipe)))) != cudaSuccess)
         return bail(e, "cudaFuncSetAttribute(k_shade)");
     cudaEventCreate(&ctx->ev0);
     cudaEventCreate(&ctx->ev1);
@@ -589,6 +589,8 @@ static int render_pixels(sptx_ctx *ctx, const std::vector<int2> &pixels, int s0,
             R.sampleList = dSampleList;
             const int64_t nPaths = (int64_t)nPix * R.samplesInPass;
             const int g = grid_for(ctx, nPaths);
+            // one resident 512-thread block per SM (128 registers per thread)
+            const int gShade = (int)std::min<int64_t>((nPaths + kShadeBlock - 1) / kShadeBlock, ctx->smCount);
             k_set_counters<<<1, 1, 0, ctx->stream>>>(A.counters, 0, 0, 1, 0);
             ++launches;
             tic(0);
@@ -605,7 +607,7 @@ static int render_pixels(sptx_ctx *ctx, const std::vector<int2> &pixels, int s0,
                 k_set_counters<<<1, 1, 0, ctx->stream>>>(A.counters, qi ^ 1, 0, 2, 0);
                 ++launches;
                 tic(2);
-                k_shade<<<g, kBlock, kBlock * sizeof(Recipe), ctx->stream>>>(ctx->S, ctx->H, A, R, qi, betaIn, ctx->dCnt);
+                k_shade<<<gShade, kShadeBlock, kShadeBlock * sizeof(Recipe), ctx->stream>>>(ctx->S, ctx->H, A, R, qi, betaIn, ctx->dCnt);
                 toc();
                 if (bounce < maxDepth) {
                     tic(3);
