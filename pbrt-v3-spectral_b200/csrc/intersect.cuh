@@ -195,6 +195,16 @@ struct SphereHit {
 SPTX_NOINL bool sphere_test(const sptx_sphere &sp, const Ray &wr, SphereHit *h) {
     V3 oErr, dErr;
     Ray ray = xf_ray_err(sp.w2o, wr, &oErr, &dErr);
+    {
+        // Early out on the value parts alone: Quadratic(EFloat...) decides "no real
+        // root" from the float values of a, b, c in double (core/efloat.h:266-270);
+        // the error bounds play no part in that decision.
+        const V3 o = ray.o, d = ray.d;
+        const float av = d.x * d.x + d.y * d.y + d.z * d.z;
+        const float bv = 2.f * (d.x * o.x + d.y * o.y + d.z * o.z);
+        const float cv = o.x * o.x + o.y * o.y + o.z * o.z - sp.radius * sp.radius;
+        if ((double)bv * (double)bv - 4. * (double)av * (double)cv < 0.) return false;
+    }
     EF ox = ef(ray.o.x, oErr.x), oy = ef(ray.o.y, oErr.y), oz = ef(ray.o.z, oErr.z);
     EF dx = ef(ray.d.x, dErr.x), dy = ef(ray.d.y, dErr.y), dz = ef(ray.d.z, dErr.z);
     EF a = dx * dx + dy * dy + dz * dz;
@@ -322,41 +332,25 @@ __device__ bool traverse_bvh(const DScene &S, int bvhIndex, Ray &ray, HitRec *hi
     int neg[3] = {invDir.x < 0, invDir.y < 0, invDir.z < 0};
     int stack[64];
     int sp = 0, cur = 0;
-    while (true) {
-        float4 n0 = __ldg(nodes + 2 * (size_t)cur), n1 = __ldg(nodes + 2 * (size_t)cur + 1);
-        if (COUNT) cnt->nodes++;
-        if (slab_test(n0, n1, ray.o, invDir, neg, ray.tMax)) {
-            int offset = __float_as_int(n1.z);
-            unsigned meta = (unsigned)__float_as_int(n1.w);
-            int nPrims = (int)(meta & 0xffffu);
-            if (nPrims > 0) {
-                for (int i = 0; i < nPrims; ++i) {
-                    int gp = B.prim_base + offset + i;
-                    const float4 *lv = S.leafv + 3 * (size_t)gp;
-                    float4 v0 = __ldg(lv), v1 = __ldg(lv + 1), v2 = __ldg(lv + 2);
-                    int kind = __float_as_int(v2.w), shape = __float_as_int(v2.y);
-                    if (COUNT) cnt->tests++;
-                    if (LEVEL == 0 && kind == SPTX_PRIM_INSTANCE) {
-                        // TransformedPrimitive::Intersect[P], core/primitive.cpp:78-99
-                        const sptx_instance &I = S.instances[shape];
-                        Ray r2 = xf_ray(I.w2p, ray);
-                        HitRec h2 = *hit;
-                        if (traverse_bvh<ANY, COUNT, 1>(S, I.bvh, r2, &h2, cnt)) {
-                            if (ANY) return true;
-                            ray.tMax = r2.tMax;
-                            *hit = h2;
-                            hit->inst = shape;
-                            found = true;
-                        }
-                    } else if (prim_test<ANY>(S, gp, ray, hit, kind, shape, v0, v1, v2)) {
-                        if (ANY) return true;
-                        if (LEVEL == 0) hit->inst = -1;
-                        found = true;
-                    }
+    // "while-while": every lane first walks interior nodes until it holds a
+    // leaf (or runs out of nodes); the warp reconverges, then the lanes that
+    // hold a leaf run the (long) primitive tests together.  Per ray the node
+    // and primitive order is exactly the reference's.
+    bool done = false;
+    while (!done) {
+        int leafOffset = 0, leafN = 0;
+        while (true) {
+            float4 n0 = __ldg(nodes + 2 * (size_t)cur), n1 = __ldg(nodes + 2 * (size_t)cur + 1);
+            if (COUNT) cnt->nodes++;
+            if (slab_test(n0, n1, ray.o, invDir, neg, ray.tMax)) {
+                int offset = __float_as_int(n1.z);
+                unsigned meta = (unsigned)__float_as_int(n1.w);
+                int nPrims = (int)(meta & 0xffffu);
+                if (nPrims > 0) {
+                    leafOffset = offset;
+                    leafN = nPrims;
+                    break;
                 }
-                if (sp == 0) break;
-                cur = stack[--sp];
-            } else {
                 int axis = (int)((meta >> 16) & 0xffu);
                 if (neg[axis]) {
                     stack[sp++] = cur + 1;
@@ -365,10 +359,43 @@ __device__ bool traverse_bvh(const DScene &S, int bvhIndex, Ray &ray, HitRec *hi
                     stack[sp++] = offset;
                     cur = cur + 1;
                 }
+            } else {
+                if (sp == 0) {
+                    done = true;
+                    break;
+                }
+                cur = stack[--sp];
             }
-        } else {
-            if (sp == 0) break;
-            cur = stack[--sp];
+        }
+        if (leafN > 0) {
+            for (int i = 0; i < leafN; ++i) {
+                int gp = B.prim_base + leafOffset + i;
+                const float4 *lv = S.leafv + 3 * (size_t)gp;
+                float4 v0 = __ldg(lv), v1 = __ldg(lv + 1), v2 = __ldg(lv + 2);
+                int kind = __float_as_int(v2.w), shape = __float_as_int(v2.y);
+                if (COUNT) cnt->tests++;
+                if (LEVEL == 0 && kind == SPTX_PRIM_INSTANCE) {
+                    // TransformedPrimitive::Intersect[P], core/primitive.cpp:78-99
+                    const sptx_instance &I = S.instances[shape];
+                    Ray r2 = xf_ray(I.w2p, ray);
+                    HitRec h2 = *hit;
+                    if (traverse_bvh<ANY, COUNT, 1>(S, I.bvh, r2, &h2, cnt)) {
+                        if (ANY) return true;
+                        ray.tMax = r2.tMax;
+                        *hit = h2;
+                        hit->inst = shape;
+                        found = true;
+                    }
+                } else if (prim_test<ANY>(S, gp, ray, hit, kind, shape, v0, v1, v2)) {
+                    if (ANY) return true;
+                    if (LEVEL == 0) hit->inst = -1;
+                    found = true;
+                }
+            }
+            if (sp == 0)
+                done = true;
+            else
+                cur = stack[--sp];
         }
     }
     return found;

@@ -123,7 +123,7 @@ SPTX_NOINL void bin_pass(const DScene &S, const PathArrays &A, Recipe *wr, int l
 // warp): they keep the block's warps inside the same few KB of code, so that
 // the SM's instruction cache serves all of them from one fetch (the kernel is
 // ~200 KB of SASS; see DESIGN.md, "k_shade and the instruction cache").
-constexpr int kShadeBlock = 512;
+constexpr int kShadeBlock = 1024;
 #define SPTX_STAGE() __syncthreads()
 
 __global__ void __launch_bounds__(kShadeBlock, 1)
