@@ -53,18 +53,36 @@ __global__ void k_generate(DScene S, DCamera C, DSampler H, PathArrays A, Render
 
 // ---- K2: closest hit for the active queue ------------------------------------
 template <bool COUNT>
-__global__ void k_intersect(DScene S, PathArrays A, int qi, DeviceCounters *cnt) {
+__global__ void __launch_bounds__(kBlock, 6)
+k_intersect(DScene S, PathArrays A, int qi, DeviceCounters *cnt) {
     const int n = A.counters[qi];
     const int *queue = A.q[qi];
+    const int lane = threadIdx.x & 31;
     TravCounters tc{0, 0};
-    for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
-        const int i = queue[k];
-        float4 ra = A.rayA[i], rb = A.rayB[i];
-        Ray ray{mk(ra.x, ra.y, ra.z), mk(ra.w, rb.x, rb.y), kInf};
-        HitRec h;
-        scene_intersect<COUNT>(S, ray, &h, &tc);
-        A.hitA[i] = make_float4(__int_as_float(h.prim), __int_as_float(h.inst), h.b0, h.b1);
-        A.hitB[i] = make_float4(h.b2, ray.tMax, 0.f, 0.f);
+    for (int k0 = blockIdx.x * blockDim.x; k0 < n; k0 += gridDim.x * blockDim.x) {
+        const int k = k0 + threadIdx.x;
+        const bool valid = k < n;
+        int i = 0, cls = 0;
+        if (valid) {
+            i = queue[k];
+            float4 ra = A.rayA[i], rb = A.rayB[i];
+            Ray ray{mk(ra.x, ra.y, ra.z), mk(ra.w, rb.x, rb.y), kInf};
+            HitRec h;
+            scene_intersect<COUNT>(S, ray, &h, &tc);
+            A.hitA[i] = make_float4(__int_as_float(h.prim), __int_as_float(h.inst), h.b0, h.b1);
+            A.hitB[i] = make_float4(h.b2, ray.tMax, 0.f, 0.f);
+            if (h.prim >= 0) cls = S.prim_class[h.prim];
+        }
+        // append to the queue of the hit's shading class: one atomic per class per warp
+        const unsigned vmask = __ballot_sync(0xffffffffu, valid);
+        if (valid) {
+            const unsigned peers = __match_any_sync(vmask, cls);
+            const int leader = __ffs(peers) - 1;
+            int base = 0;
+            if (lane == leader) base = atomicAdd(A.counters + kClassCounter0 + cls, __popc(peers));
+            base = __shfl_sync(peers, base, leader);
+            A.qc[(size_t)cls * A.capacity + base + __popc(peers & ((1u << lane) - 1u))] = i;
+        }
     }
     if (COUNT) {
         atomicAdd(&cnt->nodes[0], (unsigned long long)tc.nodes);

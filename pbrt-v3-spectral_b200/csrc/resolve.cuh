@@ -5,52 +5,68 @@
 namespace sptx {
 
 // ---- K4 ------------------------------------------------------------------------
-// VisibilityTester::Unoccluded (core/light.cpp:59-61) for the light sample and
-// the closest-hit test of the BSDF-sampled direction (core/integrator.cpp:
-// 190-212), then L += beta * (Ld / lightPdf) (integrator.cpp:104-105,
-// path.cpp:122-128).
+// The two rays of EstimateDirect.  K4a traces the (few) BSDF-sampled MIS rays as
+// closest-hit rays and records whether they reach the sampled light
+// (core/integrator.cpp:190-212); K4b traces the shadow rays
+// (VisibilityTester::Unoccluded, core/light.cpp:59-61) and adds
+// L += beta * (Ld / lightPdf) (integrator.cpp:104-105, path.cpp:122-128).
 template <bool COUNT>
-__global__ void __launch_bounds__(kBlock)
+__global__ void __launch_bounds__(kBlock, 6)
+k_mis(DScene S, PathArrays A, DeviceCounters *cnt) {
+    TravCounters tc{0, 0};
+    const int n = A.counters[4];
+    for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
+        const int i = A.qMis[k];
+        const float4 ma = A.misA[i], mb = A.misB[i];
+        const int lightNum = __float_as_int(mb.z);
+        Ray r{mk(ma.x, ma.y, ma.z), mk(ma.w, mb.x, mb.y), kInf};
+        HitRec h;
+        bool useB = false;
+        if (scene_intersect<COUNT>(S, r, &h, &tc)) {
+            if (S.prims[h.prim].light == lightNum) {
+                const sptx_light &Lt = S.lights[lightNum];
+                if (Lt.two_sided)
+                    useB = true;
+                else {
+                    Isect it;
+                    if (build_interaction(S, r, h.prim, h.inst, h.b0, h.b1, h.b2, &it))
+                        useB = dot(it.n, -r.d) > 0;
+                }
+            }
+        }
+        if (useB) A.misB[i].w = __int_as_float(__float_as_int(mb.w) | NEE_MIS_REACHED_LIGHT);
+    }
+    if (COUNT) {
+        atomicAdd(&cnt->nodes[1], (unsigned long long)tc.nodes);
+        atomicAdd(&cnt->tests[1], (unsigned long long)tc.tests);
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&cnt->closestRays, (unsigned long long)n);
+}
+
+template <bool COUNT>
+__global__ void __launch_bounds__(kBlock, 6)
 k_resolve(DScene S, PathArrays A, int betaIn, DeviceCounters *cnt) {
     TravCounters tc{0, 0};
     const int n = A.counters[2];
     const float *beta = A.beta[betaIn];
     const int lane = threadIdx.x & 31;
-    unsigned long long nShadow = 0, nClosest = 0;
+    unsigned long long nShadow = 0;
     for (int k0 = blockIdx.x * blockDim.x; k0 < n; k0 += gridDim.x * blockDim.x) {
         const int k = k0 + threadIdx.x;
         bool useA = false, useB = false;
         int i = 0;
         float lightPdfSel = 1.f;
         if (k < n) {
-        i = A.qNee[k];
-        const float4 sa = A.shA[i], sb = A.shB[i];
-        const float4 ma = A.misA[i], mb = A.misB[i];
-        const int flags = __float_as_int(mb.w);
-        const int lightNum = __float_as_int(mb.z);
-        lightPdfSel = sb.w;
-        if (flags & NEE_HAS_SHADOW) {
-            Ray r{mk(sa.x, sa.y, sa.z), mk(sa.w, sb.x, sb.y), sb.z};
-            useA = !scene_intersect_p<COUNT>(S, r, &tc);
-            ++nShadow;
-        }
-        if (flags & NEE_HAS_MIS) {
-            Ray r{mk(ma.x, ma.y, ma.z), mk(ma.w, mb.x, mb.y), kInf};
-            HitRec h;
-            ++nClosest;
-            if (scene_intersect<COUNT>(S, r, &h, &tc)) {
-                if (S.prims[h.prim].light == lightNum) {
-                    const sptx_light &Lt = S.lights[lightNum];
-                    if (Lt.two_sided)
-                        useB = true;
-                    else {
-                        Isect it;
-                        if (build_interaction(S, r, h.prim, h.inst, h.b0, h.b1, h.b2, &it))
-                            useB = dot(it.n, -r.d) > 0;
-                    }
-                }
+            i = A.qNee[k];
+            const float4 sa = A.shA[i], sb = A.shB[i];
+            const int flags = __float_as_int(A.misB[i].w);
+            lightPdfSel = sb.w;
+            useB = (flags & NEE_MIS_REACHED_LIGHT) != 0;
+            if (flags & NEE_HAS_SHADOW) {
+                Ray r{mk(sa.x, sa.y, sa.z), mk(sa.w, sb.x, sb.y), sb.z};
+                useA = !scene_intersect_p<COUNT>(S, r, &tc);
+                ++nShadow;
             }
-        }
         }
         // bin phase: the warp walks its paths, lane = bin
         const unsigned mA = __ballot_sync(0xffffffffu, useA);
@@ -70,15 +86,9 @@ k_resolve(DScene S, PathArrays A, int betaIn, DeviceCounters *cnt) {
         atomicAdd(&cnt->nodes[1], (unsigned long long)tc.nodes);
         atomicAdd(&cnt->tests[1], (unsigned long long)tc.tests);
     }
-    // one atomic per warp for the ray counters
-    for (int o = 16; o > 0; o >>= 1) {
-        nShadow += __shfl_down_sync(0xffffffffu, nShadow, o);
-        nClosest += __shfl_down_sync(0xffffffffu, nClosest, o);
-    }
-    if ((threadIdx.x & 31) == 0) {
-        if (nShadow) atomicAdd(&cnt->shadowRays, nShadow);
-        if (nClosest) atomicAdd(&cnt->closestRays, nClosest);
-    }
+    // one atomic per warp for the ray counter
+    for (int o = 16; o > 0; o >>= 1) nShadow += __shfl_down_sync(0xffffffffu, nShadow, o);
+    if (lane == 0 && nShadow) atomicAdd(&cnt->shadowRays, nShadow);
 }
 
 // ---- K5: film accumulation, one thread per pixel ------------------------------
@@ -130,6 +140,16 @@ SPTX_DEV float guard_scale(const DScene &S, const DFilm &F, const PathArrays &A,
 
 __global__ void __launch_bounds__(kBlock)
 k_film(DScene S, DFilm F, PathArrays A, RenderParams R) {
+#ifdef SPTX_STAGE_CLOCKS
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        unsigned long long tot = 0;
+        for (int c = 0; c < 24; ++c) tot += g_stageClocks[c];
+        for (int c = 0; c < 17; ++c) {
+            printf("stage slot %2d: %5.1f%%\n", c, 100.0 * (double)g_stageClocks[c] / (double)tot);
+            g_stageClocks[c] = 0;
+        }
+    }
+#endif
     for (int pix = blockIdx.x * blockDim.x + threadIdx.x; pix < R.nPix;
          pix += gridDim.x * blockDim.x) {
         const int2 pxy = R.pixels[pix];

@@ -73,12 +73,18 @@ struct Recipe {
 SPTX_NOINL void bin_pass(const DScene &S, const PathArrays &A, Recipe *wr, int lane,
                          const float *betaCur, float *betaNext) {
     const bool live = lane < SPTX_NBINS;
-    for (int p = 0; p < 32; ++p) {
+    unsigned todo = __ballot_sync(0xffffffffu, wr[lane].path >= 0 && wr[lane].work != 0);
+    if (todo == 0) return;
+    // the next path's throughput row is requested while this one is processed
+    float betaAhead = betaCur[(size_t)wr[__ffs(todo) - 1].path * SPTX_SPECTRUM_STRIDE + lane];
+    while (todo) {
+        const int p = __ffs(todo) - 1;
+        todo &= todo - 1;
         const Recipe &r = wr[p];
         const int work = r.work;
-        if (r.path < 0 || work == 0) continue;
         const size_t at = (size_t)r.path * SPTX_SPECTRUM_STRIDE + lane;
-        const float beta = betaCur[at];
+        const float beta = betaAhead;
+        if (todo) betaAhead = betaCur[(size_t)wr[__ffs(todo) - 1].path * SPTX_SPECTRUM_STRIDE + lane];
         if ((work & W_EMIT) && live) A.L[at] += beta * spec(S, r.emitRow, lane);
         int black = 0;
         float mb = 0.f;
@@ -124,24 +130,56 @@ SPTX_NOINL void bin_pass(const DScene &S, const PathArrays &A, Recipe *wr, int l
 // the SM's instruction cache serves all of them from one fetch (the kernel is
 // ~200 KB of SASS; see DESIGN.md, "k_shade and the instruction cache").
 constexpr int kShadeBlock = 1024;
-#define SPTX_STAGE() __syncthreads()
+constexpr int kShadeBlocksPerSM = 1;
+#ifdef SPTX_STAGE_CLOCKS  // diagnosis build: per-stage warp clocks, printed by k_film
+__device__ unsigned long long g_stageClocks[32];
+#define SPTX_TICK(slot)                      \
+    do {                                     \
+        long long now_ = clock64();          \
+        stageClk[slot] += now_ - tPrev;      \
+        tPrev = now_;                        \
+    } while (0)
+#else
+#define SPTX_TICK(slot)
+#endif
+#define SPTX_STAGE(slot)  \
+    do {                  \
+        SPTX_TICK(slot);  \
+        __syncthreads();  \
+        SPTX_TICK(slot + 1); \
+    } while (0)
 
-__global__ void __launch_bounds__(kShadeBlock, 1)
+__global__ void __launch_bounds__(kShadeBlock, kShadeBlocksPerSM)
 k_shade(DScene S, DSampler H, PathArrays A, RenderParams R, int qi, int betaIn,
         DeviceCounters *cnt) {
     extern __shared__ unsigned char smemRaw[];
     Recipe *recipes = reinterpret_cast<Recipe *>(smemRaw);
-    const int n = A.counters[qi];
-    const int *queue = A.q[qi];
+    // work list: the class queues one after the other, in block-sized chunks
+    int classN[kShadeClasses], nChunks = 0, n = 0;
+    for (int c = 0; c < kShadeClasses; ++c) {
+        classN[c] = A.counters[kClassCounter0 + c];
+        nChunks += (classN[c] + (int)blockDim.x - 1) / (int)blockDim.x;
+        n += classN[c];
+    }
     const float *betaCur = A.beta[betaIn];
     float *betaNext = A.beta[betaIn ^ 1];
     const int lane = threadIdx.x & 31;
     Recipe *wr = recipes + (threadIdx.x & ~31);
     Recipe &rc = recipes[threadIdx.x];
     const int noSpec = BSDF_ALL & ~BSDF_SPECULAR;
-    for (int k0 = blockIdx.x * blockDim.x; k0 < n; k0 += gridDim.x * blockDim.x) {
-        const int k = k0 + threadIdx.x;
-        bool alive = k < n;
+#ifdef SPTX_STAGE_CLOCKS
+    long long stageClk[24] = {0};
+    long long tPrev = clock64();
+#endif
+    for (int chunk = blockIdx.x; chunk < nChunks; chunk += gridDim.x) {
+        int cls = 0, first = chunk;
+        while (first >= (classN[cls] + (int)blockDim.x - 1) / (int)blockDim.x) {
+            first -= (classN[cls] + (int)blockDim.x - 1) / (int)blockDim.x;
+            ++cls;
+        }
+        const int *queue = A.qc + (size_t)cls * A.capacity;
+        const int k = first * (int)blockDim.x + (int)threadIdx.x;
+        bool alive = k < classN[cls];
         int i = 0;
         rc.path = -1;
         rc.work = 0;
@@ -155,6 +193,8 @@ k_shade(DScene S, DSampler H, PathArrays A, RenderParams R, int qi, int betaIn,
         if (alive) {
             i = queue[k];
             rc.path = i;
+            // the bin passes read this path's throughput row much later: have it in L2 by then
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(betaCur + (size_t)i * SPTX_SPECTRUM_STRIDE));
             const float4 ra = A.rayA[i], rb = A.rayB[i];
             const float4 ha = A.hitA[i], hb = A.hitB[i];
             ray.o = mk(ra.x, ra.y, ra.z);
@@ -182,7 +222,7 @@ k_shade(DScene S, DSampler H, PathArrays A, RenderParams R, int qi, int betaIn,
             }
             alive = haveIsect && bounces < R.maxDepth;
         }
-        SPTX_STAGE();
+        SPTX_STAGE(0);
         // ---- stage 1: BSDF frame, light choice (integrator.cpp:85-106) ----
         bool nee = false;
         V2 uLight{0, 0}, uScattering{0, 0};
@@ -197,7 +237,7 @@ k_shade(DScene S, DSampler H, PathArrays A, RenderParams R, int qi, int betaIn,
                 }
             }
         }
-        SPTX_STAGE();
+        SPTX_STAGE(2);
         // ---- stage 2: light sampling strategy (integrator.cpp:119-163) ----
         bool delta = false, wantShadow = false, wantMis = false;
         V3 shO = mk(0, 0, 0), shD = mk(0, 0, 0), misO = mk(0, 0, 0), misD = mk(0, 0, 0);
@@ -210,7 +250,7 @@ k_shade(DScene S, DSampler H, PathArrays A, RenderParams R, int qi, int betaIn,
             RefPoint ref{it.p, it.pError, it.n};
             ls = light_sample_li(S, Lt, ref, uLight);
         }
-        SPTX_STAGE();
+        SPTX_STAGE(4);
         // (Li.IsBlack() is decided per bin by the pass: Recipe::black)
         if (nee && ls.pdf > 0 && !ls.black) {
             bsdf_f(S, bs, it.wo, ls.wi, noSpec, &rc.f);
@@ -227,12 +267,12 @@ k_shade(DScene S, DSampler H, PathArrays A, RenderParams R, int qi, int betaIn,
             shD = target - shO;
             wantShadow = true;
         }
-        SPTX_STAGE();
+        SPTX_STAGE(6);
         bin_pass(S, A, wr, lane, betaCur, betaNext);
         __syncwarp();
         if (wantShadow && !rc.black) neeFlags |= NEE_HAS_SHADOW;
         rc.work = 0;
-        SPTX_STAGE();
+        SPTX_STAGE(8);
         // ---- stage 3: BSDF sampling strategy (integrator.cpp:166-213) ----
         if (nee && !delta) {
             float sPdf;
@@ -262,7 +302,7 @@ k_shade(DScene S, DSampler H, PathArrays A, RenderParams R, int qi, int betaIn,
                 }
             }
         }
-        SPTX_STAGE();
+        SPTX_STAGE(10);
         bin_pass(S, A, wr, lane, betaCur, betaNext);
         __syncwarp();
         if (wantMis && !rc.black) neeFlags |= NEE_HAS_MIS;
@@ -273,7 +313,7 @@ k_shade(DScene S, DSampler H, PathArrays A, RenderParams R, int qi, int betaIn,
             A.misA[i] = make_float4(misO.x, misO.y, misO.z, misD.x);
             A.misB[i] = make_float4(misD.y, misD.z, __int_as_float(lightNum), __int_as_float(neeFlags));
         }
-        SPTX_STAGE();
+        SPTX_STAGE(12);
         // ---- stage 4: BSDF sample for the next path segment (path.cpp:131-150) ----
         V3 nextO = mk(0, 0, 0), nextD = mk(0, 0, 0);
         int flagsC = 0;
@@ -293,7 +333,7 @@ k_shade(DScene S, DSampler H, PathArrays A, RenderParams R, int qi, int betaIn,
             } else
                 alive = false;
         }
-        SPTX_STAGE();
+        SPTX_STAGE(14);
         bin_pass(S, A, wr, lane, betaCur, betaNext);
         __syncwarp();
         // ---- epilogue: Russian roulette (path.cpp:176-184), next ray ----
@@ -327,8 +367,14 @@ k_shade(DScene S, DSampler H, PathArrays A, RenderParams R, int qi, int betaIn,
         }
         __syncwarp();
         queue_push(A.qNee, A.counters + 2, i, neeFlags != 0);
+        queue_push(A.qMis, A.counters + 4, i, (neeFlags & NEE_HAS_MIS) != 0);
         queue_push(A.q[qi ^ 1], A.counters + (qi ^ 1), i, alive);
+        SPTX_TICK(16);
     }
+#ifdef SPTX_STAGE_CLOCKS
+    if (lane == 0)
+        for (int c = 0; c < 24; ++c) atomicAdd(&g_stageClocks[c], (unsigned long long)stageClk[c]);
+#endif
     if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&cnt->vertices, (unsigned long long)n);
 }
 

@@ -335,6 +335,29 @@ extern "C" int sptx_upload_scene(sptx_ctx *ctx, const sptx_scene_desc *sc) {
     if ((rc = upload(ctx, pool, sc->instances, sc->n_instances, &S.instances))) return rc;
     if ((rc = upload(ctx, pool, sc->materials, sc->n_materials, &S.materials))) return rc;
     if ((rc = upload(ctx, pool, sc->lobes, sc->n_lobes, &S.lobes))) return rc;
+    {
+        // shading class of a material = its list of (lobe type, fresnel kind); primitives
+        // carry the class so K2 can sort the paths it hands to K3
+        std::vector<std::vector<int>> sigs;
+        std::vector<uint8_t> matClass((size_t)sc->n_materials, 1);
+        for (int64_t m = 0; m < sc->n_materials; ++m) {
+            std::vector<int> sig;
+            for (int l = 0; l < sc->materials[m].n_lobes; ++l) {
+                const sptx_lobe &L = sc->lobes[sc->materials[m].first_lobe + l];
+                sig.push_back(L.type * 16 + L.fresnel);
+            }
+            size_t k = 0;
+            while (k < sigs.size() && sigs[k] != sig) ++k;
+            if (k == sigs.size()) sigs.push_back(sig);
+            matClass[(size_t)m] = (uint8_t)(1 + k % (kShadeClasses - 1));
+        }
+        std::vector<uint8_t> primClass((size_t)std::max<int64_t>(sc->n_prims, 1), 1);
+        for (int64_t i = 0; i < sc->n_prims; ++i) {
+            const int m = sc->prims[i].material;
+            primClass[(size_t)i] = m >= 0 ? matClass[(size_t)m] : (uint8_t)1;
+        }
+        if ((rc = upload(ctx, pool, primClass.data(), (int64_t)primClass.size(), &S.prim_class))) return rc;
+    }
     if ((rc = upload(ctx, pool, sc->spectra, SPTX_SPECTRUM_STRIDE * sc->n_spectra, &S.spectra))) return rc;
     if ((rc = upload(ctx, pool, sc->lights, sc->n_lights, &S.lights))) return rc;
     S.n_lights = (int)sc->n_lights;
@@ -493,6 +516,15 @@ __global__ void k_set_counters(int *counters, int a, int va, int b, int vb) {
     if (a >= 0) counters[a] = va;
     if (b >= 0) counters[b] = vb;
 }
+// start of a bounce: empty the queues this bounce fills
+__global__ void k_reset_bounce(int *counters, int qNext) {
+    if (threadIdx.x < kShadeClasses) counters[kClassCounter0 + threadIdx.x] = 0;
+    if (threadIdx.x == 0) {
+        counters[qNext] = 0;
+        counters[2] = 0;
+        counters[4] = 0;
+    }
+}
 
 static int ensure_paths(sptx_ctx *ctx, int64_t P) {
     if (ctx->allocatedPaths >= P) return SPTX_OK;
@@ -525,10 +557,12 @@ static int ensure_paths(sptx_ctx *ctx, int64_t P) {
     DA(q[0], P);
     DA(q[1], P);
     DA(qNee, P);
-    DA(counters, 8);
+    DA(qMis, P);
+    DA(qc, P * kShadeClasses);
+    DA(counters, 16);
     DA(spill, P);
 #undef DA
-    CK(cudaMemsetAsync(A.counters, 0, 8 * sizeof(int), ctx->stream));
+    CK(cudaMemsetAsync(A.counters, 0, 16 * sizeof(int), ctx->stream));
     ctx->allocatedPaths = P;
     return SPTX_OK;
 }
@@ -590,7 +624,8 @@ static int render_pixels(sptx_ctx *ctx, const std::vector<int2> &pixels, int s0,
             const int64_t nPaths = (int64_t)nPix * R.samplesInPass;
             const int g = grid_for(ctx, nPaths);
             // one resident 512-thread block per SM (128 registers per thread)
-            const int gShade = (int)std::min<int64_t>((nPaths + kShadeBlock - 1) / kShadeBlock, ctx->smCount);
+            const int gShade = (int)std::min<int64_t>((nPaths + kShadeBlock - 1) / kShadeBlock,
+                                                     (int64_t)ctx->smCount * kShadeBlocksPerSM);
             k_set_counters<<<1, 1, 0, ctx->stream>>>(A.counters, 0, 0, 1, 0);
             ++launches;
             tic(0);
@@ -598,23 +633,27 @@ static int render_pixels(sptx_ctx *ctx, const std::vector<int2> &pixels, int s0,
             toc();
             int qi = 0, betaIn = 0;
             for (int bounce = 0; bounce <= maxDepth; ++bounce) {
+                k_reset_bounce<<<1, 32, 0, ctx->stream>>>(A.counters, qi ^ 1);
+                ++launches;
                 tic(1);
                 if (cv)
                     k_intersect<true><<<g, kBlock, 0, ctx->stream>>>(ctx->S, A, qi, ctx->dCnt);
                 else
                     k_intersect<false><<<g, kBlock, 0, ctx->stream>>>(ctx->S, A, qi, ctx->dCnt);
                 toc();
-                k_set_counters<<<1, 1, 0, ctx->stream>>>(A.counters, qi ^ 1, 0, 2, 0);
-                ++launches;
                 tic(2);
                 k_shade<<<gShade, kShadeBlock, kShadeBlock * sizeof(Recipe), ctx->stream>>>(ctx->S, ctx->H, A, R, qi, betaIn, ctx->dCnt);
                 toc();
                 if (bounce < maxDepth) {
                     tic(3);
-                    if (cv)
+                    if (cv) {
+                        k_mis<true><<<g, kBlock, 0, ctx->stream>>>(ctx->S, A, ctx->dCnt);
                         k_resolve<true><<<g, kBlock, 0, ctx->stream>>>(ctx->S, A, betaIn, ctx->dCnt);
-                    else
+                    } else {
+                        k_mis<false><<<g, kBlock, 0, ctx->stream>>>(ctx->S, A, ctx->dCnt);
                         k_resolve<false><<<g, kBlock, 0, ctx->stream>>>(ctx->S, A, betaIn, ctx->dCnt);
+                    }
+                    ++launches;
                     toc();
                 }
                 qi ^= 1;

@@ -31,11 +31,18 @@ struct PathArrays {
     // queues of path ids
     int *q[2];
     int *qNee;
-    int *counters;  // [0],[1]: sizes of q[0], q[1]; [2]: qNee size; [3]: error flags
+    int *qMis;  // subset of qNee that also has a BSDF-sampled MIS ray (counters[4])
+    // the active queue again, split by shading class (written by K2, read by K3):
+    // warps of K3 then run one kind of material code
+    int *qc;        // [kShadeClasses][P]
+    int *counters;  // [0],[1]: sizes of q[0], q[1]; [2]: qNee size; [3]: error flags;
+                    // [8 .. 8+kShadeClasses): sizes of the class queues
     uint8_t *spill;  // per path: film sample needs the atomic (wide filter) pass
 };
 
-enum { NEE_HAS_SHADOW = 1, NEE_HAS_MIS = 2 };
+constexpr int kShadeClasses = 8;  // class 0 = no hit
+constexpr int kClassCounter0 = 8;
+enum { NEE_HAS_SHADOW = 1, NEE_HAS_MIS = 2, NEE_MIS_REACHED_LIGHT = 4 };
 enum { ERR_DIM_OVERFLOW = 1, ERR_INTERACTION = 2, ERR_TERMS = 4 };
 
 struct RenderParams {
