@@ -68,18 +68,36 @@ k_resolve(DScene S, PathArrays A, int betaIn, DeviceCounters *cnt) {
                 ++nShadow;
             }
         }
-        // bin phase: the warp walks its paths, lane = bin
+        // bin phase: the warp walks its paths, lane = bin; four paths per round so that
+        // their rows are in flight together
         const unsigned mA = __ballot_sync(0xffffffffu, useA);
         const unsigned mB = __ballot_sync(0xffffffffu, useB);
-        for (unsigned m = mA | mB; m; m &= m - 1) {
-            const int p = __ffs(m) - 1;
-            const int ip = __shfl_sync(0xffffffffu, i, p);
-            const float sel = __shfl_sync(0xffffffffu, lightPdfSel, p);
-            const size_t at = (size_t)ip * SPTX_SPECTRUM_STRIDE + lane;
-            float Ld = 0.f;
-            if ((mA >> p) & 1u) Ld += A.fa[at];
-            if ((mB >> p) & 1u) Ld += A.fb[at];
-            A.L[at] += beta[at] * (Ld / sel);
+        unsigned m = mA | mB;
+        while (m) {
+            size_t at[4];
+            float sel[4], va[4], vb[4], bt[4], Lv[4];
+            bool on[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                on[j] = m != 0;
+                const int p = on[j] ? __ffs(m) - 1 : 0;
+                m &= m - 1;
+                const int ip = __shfl_sync(0xffffffffu, i, p);
+                sel[j] = __shfl_sync(0xffffffffu, lightPdfSel, p);
+                at[j] = (size_t)ip * SPTX_SPECTRUM_STRIDE + lane;
+                va[j] = (on[j] && ((mA >> p) & 1u)) ? A.fa[at[j]] : 0.f;
+                vb[j] = (on[j] && ((mB >> p) & 1u)) ? A.fb[at[j]] : 0.f;
+                bt[j] = on[j] ? beta[at[j]] : 0.f;
+                Lv[j] = on[j] ? A.L[at[j]] : 0.f;
+                // Ld = Spectrum(0) + fa + fb in the order EstimateDirect adds them
+                float Ld = 0.f;
+                if ((mA >> p) & 1u) Ld += va[j];
+                if ((mB >> p) & 1u) Ld += vb[j];
+                va[j] = Ld;
+            }
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+                if (on[j]) A.L[at[j]] = Lv[j] + bt[j] * (va[j] / sel[j]);
         }
     }
     if (COUNT) {
