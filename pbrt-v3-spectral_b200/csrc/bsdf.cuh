@@ -117,6 +117,54 @@ SPTX_DEV float fsum_bin(const DScene &S, const FSum &f, int b) {
     return v;
 }
 
+// Four consecutive bins (4c .. 4c+3) of a term / of the sum: the thread-per-path
+// form.  Same per-bin operation order as fterm_bin.
+SPTX_DEV float4 spec4(const DScene &S, int row, int c) {
+    return __ldg(reinterpret_cast<const float4 *>(S.spectra + (size_t)row * SPTX_SPECTRUM_STRIDE) + c);
+}
+SPTX_DEV float4 fterm4(const DScene &S, const FTerm &t, int c) {
+    const float4 R = spec4(S, t.R, c);
+    switch (t.kind) {
+    case TERM_R_S:
+        return make_float4(R.x * t.s0, R.y * t.s0, R.z * t.s0, R.w * t.s0);
+    case TERM_R_S_S:
+        return make_float4(R.x * t.s0 * t.s1, R.y * t.s0 * t.s1, R.z * t.s0 * t.s1, R.w * t.s0 * t.s1);
+    case TERM_MICRO_S:
+        return make_float4(R.x * t.s0 * t.s1 * t.s2 / t.s3, R.y * t.s0 * t.s1 * t.s2 / t.s3,
+                           R.z * t.s0 * t.s1 * t.s2 / t.s3, R.w * t.s0 * t.s1 * t.s2 / t.s3);
+    case TERM_MICRO_COND: {
+        const float4 ei = spec4(S, t.e0, c), et = spec4(S, t.e1, c), k = spec4(S, t.e2, c);
+        return make_float4(R.x * t.s0 * t.s1 * fr_conductor_bin(t.s2, ei.x, et.x, k.x) / t.s3,
+                           R.y * t.s0 * t.s1 * fr_conductor_bin(t.s2, ei.y, et.y, k.y) / t.s3,
+                           R.z * t.s0 * t.s1 * fr_conductor_bin(t.s2, ei.z, et.z, k.z) / t.s3,
+                           R.w * t.s0 * t.s1 * fr_conductor_bin(t.s2, ei.w, et.w, k.w) / t.s3);
+    }
+    case TERM_S_R_DIV:
+        return make_float4(t.s0 * R.x / t.s1, t.s0 * R.y / t.s1, t.s0 * R.z / t.s1, t.s0 * R.w / t.s1);
+    case TERM_COND_R_DIV: {
+        const float4 ei = spec4(S, t.e0, c), et = spec4(S, t.e1, c), k = spec4(S, t.e2, c);
+        return make_float4(fr_conductor_bin(t.s0, ei.x, et.x, k.x) * R.x / t.s1,
+                           fr_conductor_bin(t.s0, ei.y, et.y, k.y) * R.y / t.s1,
+                           fr_conductor_bin(t.s0, ei.z, et.z, k.z) * R.z / t.s1,
+                           fr_conductor_bin(t.s0, ei.w, et.w, k.w) * R.w / t.s1);
+    }
+    default:  // TERM_T_S_S_DIV
+        return make_float4((R.x * t.s0) * t.s1 / t.s2, (R.y * t.s0) * t.s1 / t.s2,
+                           (R.z * t.s0) * t.s1 / t.s2, (R.w * t.s0) * t.s1 / t.s2);
+    }
+}
+SPTX_DEV float4 fsum4(const DScene &S, const FSum &f, int c) {
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int i = 0; i < f.n; ++i) {
+        const float4 t = fterm4(S, f.t[i], c);
+        v.x += t.x;
+        v.y += t.y;
+        v.z += t.z;
+        v.w += t.w;
+    }
+    return v;
+}
+
 // ---- local shading frame trigonometry, core/reflection.h:55-100 ------------
 SPTX_DEV float cos_theta(V3 w) { return w.z; }
 SPTX_DEV float cos2_theta(V3 w) { return w.z * w.z; }

@@ -3,15 +3,11 @@
 // integrators/path.cpp:88-184 for the vertex, core/integrator.cpp:85-215
 // (UniformSampleOneLight, EstimateDirect) for next-event estimation.
 //
-// Two kinds of phases alternate, so that the 31-bin arithmetic never diverges:
-//   scalar phase  one THREAD per path: interaction, BSDF frame, light choice,
-//                 light / BSDF sampling, pdfs, MIS weights, spawned rays.  The
-//                 spectral work it implies is written to shared memory as a
-//                 "recipe" (formula ids + spectrum rows + scalars).
-//   bin phase     the WARP walks its 32 recipes; lane b evaluates bin b.  Path
-//                 spectra are path-major ([P][32] floats), so every access is
-//                 one 128-byte line no matter how scattered the queue is, and
-//                 all branches are warp-uniform.
+// One thread per path.  K2 hands the paths over sorted by shading class, so a
+// warp holds one kind of material and the 31-bin loops of its paths run without
+// diverging; no shared memory is used (the L1 keeps the whole carve-out for
+// the per-thread interaction / BSDF state).  Spectra are path-major ([P][32]
+// floats): a thread moves its 128-byte rows as float4.
 // The two rays EstimateDirect traces (shadow ray, BSDF-sampled MIS ray) are
 // written out with their per-bin contributions (fa, fb) and traced by K4.
 #pragma once
@@ -45,127 +41,53 @@ SPTX_DEV float power_heuristic(float fPdf, float gPdf) {
 }
 
 
-// What one pass of the bin phase has to do for one path.
-enum {
-    W_EMIT = 1,      // L += beta * Le
-    W_FA = 2,        // fa = f * |wi.ns| * Li [* weight] / lightPdf   (light-sampling strategy)
-    W_FB = 4,        // fb = f * |wi.ns| * Le * weight / scatteringPdf (BSDF-sampling strategy)
-    W_FC = 8,        // betaNext = beta * (f * |wi.ns| / pdf); max(betaNext * etaScale)
-    W_FA_DELTA = 16  // delta light: no MIS weight
+struct Row4 {
+    float4 *p;
+    SPTX_DEV float4 ld(int c) const { return p[c]; }
+    SPTX_DEV void st(int c, float4 v) const { p[c] = v; }
 };
-
-struct Recipe {
-    int path;      // path id, -1 = idle lane
-    int work;      // W_* flags of the pending pass
-    int emitRow;   // Le spectrum row (W_EMIT)
-    int row;       // W_FA: light-sample radiance row; W_FB: Lemit row of the MIS light
-    float rowDiv;  // W_FA: 0, or divide the row by it (point light: I / d^2)
-    float ad, weight, pdf;
-    float etaScale;  // W_FC
-    float rrDiv;     // epilogue: betaNext /= rrDiv
-    // results of the pass
-    int black;  // f (or Li) is black in every bin
-    float maxBeta;
-    FSum f;
-};
-
-// One pass of the bin phase: the warp walks its 32 recipes, lane = bin.
-SPTX_NOINL void bin_pass(const DScene &S, const PathArrays &A, Recipe *wr, int lane,
-                         const float *betaCur, float *betaNext) {
-    const bool live = lane < SPTX_NBINS;
-    unsigned todo = __ballot_sync(0xffffffffu, wr[lane].path >= 0 && wr[lane].work != 0);
-    if (todo == 0) return;
-    // the next path's throughput row is requested while this one is processed
-    float betaAhead = betaCur[(size_t)wr[__ffs(todo) - 1].path * SPTX_SPECTRUM_STRIDE + lane];
-    while (todo) {
-        const int p = __ffs(todo) - 1;
-        todo &= todo - 1;
-        const Recipe &r = wr[p];
-        const int work = r.work;
-        const size_t at = (size_t)r.path * SPTX_SPECTRUM_STRIDE + lane;
-        const float beta = betaAhead;
-        if (todo) betaAhead = betaCur[(size_t)wr[__ffs(todo) - 1].path * SPTX_SPECTRUM_STRIDE + lane];
-        if ((work & W_EMIT) && live) A.L[at] += beta * spec(S, r.emitRow, lane);
-        int black = 0;
-        float mb = 0.f;
-        if (work & (W_FA | W_FB | W_FC)) {
-            const float fs = live ? fsum_bin(S, r.f, lane) : 0.f;
-            if (work & W_FA) {
-                const float fv = fs * r.ad;
-                float li = live ? spec(S, r.row, lane) : 0.f;
-                if (r.rowDiv != 0.f) li = li / r.rowDiv;
-                float c = fv * li;
-                if (!(work & W_FA_DELTA)) c = c * r.weight;
-                A.fa[at] = c / r.pdf;
-                if (__ballot_sync(0xffffffffu, fv != 0.f) == 0) black = 1;
-                if (__ballot_sync(0xffffffffu, li != 0.f) == 0) black = 1;
-            } else if (work & W_FB) {
-                const float fv = fs * r.ad;
-                const float le = live ? spec(S, r.row, lane) : 0.f;
-                A.fb[at] = fv * le * r.weight / r.pdf;
-                if (__ballot_sync(0xffffffffu, fv != 0.f) == 0) black = 1;
-            } else {
-                const float nb = beta * (fs * r.ad / r.pdf);
-                betaNext[at] = nb;
-                if (__ballot_sync(0xffffffffu, fs != 0.f) == 0) black = 1;
-                // MaxComponentValue(beta * etaScale): max does not depend on the order
-                float v = live ? nb * r.etaScale : -kInf;
-                for (int o = 16; o > 0; o >>= 1) {
-                    float w = __shfl_xor_sync(0xffffffffu, v, o);
-                    v = (v < w) ? w : v;
-                }
-                mb = v;
-            }
-        }
-        if (lane == 0) {
-            wr[p].black = black;
-            wr[p].maxBeta = mb;
-        }
-    }
+SPTX_DEV Row4 row4(float *base, int i) {
+    return Row4{reinterpret_cast<float4 *>(base + (size_t)i * SPTX_SPECTRUM_STRIDE)};
+}
+// bins of chunk c that exist (the last chunk has the pad word)
+SPTX_DEV bool any_nonzero4(float4 v, int c) {
+    return v.x != 0.f || v.y != 0.f || v.z != 0.f || (c < 7 && v.w != 0.f);
 }
 
 // The vertex is cut into stages with a block barrier between them.  The
-// barriers are not needed for correctness (a recipe is only shared inside its
-// warp): they keep the block's warps inside the same few KB of code, so that
-// the SM's instruction cache serves all of them from one fetch (the kernel is
-// ~200 KB of SASS; see DESIGN.md, "k_shade and the instruction cache").
+// barriers are not needed for correctness: they keep the SM's warps inside the
+// same few KB of code, so that the instruction cache serves all of them from
+// one fetch (the kernel is ~200 KB of SASS and a warp walks most of it once per
+// vertex; free-running warps had a 53 % instruction-cache hit rate -- DESIGN.md 5).
+// One 1024-thread block per SM.
 constexpr int kShadeBlock = 1024;
-constexpr int kShadeBlocksPerSM = 1;
 #ifdef SPTX_STAGE_CLOCKS  // diagnosis build: per-stage warp clocks, printed by k_film
 __device__ unsigned long long g_stageClocks[32];
-#define SPTX_TICK(slot)                      \
-    do {                                     \
-        long long now_ = clock64();          \
-        stageClk[slot] += now_ - tPrev;      \
-        tPrev = now_;                        \
+#define SPTX_TICK(slot)                 \
+    do {                                \
+        long long now_ = clock64();     \
+        stageClk[slot] += now_ - tPrev; \
+        tPrev = now_;                   \
     } while (0)
 #else
 #define SPTX_TICK(slot)
 #endif
-#define SPTX_STAGE(slot)  \
-    do {                  \
-        SPTX_TICK(slot);  \
-        __syncthreads();  \
+#define SPTX_STAGE(slot)     \
+    do {                     \
+        SPTX_TICK(slot);     \
+        __syncthreads();     \
         SPTX_TICK(slot + 1); \
     } while (0)
 
-__global__ void __launch_bounds__(kShadeBlock, kShadeBlocksPerSM)
+__global__ void __launch_bounds__(kShadeBlock, 1)
 k_shade(DScene S, DSampler H, PathArrays A, RenderParams R, int qi, int betaIn,
         DeviceCounters *cnt) {
-    extern __shared__ unsigned char smemRaw[];
-    Recipe *recipes = reinterpret_cast<Recipe *>(smemRaw);
-    // work list: the class queues one after the other, in block-sized chunks
     int classN[kShadeClasses], nChunks = 0, n = 0;
     for (int c = 0; c < kShadeClasses; ++c) {
         classN[c] = A.counters[kClassCounter0 + c];
         nChunks += (classN[c] + (int)blockDim.x - 1) / (int)blockDim.x;
         n += classN[c];
     }
-    const float *betaCur = A.beta[betaIn];
-    float *betaNext = A.beta[betaIn ^ 1];
-    const int lane = threadIdx.x & 31;
-    Recipe *wr = recipes + (threadIdx.x & ~31);
-    Recipe &rc = recipes[threadIdx.x];
     const int noSpec = BSDF_ALL & ~BSDF_SPECULAR;
 #ifdef SPTX_STAGE_CLOCKS
     long long stageClk[24] = {0};
@@ -181,20 +103,16 @@ k_shade(DScene S, DSampler H, PathArrays A, RenderParams R, int qi, int betaIn,
         const int k = first * (int)blockDim.x + (int)threadIdx.x;
         bool alive = k < classN[cls];
         int i = 0;
-        rc.path = -1;
-        rc.work = 0;
         SampleStream st{0, 0};
         int bounces = 0, neeFlags = 0, lightNum = 0;
         float lightPdfSel = 0.f, etaScale = 1.f, rayWeight = 0.f;
         Isect it;
         Bsdf bs;
+        FSum f;
         Ray ray{mk(0, 0, 0), mk(0, 0, 1), kInf};
         // ---- stage 0: interaction, emission (path.cpp:91-112) ----
         if (alive) {
             i = queue[k];
-            rc.path = i;
-            // the bin passes read this path's throughput row much later: have it in L2 by then
-            asm volatile("prefetch.global.L2 [%0];" ::"l"(betaCur + (size_t)i * SPTX_SPECTRUM_STRIDE));
             const float4 ra = A.rayA[i], rb = A.rayB[i];
             const float4 ha = A.hitA[i], hb = A.hitB[i];
             ray.o = mk(ra.x, ra.y, ra.z);
@@ -216,8 +134,16 @@ k_shade(DScene S, DSampler H, PathArrays A, RenderParams R, int qi, int betaIn,
             if ((bounces == 0 || specularBounce) && haveIsect && it.light >= 0) {
                 const sptx_light &Lt = S.lights[it.light];
                 if (Lt.two_sided || dot(it.n, -ray.d) > 0) {
-                    rc.work = W_EMIT;
-                    rc.emitRow = Lt.spectrum;
+                    const Row4 Lr = row4(A.L, i), br = row4(A.beta[betaIn], i);
+                    for (int c = 0; c < 8; ++c) {
+                        float4 l = Lr.ld(c);
+                        const float4 b = br.ld(c), e = spec4(S, Lt.spectrum, c);
+                        l.x += b.x * e.x;
+                        l.y += b.y * e.y;
+                        l.z += b.z * e.z;
+                        l.w += b.w * e.w;
+                        Lr.st(c, l);
+                    }
                 }
             }
             alive = haveIsect && bounces < R.maxDepth;
@@ -239,7 +165,7 @@ k_shade(DScene S, DSampler H, PathArrays A, RenderParams R, int qi, int betaIn,
         }
         SPTX_STAGE(2);
         // ---- stage 2: light sampling strategy (integrator.cpp:119-163) ----
-        bool delta = false, wantShadow = false, wantMis = false;
+        bool delta = false;
         V3 shO = mk(0, 0, 0), shD = mk(0, 0, 0), misO = mk(0, 0, 0), misD = mk(0, 0, 0);
         LiSample ls;
         ls.pdf = 0.f;
@@ -251,39 +177,54 @@ k_shade(DScene S, DSampler H, PathArrays A, RenderParams R, int qi, int betaIn,
             ls = light_sample_li(S, Lt, ref, uLight);
         }
         SPTX_STAGE(4);
-        // (Li.IsBlack() is decided per bin by the pass: Recipe::black)
         if (nee && ls.pdf > 0 && !ls.black) {
-            bsdf_f(S, bs, it.wo, ls.wi, noSpec, &rc.f);
-            rc.ad = absdot(ls.wi, it.ns);
+            bsdf_f(S, bs, it.wo, ls.wi, noSpec, &f);
+            const float ad = absdot(ls.wi, it.ns);
             const float scatteringPdf = bsdf_pdf(S, bs, it.wo, ls.wi, noSpec);
-            rc.weight = delta ? 1.f : power_heuristic(ls.pdf, scatteringPdf);
-            rc.pdf = ls.pdf;
-            rc.row = ls.spectrum;
-            rc.rowDiv = ls.divisor;
-            rc.work |= W_FA | (delta ? W_FA_DELTA : 0);
-            // VisibilityTester(ref, pShape) -> SpawnRayTo(Interaction)
-            shO = offset_ray_origin(it.p, it.pError, it.n, ls.lp.p - it.p);
-            V3 target = offset_ray_origin(ls.lp.p, ls.lp.pError, ls.lp.n, shO - ls.lp.p);
-            shD = target - shO;
-            wantShadow = true;
+            const float weight = delta ? 1.f : power_heuristic(ls.pdf, scatteringPdf);
+            const Row4 fa = row4(A.fa, i);
+            bool fNon = false, liNon = false;
+            for (int c = 0; c < 8; ++c) {
+                float4 fv = fsum4(S, f, c), li = spec4(S, ls.spectrum, c);
+                if (ls.divisor != 0.f) {
+                    li.x = li.x / ls.divisor;
+                    li.y = li.y / ls.divisor;
+                    li.z = li.z / ls.divisor;
+                    li.w = li.w / ls.divisor;
+                }
+                fv.x *= ad;
+                fv.y *= ad;
+                fv.z *= ad;
+                fv.w *= ad;
+                float4 o = make_float4(fv.x * li.x, fv.y * li.y, fv.z * li.z, fv.w * li.w);
+                if (!delta) {
+                    o.x = o.x * weight;
+                    o.y = o.y * weight;
+                    o.z = o.z * weight;
+                    o.w = o.w * weight;
+                }
+                fa.st(c, make_float4(o.x / ls.pdf, o.y / ls.pdf, o.z / ls.pdf, o.w / ls.pdf));
+                fNon |= any_nonzero4(fv, c);
+                liNon |= any_nonzero4(li, c);
+            }
+            if (fNon && liNon) {
+                // VisibilityTester(ref, pShape) -> SpawnRayTo(Interaction)
+                shO = offset_ray_origin(it.p, it.pError, it.n, ls.lp.p - it.p);
+                V3 target = offset_ray_origin(ls.lp.p, ls.lp.pError, ls.lp.n, shO - ls.lp.p);
+                shD = target - shO;
+                neeFlags |= NEE_HAS_SHADOW;
+            }
         }
         SPTX_STAGE(6);
-        bin_pass(S, A, wr, lane, betaCur, betaNext);
-        __syncwarp();
-        if (wantShadow && !rc.black) neeFlags |= NEE_HAS_SHADOW;
-        rc.work = 0;
-        SPTX_STAGE(8);
         // ---- stage 3: BSDF sampling strategy (integrator.cpp:166-213) ----
         if (nee && !delta) {
             float sPdf;
             int sType;
-            bsdf_sample_f(S, bs, it.wo, uScattering, noSpec, &misD, &sPdf, &sType, &rc.f);
-            if (rc.f.n > 0 && sPdf > 0) {
+            bsdf_sample_f(S, bs, it.wo, uScattering, noSpec, &misD, &sPdf, &sType, &f);
+            if (f.n > 0 && sPdf > 0) {
                 float weight = 1.f;
                 bool skip = false;
                 if (!(sType & BSDF_SPECULAR)) {
-                    // (evaluated before the blackness of f is known: no side effects, and
-                    //  a black f contributes nothing either way)
                     RefPoint ref{it.p, it.pError, it.n};
                     float lightPdf = light_pdf_li(S, S.lights[lightNum], ref, misD);
                     if (lightPdf == 0)
@@ -292,87 +233,97 @@ k_shade(DScene S, DSampler H, PathArrays A, RenderParams R, int qi, int betaIn,
                         weight = power_heuristic(sPdf, lightPdf);
                 }
                 if (!skip) {
-                    rc.ad = absdot(misD, it.ns);
-                    rc.weight = weight;
-                    rc.pdf = sPdf;
-                    rc.row = S.lights[lightNum].spectrum;
-                    rc.work = W_FB;
-                    misO = offset_ray_origin(it.p, it.pError, it.n, misD);
-                    wantMis = true;
+                    const float ad = absdot(misD, it.ns);
+                    const int leRow = S.lights[lightNum].spectrum;
+                    const Row4 fb = row4(A.fb, i);
+                    bool fNon = false;
+                    for (int c = 0; c < 8; ++c) {
+                        float4 fv = fsum4(S, f, c);
+                        const float4 le = spec4(S, leRow, c);
+                        fv.x *= ad;
+                        fv.y *= ad;
+                        fv.z *= ad;
+                        fv.w *= ad;
+                        fb.st(c, make_float4(fv.x * le.x * weight / sPdf, fv.y * le.y * weight / sPdf,
+                                             fv.z * le.z * weight / sPdf, fv.w * le.w * weight / sPdf));
+                        fNon |= any_nonzero4(fv, c);
+                    }
+                    if (fNon) {
+                        misO = offset_ray_origin(it.p, it.pError, it.n, misD);
+                        neeFlags |= NEE_HAS_MIS;
+                    }
                 }
             }
         }
-        SPTX_STAGE(10);
-        bin_pass(S, A, wr, lane, betaCur, betaNext);
-        __syncwarp();
-        if (wantMis && !rc.black) neeFlags |= NEE_HAS_MIS;
-        rc.work = 0;
         if (neeFlags) {
             A.shA[i] = make_float4(shO.x, shO.y, shO.z, shD.x);
             A.shB[i] = make_float4(shD.y, shD.z, 1.f - kShadowEpsilon, lightPdfSel);
             A.misA[i] = make_float4(misO.x, misO.y, misO.z, misD.x);
             A.misB[i] = make_float4(misD.y, misD.z, __int_as_float(lightNum), __int_as_float(neeFlags));
         }
-        SPTX_STAGE(12);
+        SPTX_STAGE(8);
         // ---- stage 4: BSDF sample for the next path segment (path.cpp:131-150) ----
-        V3 nextO = mk(0, 0, 0), nextD = mk(0, 0, 0);
-        int flagsC = 0;
         if (alive) {
+            V3 wi;
             float pdf;
-            bsdf_sample_f(S, bs, it.wo, get2d(H, st), BSDF_ALL, &nextD, &pdf, &flagsC, &rc.f);
-            if (rc.f.n > 0 && pdf != 0.f) {
-                rc.ad = absdot(nextD, it.ns);
-                rc.pdf = pdf;
-                if ((flagsC & BSDF_SPECULAR) && (flagsC & BSDF_TRANSMISSION)) {
+            int flags;
+            bsdf_sample_f(S, bs, it.wo, get2d(H, st), BSDF_ALL, &wi, &pdf, &flags, &f);
+            bool fNon = false;
+            float maxBeta = 0.f;
+            const Row4 bIn = row4(A.beta[betaIn], i), bOut = row4(A.beta[betaIn ^ 1], i);
+            if (f.n > 0 && pdf != 0.f) {
+                if ((flags & BSDF_SPECULAR) && (flags & BSDF_TRANSMISSION)) {
                     float eta = bs.eta;
                     etaScale *= (dot(it.wo, it.n) > 0) ? (eta * eta) : 1.f / (eta * eta);
                 }
-                rc.etaScale = etaScale;
-                rc.work = W_FC;
-                nextO = offset_ray_origin(it.p, it.pError, it.n, nextD);
-            } else
+                const float ad = absdot(wi, it.ns);
+                for (int c = 0; c < 8; ++c) {
+                    const float4 fv = fsum4(S, f, c), b = bIn.ld(c);
+                    const float4 nb = make_float4(b.x * (fv.x * ad / pdf), b.y * (fv.y * ad / pdf),
+                                                  b.z * (fv.z * ad / pdf), b.w * (fv.w * ad / pdf));
+                    bOut.st(c, nb);
+                    fNon |= any_nonzero4(fv, c);
+                    // MaxComponentValue(beta * etaScale), std::max order (path.cpp:176-177)
+                    const float v0 = nb.x * etaScale, v1 = nb.y * etaScale, v2 = nb.z * etaScale,
+                                v3 = nb.w * etaScale;
+                    maxBeta = (c == 0) ? v0 : ((maxBeta < v0) ? v0 : maxBeta);
+                    maxBeta = (maxBeta < v1) ? v1 : maxBeta;
+                    maxBeta = (maxBeta < v2) ? v2 : maxBeta;
+                    if (c < 7) maxBeta = (maxBeta < v3) ? v3 : maxBeta;
+                }
+            }
+            if (!fNon || pdf == 0.f)
                 alive = false;
-        }
-        SPTX_STAGE(14);
-        bin_pass(S, A, wr, lane, betaCur, betaNext);
-        __syncwarp();
-        // ---- epilogue: Russian roulette (path.cpp:176-184), next ray ----
-        rc.rrDiv = 0.f;
-        if (alive && rc.black) alive = false;  // f.IsBlack() (path.cpp:137)
-        if (alive) {
-            const float maxBeta = rc.maxBeta;
-            if (maxBeta < R.rrThreshold && bounces > 3) {
-                float q = fmaxf(.05f, 1.f - maxBeta);
-                if (get1d(H, st) < q)
-                    alive = false;
-                else
-                    rc.rrDiv = 1.f - q;
+            else {
+                // Russian roulette (path.cpp:176-184)
+                if (maxBeta < R.rrThreshold && bounces > 3) {
+                    float q = fmaxf(.05f, 1.f - maxBeta);
+                    if (get1d(H, st) < q)
+                        alive = false;
+                    else {
+                        const float inv = 1.f - q;
+                        for (int c = 0; c < 8; ++c) {
+                            float4 b = bOut.ld(c);
+                            bOut.st(c, make_float4(b.x / inv, b.y / inv, b.z / inv, b.w / inv));
+                        }
+                    }
+                }
+                if (alive) {
+                    V3 o = offset_ray_origin(it.p, it.pError, it.n, wi);
+                    A.rayA[i] = make_float4(o.x, o.y, o.z, wi.x);
+                    A.rayB[i] = make_float4(wi.y, wi.z, etaScale, rayWeight);
+                    if (st.dim >= H.s.n_dims) atomicOr(A.counters + 3, ERR_DIM_OVERFLOW);
+                    A.info[i] = pack_info(bounces + 1, (flags & BSDF_SPECULAR) ? 1 : 0, st.dim);
+                }
             }
         }
-        if (alive) {
-            A.rayA[i] = make_float4(nextO.x, nextO.y, nextO.z, nextD.x);
-            A.rayB[i] = make_float4(nextD.y, nextD.z, etaScale, rayWeight);
-            if (st.dim >= H.s.n_dims) atomicOr(A.counters + 3, ERR_DIM_OVERFLOW);
-            A.info[i] = pack_info(bounces + 1, (flagsC & BSDF_SPECULAR) ? 1 : 0, st.dim);
-        }
-        // beta /= 1 - q for the survivors of the roulette (only when bounces > 3)
-        const unsigned needDiv = __ballot_sync(0xffffffffu, rc.path >= 0 && rc.rrDiv != 0.f);
-        if (needDiv) {
-            __syncwarp();
-            for (unsigned m = needDiv; m; m &= m - 1) {
-                const Recipe &r = wr[__ffs(m) - 1];
-                const size_t at = (size_t)r.path * SPTX_SPECTRUM_STRIDE + lane;
-                betaNext[at] = betaNext[at] / r.rrDiv;
-            }
-        }
-        __syncwarp();
         queue_push(A.qNee, A.counters + 2, i, neeFlags != 0);
         queue_push(A.qMis, A.counters + 4, i, (neeFlags & NEE_HAS_MIS) != 0);
         queue_push(A.q[qi ^ 1], A.counters + (qi ^ 1), i, alive);
-        SPTX_TICK(16);
+        SPTX_TICK(10);
     }
 #ifdef SPTX_STAGE_CLOCKS
-    if (lane == 0)
+    if ((threadIdx.x & 31) == 0)
         for (int c = 0; c < 24; ++c) atomicAdd(&g_stageClocks[c], (unsigned long long)stageClk[c]);
 #endif
     if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&cnt->vertices, (unsigned long long)n);

@@ -141,10 +141,6 @@ extern "C" int sptx_create(int device, sptx_ctx **out) {
     ctx->smCount = prop.multiProcessorCount;
     if ((e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess)
         return bail(e, "cudaStreamCreate");
-    // k_shade keeps one recipe per thread in shared memory (more than 48 KB per block)
-    if ((e = cudaFuncSetAttribute(k_shade, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  (int)(kShadeBlock * sizeof(Recipe)))) != cudaSuccess)
-        return bail(e, "cudaFuncSetAttribute(k_shade)");
     cudaEventCreate(&ctx->ev0);
     cudaEventCreate(&ctx->ev1);
     cudaEventCreate(&ctx->ev2);
@@ -623,9 +619,9 @@ static int render_pixels(sptx_ctx *ctx, const std::vector<int2> &pixels, int s0,
             R.sampleList = dSampleList;
             const int64_t nPaths = (int64_t)nPix * R.samplesInPass;
             const int g = grid_for(ctx, nPaths);
-            // one resident 512-thread block per SM (128 registers per thread)
-            const int gShade = (int)std::min<int64_t>((nPaths + kShadeBlock - 1) / kShadeBlock,
-                                                     (int64_t)ctx->smCount * kShadeBlocksPerSM);
+            // one resident block per SM; chunks = class queues in block-sized pieces
+            const int gShade = (int)std::min<int64_t>((nPaths + kShadeBlock - 1) / kShadeBlock + kShadeClasses,
+                                                     (int64_t)ctx->smCount);
             k_set_counters<<<1, 1, 0, ctx->stream>>>(A.counters, 0, 0, 1, 0);
             ++launches;
             tic(0);
@@ -642,7 +638,7 @@ static int render_pixels(sptx_ctx *ctx, const std::vector<int2> &pixels, int s0,
                     k_intersect<false><<<g, kBlock, 0, ctx->stream>>>(ctx->S, A, qi, ctx->dCnt);
                 toc();
                 tic(2);
-                k_shade<<<gShade, kShadeBlock, kShadeBlock * sizeof(Recipe), ctx->stream>>>(ctx->S, ctx->H, A, R, qi, betaIn, ctx->dCnt);
+                k_shade<<<gShade, kShadeBlock, 0, ctx->stream>>>(ctx->S, ctx->H, A, R, qi, betaIn, ctx->dCnt);
                 toc();
                 if (bounce < maxDepth) {
                     tic(3);
