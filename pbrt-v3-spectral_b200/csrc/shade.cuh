@@ -72,16 +72,21 @@ __device__ unsigned long long g_stageClocks[32];
 #else
 #define SPTX_TICK(slot)
 #endif
-#define SPTX_STAGE(slot)     \
-    do {                     \
-        SPTX_TICK(slot);     \
-        __syncthreads();     \
-        SPTX_TICK(slot + 1); \
+#ifndef SPTX_STAGE_MASK
+#define SPTX_STAGE_MASK 0x11
+#endif
+#define SPTX_STAGE(slot)                                       \
+    do {                                                       \
+        SPTX_TICK(slot);                                       \
+        if ((SPTX_STAGE_MASK >> (slot)) & 1) __syncthreads();  \
+        SPTX_TICK(slot + 1);                                   \
     } while (0)
 
 __global__ void __launch_bounds__(kShadeBlock, 1)
-k_shade(DScene S, DSampler H, PathArrays A, RenderParams R, int qi, int betaIn,
-        DeviceCounters *cnt) {
+k_shade(const DScene *__restrict__ Sp, const DSampler *__restrict__ Hp, PathArrays A, RenderParams R,
+        int qi, int betaIn, DeviceCounters *cnt) {
+    const DScene &S = *Sp;
+    const DSampler &H = *Hp;
     int classN[kShadeClasses], nChunks = 0, n = 0;
     for (int c = 0; c < kShadeClasses; ++c) {
         classN[c] = A.counters[kClassCounter0 + c];

@@ -27,6 +27,10 @@ struct sptx_ctx {
     DScene S;
     DCamera C;
     DSampler H;
+    // device copies of S and H: the large kernels take pointers, so that handing the
+    // descriptors to non-inlined device functions does not copy them to each thread's stack
+    DScene *dS = nullptr;
+    DSampler *dH = nullptr;
     DFilm F;
     PathArrays A;
     sptx_integrator integ;
@@ -162,6 +166,8 @@ extern "C" void sptx_destroy(sptx_ctx *ctx) {
     free_pool(ctx->sceneAllocs);
     free_pool(ctx->pathAllocs);
     if (ctx->dCnt) cudaFree(ctx->dCnt);
+    if (ctx->dS) cudaFree(ctx->dS);
+    if (ctx->dH) cudaFree(ctx->dH);
     cudaEventDestroy(ctx->ev0);
     cudaEventDestroy(ctx->ev1);
     cudaEventDestroy(ctx->ev2);
@@ -500,6 +506,12 @@ extern "C" int sptx_upload_scene(sptx_ctx *ctx, const sptx_scene_desc *sc) {
     if ((rc = dalloc(ctx, pool, (int64_t)F.width * F.height * SPTX_SPECTRUM_STRIDE, &F.pixels))) return rc;
     CK(cudaMemsetAsync(F.pixels, 0, (size_t)std::max<int64_t>(1, (int64_t)F.width * F.height) *
                                         SPTX_SPECTRUM_STRIDE * sizeof(float), ctx->stream));
+    if (!ctx->dS) {
+        CK(cudaMalloc(&ctx->dS, sizeof(DScene)));
+        CK(cudaMalloc(&ctx->dH, sizeof(DSampler)));
+    }
+    CK(cudaMemcpyAsync(ctx->dS, &ctx->S, sizeof(DScene), cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(ctx->dH, &ctx->H, sizeof(DSampler), cudaMemcpyHostToDevice, ctx->stream));
     CK(cudaGetLastError());
     CK(cudaStreamSynchronize(ctx->stream));
     ctx->haveScene = true;
@@ -638,7 +650,7 @@ static int render_pixels(sptx_ctx *ctx, const std::vector<int2> &pixels, int s0,
                     k_intersect<false><<<g, kBlock, 0, ctx->stream>>>(ctx->S, A, qi, ctx->dCnt);
                 toc();
                 tic(2);
-                k_shade<<<gShade, kShadeBlock, 0, ctx->stream>>>(ctx->S, ctx->H, A, R, qi, betaIn, ctx->dCnt);
+                k_shade<<<gShade, kShadeBlock, 0, ctx->stream>>>(ctx->dS, ctx->dH, A, R, qi, betaIn, ctx->dCnt);
                 toc();
                 if (bounce < maxDepth) {
                     tic(3);
