@@ -134,6 +134,7 @@ class CudaArray:
 def bench_ours(args):
     import torch
     capi = importlib.import_module("pbrt-v3-spectral_b200.capi")
+    part = importlib.import_module("pbrt-v3-spectral_b200.partition")
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -156,8 +157,7 @@ def bench_ours(args):
 
     def step_range(k):
         # consecutive sample numbers; with N ranks, rank r takes the r-th block of each step
-        s0 = ((k * world + rank) * SPP_STEP) % max(SPP_TOTAL * world, SPP_STEP)
-        return s0, s0 + SPP_STEP
+        return part.sample_block(k, rank, world, SPP_STEP, SPP_TOTAL)
 
     for k in range(W):
         ctx.render(*step_range(k))
@@ -178,7 +178,7 @@ def bench_ours(args):
     reduce_ms = 0.0
     if dist:
         ev0.record()
-        dist.reduce(film, dst=0, op=dist.ReduceOp.SUM)
+        part.reduce_film(film, dist, dst=0)
         ev1.record()
         torch.cuda.synchronize()
         reduce_ms = ev0.elapsed_time(ev1)

@@ -1,0 +1,54 @@
+"""Multi-GPU host logic: how a render is split across ranks and how the films meet again.
+
+The reference splits the image into 16x16 tiles over threads and merges them with
+Film::MergeFilmTile (src/core/integrator.cpp:235-249, src/core/film.cpp:124-142).  Across GPUs
+the natural split is by Halton sample number instead: every sample of a pixel is independent
+(HaltonSampler::GetIndexForSample is a pure function of the sample number,
+src/samplers/halton.cpp:96-115), the scene is replicated, and each rank renders ALL pixels for
+its own block of sample numbers.  The only exchange step is the sum of the per-rank films.
+
+No CUDA in this file: it is exercised on CPU with the gloo backend (tests/test_cpu.py) and used
+with NCCL device tensors by bench.py.
+"""
+
+
+def sample_block(step, rank, world, spp_step, spp_total=None):
+    """Half-open range of sample numbers rank `rank` renders in step `step`.
+
+    Step k covers the `world * spp_step` consecutive sample numbers starting at
+    k * world * spp_step; rank r takes the r-th block of spp_step.  With spp_total given the
+    numbering wraps (benchmark loops longer than one render reuse sample numbers).
+    """
+    if not (0 <= rank < world):
+        raise ValueError("rank %d outside world of %d" % (rank, world))
+    if spp_step <= 0:
+        raise ValueError("spp_step must be positive")
+    s0 = (step * world + rank) * spp_step
+    if spp_total is not None:
+        s0 %= max(spp_total * world, spp_step)
+    return s0, s0 + spp_step
+
+
+def split_samples(spp, world):
+    """Partition sample numbers [0, spp) into `world` contiguous blocks (sizes differ by <= 1)."""
+    if world <= 0:
+        raise ValueError("world must be positive")
+    base, extra = divmod(spp, world)
+    out, s = [], 0
+    for r in range(world):
+        n = base + (1 if r < extra else 0)
+        out.append((s, s + n))
+        s += n
+    return out
+
+
+def reduce_film(film, dist=None, dst=0):
+    """Sum the per-rank films onto rank `dst` (in place), the multi-GPU MergeFilmTile.
+
+    `film` is a torch tensor viewing [H][W][32] float32 (31 bins of contribSum + filterWeightSum);
+    both parts are plain sums, so one SUM reduce merges them.  With dist None (single process)
+    this is a no-op.  Returns the tensor.
+    """
+    if dist is not None and dist.is_initialized() and dist.get_world_size() > 1:
+        dist.reduce(film, dst=dst, op=dist.ReduceOp.SUM)
+    return film
