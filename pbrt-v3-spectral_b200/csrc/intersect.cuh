@@ -368,7 +368,10 @@ __device__ bool traverse_bvh(const DScene &S, int bvhIndex, Ray &ray, HitRec *hi
             }
         }
         if (leafN > 0) {
-            for (int i = 0; i < leafN; ++i) {
+            // (any-hit leaves through the flags, not a return: the loops stay structured and
+            //  the warp keeps reconverging after the node phase)
+            bool stop = false;
+            for (int i = 0; i < leafN && !stop; ++i) {
                 int gp = B.prim_base + leafOffset + i;
                 const float4 *lv = S.leafv + 3 * (size_t)gp;
                 float4 v0 = __ldg(lv), v1 = __ldg(lv + 1), v2 = __ldg(lv + 2);
@@ -380,19 +383,24 @@ __device__ bool traverse_bvh(const DScene &S, int bvhIndex, Ray &ray, HitRec *hi
                     Ray r2 = xf_ray(I.w2p, ray);
                     HitRec h2 = *hit;
                     if (traverse_bvh<ANY, COUNT, 1>(S, I.bvh, r2, &h2, cnt)) {
-                        if (ANY) return true;
-                        ray.tMax = r2.tMax;
-                        *hit = h2;
-                        hit->inst = shape;
                         found = true;
+                        if (ANY)
+                            stop = true;
+                        else {
+                            ray.tMax = r2.tMax;
+                            *hit = h2;
+                            hit->inst = shape;
+                        }
                     }
                 } else if (prim_test<ANY>(S, gp, ray, hit, kind, shape, v0, v1, v2)) {
-                    if (ANY) return true;
-                    if (LEVEL == 0) hit->inst = -1;
                     found = true;
+                    if (ANY)
+                        stop = true;
+                    else if (LEVEL == 0)
+                        hit->inst = -1;
                 }
             }
-            if (sp == 0)
+            if (stop || sp == 0)
                 done = true;
             else
                 cur = stack[--sp];
