@@ -161,7 +161,7 @@ k_film(DScene S, DFilm F, PathArrays A, RenderParams R) {
         unsigned long long tot = 0;
         for (int c = 0; c < 24; ++c) tot += g_stageClocks[c];
         for (int c = 0; c < 17; ++c) {
-            printf("stage slot %2d: %5.1f%%\n", c, 100.0 * (double)g_stageClocks[c] / (double)tot);
+            printf("S%02d %5.1f%%  ", c, 100.0 * (double)g_stageClocks[c] / (double)tot);
             g_stageClocks[c] = 0;
         }
     }

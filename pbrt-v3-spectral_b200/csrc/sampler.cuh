@@ -133,6 +133,66 @@ SPTX_NOINL float halton_sample(const DSampler &H, uint64_t index, int dim) {
                                      (uint32_t)__ldg(H.primes + d));
 }
 
+// N consecutive scrambled dimensions of one index at once.  The digit loops are serial
+// chains (multiply-high, permutation lookup, multiply-add); interleaving the chains of the
+// dimensions a vertex consumes together overlaps their latencies.  Same integer digits and the
+// same float operations per dimension as scrambled_radical_inverse; the reversed digits stay in
+// 32 bits, which holds while index * base < 2^32 (checked, else the scalar path).
+template <int N>
+SPTX_DEV void halton_n(const DSampler &H, uint64_t index, int dim, float *out) {
+    bool fast = dim >= 2 && dim + N <= H.s.n_dims && (index >> 32) == 0;
+    uint4 tab[N];
+    if (fast) {
+#pragma unroll
+        for (int j = 0; j < N; ++j) {
+            tab[j] = __ldg(H.dim_tab + dim + j);
+            if ((uint32_t)index > tab[j].y) fast = false;  // index * base would leave 32 bits
+        }
+    }
+    if (!fast) {
+#pragma unroll
+        for (int j = 0; j < N; ++j) out[j] = halton_sample(H, index, dim + j);
+        return;
+    }
+    uint32_t a[N], rev[N];
+    float invN[N];
+#pragma unroll
+    for (int j = 0; j < N; ++j) {
+        a[j] = (uint32_t)index;
+        rev[j] = 0;
+        invN[j] = 1.f;
+    }
+    bool more = (uint32_t)index != 0;
+    while (more) {
+        more = false;
+#pragma unroll
+        for (int j = 0; j < N; ++j) {
+            if (a[j]) {
+                const uint32_t base = tab[j].x;
+                uint32_t next = __umulhi(a[j], tab[j].y);
+                uint32_t digit = a[j] - next * base;
+                if (digit >= base) {
+                    ++next;
+                    digit -= base;
+                }
+                if (digit >= base) {
+                    ++next;
+                    digit -= base;
+                }
+                rev[j] = rev[j] * base + __ldg(H.perms + tab[j].z + digit);
+                invN[j] *= __uint_as_float(tab[j].w);
+                a[j] = next;
+                more |= next != 0;
+            }
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < N; ++j) {
+        float r = invN[j] * ((float)rev[j] + __ldg(H.dim_tail + dim + j));
+        out[j] = (kOneMinusEpsilon < r) ? kOneMinusEpsilon : r;
+    }
+}
+
 // Per-path view of the sampler: GlobalSampler::Get1D/Get2D with no array
 // requests (core/sampler.cpp:180-195): dimensions are consumed sequentially.
 struct SampleStream {
@@ -141,11 +201,10 @@ struct SampleStream {
 };
 SPTX_DEV float get1d(const DSampler &H, SampleStream &st) { return halton_sample(H, st.index, st.dim++); }
 SPTX_DEV V2 get2d(const DSampler &H, SampleStream &st) {
-    V2 p;
-    p.x = halton_sample(H, st.index, st.dim);
-    p.y = halton_sample(H, st.index, st.dim + 1);
+    float v[2];
+    halton_n<2>(H, st.index, st.dim, v);
     st.dim += 2;
-    return p;
+    return V2{v[0], v[1]};
 }
 
 }  // namespace sptx

@@ -57,6 +57,10 @@ struct DSampler {
     const int32_t *primes;
     const int32_t *prime_sums;
     const uint16_t *perms;
+    // per dimension: {base, floor((2^32-1)/base), offset into perms, bits(1.f / base)} and the
+    // constant tail invBase * perm[0] / (1 - invBase) of ScrambledRadicalInverse
+    const uint4 *dim_tab;
+    const float *dim_tail;
     const uint64_t *pixel_offset;  // per pixel of sample_bounds (Halton)
     int sb[4];                     // sample bounds x0,y0,x1,y1
 };

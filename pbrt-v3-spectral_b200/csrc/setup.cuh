@@ -101,6 +101,18 @@ __global__ void k_voxel_tables(DScene S, const float *halton5, float *tables) {
 }
 
 // Test hooks ---------------------------------------------------------------------
+// Per-dimension constants of the scrambled radical inverse (core/lowdiscrepancy.cpp:405-424),
+// computed with the device's own float operations.
+__global__ void k_halton_dims(const int32_t *primes, const int32_t *prime_sums, const uint16_t *perms,
+                              int n, uint4 *tab, float *tail) {
+    int d = blockIdx.x * blockDim.x + threadIdx.x;
+    if (d >= n) return;
+    const uint32_t base = (uint32_t)primes[d];
+    const float invBase = 1.f / (float)base;
+    tab[d] = make_uint4(base, 0xffffffffu / base, (uint32_t)prime_sums[d], __float_as_uint(invBase));
+    tail[d] = invBase * (float)(int)perms[prime_sums[d]] / (1.f - invBase);
+}
+
 __global__ void k_sampler_eval(DSampler H, const int *px, const int *py, const int *sample,
                                const int *dim, int64_t n, float *out) {
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;

@@ -160,10 +160,16 @@ k_shade(const DScene *__restrict__ Sp, const DSampler *__restrict__ Hp, PathArra
         if (alive) {
             bsdf_init(S, it, &bs);
             if (bsdf_num_components(S, bs, noSpec) > 0 && S.n_lights > 0) {
-                lightNum = select_light(S, it.p, get1d(H, st), &lightPdfSel);
+                // the five values next-event estimation consumes (Get1D, Get2D, Get2D) are pure
+                // functions of (index, dimension): evaluated together, consumed as the reference does
+                float u5[5];
+                halton_n<5>(H, st.index, st.dim, u5);
+                st.dim += 1;
+                lightNum = select_light(S, it.p, u5[0], &lightPdfSel);
                 if (lightPdfSel != 0) {
-                    uLight = get2d(H, st);
-                    uScattering = get2d(H, st);
+                    uLight = V2{u5[1], u5[2]};
+                    uScattering = V2{u5[3], u5[4]};
+                    st.dim += 4;
                     nee = true;
                 }
             }
@@ -322,10 +328,11 @@ k_shade(const DScene *__restrict__ Sp, const DSampler *__restrict__ Hp, PathArra
                 }
             }
         }
+        SPTX_TICK(10);
         queue_push(A.qNee, A.counters + 2, i, neeFlags != 0);
         queue_push(A.qMis, A.counters + 4, i, (neeFlags & NEE_HAS_MIS) != 0);
         queue_push(A.q[qi ^ 1], A.counters + (qi ^ 1), i, alive);
-        SPTX_TICK(10);
+        SPTX_TICK(11);
     }
 #ifdef SPTX_STAGE_CLOCKS
     if ((threadIdx.x & 31) == 0)

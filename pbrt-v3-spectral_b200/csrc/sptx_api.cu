@@ -488,6 +488,18 @@ extern "C" int sptx_upload_scene(sptx_ctx *ctx, const sptx_scene_desc *sc) {
     if ((rc = upload(ctx, pool, sc->prime_sums, (int64_t)sc->sampler.n_dims, &H.prime_sums))) return rc;
     if ((rc = upload(ctx, pool, sc->perms, sc->n_perms, &H.perms))) return rc;
     {
+        const int nd = std::max(1, (int)sc->sampler.n_dims);
+        uint4 *tab;
+        float *tail;
+        if ((rc = dalloc(ctx, pool, (int64_t)nd, &tab))) return rc;
+        if ((rc = dalloc(ctx, pool, (int64_t)nd, &tail))) return rc;
+        if (sc->sampler.n_dims > 0)
+            k_halton_dims<<<(nd + 127) / 128, 128, 0, ctx->stream>>>(H.primes, H.prime_sums, H.perms,
+                                                                      (int)sc->sampler.n_dims, tab, tail);
+        H.dim_tab = tab;
+        H.dim_tail = tail;
+    }
+    {
         int w = std::max(0, H.sb[2] - H.sb[0]), h = std::max(0, H.sb[3] - H.sb[1]);
         uint64_t *off;
         if ((rc = dalloc(ctx, pool, (int64_t)w * h, &off))) return rc;
