@@ -12,7 +12,13 @@
 
 #define SPTX_DEV __device__ __forceinline__
 #define SPTX_HD __host__ __device__ __forceinline__
+// (was __noinline__ while the shade kernel thrashed the instruction cache; with staged,
+//  class-sorted warps inlining wins again: structs stay in registers instead of the stack)
+#ifdef SPTX_NO_INLINE
 #define SPTX_NOINL __device__ __noinline__
+#else
+#define SPTX_NOINL __device__ __forceinline__
+#endif
 
 namespace sptx {
 

@@ -59,8 +59,11 @@ SPTX_DEV bool any_nonzero4(float4 v, int c) {
 // same few KB of code, so that the instruction cache serves all of them from
 // one fetch (the kernel is ~200 KB of SASS and a warp walks most of it once per
 // vertex; free-running warps had a 53 % instruction-cache hit rate -- DESIGN.md 5).
-// One 1024-thread block per SM.
-constexpr int kShadeBlock = 1024;
+// One 512-thread block per SM (128 registers per thread).
+#ifndef SPTX_SHADE_BLOCK
+#define SPTX_SHADE_BLOCK 512
+#endif
+constexpr int kShadeBlock = SPTX_SHADE_BLOCK;
 #ifdef SPTX_STAGE_CLOCKS  // diagnosis build: per-stage warp clocks, printed by k_film
 __device__ unsigned long long g_stageClocks[32];
 #define SPTX_TICK(slot)                 \
