@@ -176,7 +176,14 @@ k_film(DScene S, DFilm F, PathArrays A, RenderParams R) {
         if (inFilm) {
             px = F.pixels + ((size_t)(pxy.y - F.f.cropped[1]) * F.width + (pxy.x - F.f.cropped[0])) *
                                 SPTX_SPECTRUM_STRIDE;
-            for (int b = 0; b <= SPTX_NBINS; ++b) acc[b] = px[b];
+#pragma unroll
+            for (int c = 0; c < SPTX_SPECTRUM_STRIDE / 4; ++c) {
+                const float4 v = reinterpret_cast<const float4 *>(px)[c];
+                acc[4 * c] = v.x;
+                acc[4 * c + 1] = v.y;
+                acc[4 * c + 2] = v.z;
+                acc[4 * c + 3] = v.w;
+            }
         }
         bool touched = false;
         for (int s = 0; s < R.samplesInPass; ++s) {
@@ -189,20 +196,52 @@ k_film(DScene S, DFilm F, PathArrays A, RenderParams R) {
                 A.spill[i] = 1;
                 continue;
             }
-            const float g = guard_scale(S, F, A, i);
+            // the sample's radiance row, moved once (8 x 128 bit) and kept in registers
+            float Lv[SPTX_SPECTRUM_STRIDE];
+            {
+                const float4 *Lp = reinterpret_cast<const float4 *>(A.L + i * SPTX_SPECTRUM_STRIDE);
+#pragma unroll
+                for (int c = 0; c < SPTX_SPECTRUM_STRIDE / 4; ++c) {
+                    const float4 v = Lp[c];
+                    Lv[4 * c] = v.x;
+                    Lv[4 * c + 1] = v.y;
+                    Lv[4 * c + 2] = v.z;
+                    Lv[4 * c + 3] = v.w;
+                }
+            }
+            // guard of SamplerIntegrator::Render (core/integrator.cpp:295-316), as guard_scale()
+            float g = 1.f;
+            {
+                float yy = 0.f;
+                bool nan = false;
+#pragma unroll
+                for (int b = 0; b < SPTX_NBINS; ++b) {
+                    if (isnan(Lv[b])) nan = true;
+                    yy += S.cie_y[b] * Lv[b];
+                }
+                const float y = y_finish(S, yy);
+                if (nan || isinf(y))
+                    g = 0.f;
+                else if (y > F.f.max_sample_luminance)
+                    g = F.f.max_sample_luminance / y;
+            }
             const float w = A.rayB[i].w;
             const float fw = filter_weight(F, pf, x0, y0);
-            const float *Lp = A.L + i * SPTX_SPECTRUM_STRIDE;
+#pragma unroll
             for (int b = 0; b < SPTX_NBINS; ++b) {
-                float v = Lp[b];
+                float v = Lv[b];
                 v = (g == 1.f) ? v : ((g == 0.f) ? 0.f : v * g);
                 acc[b] += v * w * fw;
             }
             acc[SPTX_NBINS] += fw;
             touched = true;
         }
-        if (touched)
-            for (int b = 0; b <= SPTX_NBINS; ++b) px[b] = acc[b];
+        if (touched) {
+#pragma unroll
+            for (int c = 0; c < SPTX_SPECTRUM_STRIDE / 4; ++c)
+                reinterpret_cast<float4 *>(px)[c] =
+                    make_float4(acc[4 * c], acc[4 * c + 1], acc[4 * c + 2], acc[4 * c + 3]);
+        }
     }
 }
 
