@@ -77,7 +77,7 @@ class ClockSampler:
              "clocks_event_reasons.sw_power_cap")
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={q}",
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms", "250"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._read, daemon=True)
             self.thread.start()
@@ -242,8 +242,13 @@ def bench_ours(args):
         if name in algo:
             per_launch_bytes = algo[name] / steps_counted / max(launches_per_step[name], 1)
             achieved = per_launch_bytes / (per_launch_ms * 1e-3) * 1e-9
+            traffic = None
+            tpath = os.path.join(ROOT, "profiles", f"k_{name}_traffic.json")
+            if os.path.exists(tpath):   # dram bytes per launch from the committed ncu --set full capture
+                traffic = json.load(open(tpath)).get("dram_bytes_per_launch")
             roof = {"bound": "hbm", "kernel": "k_" + name, "achieved": achieved, "peak": peak, "unit": "GB/s",
-                    "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                    "frac": achieved / peak, "traffic": traffic, "algorithmic_bytes_per_launch": per_launch_bytes,
+                    "peak_source": peak_src,
                     "avg_launch_ms": per_launch_ms,
                     "note": "algorithmic bytes per SURVEY.md 8(d); traversal working set is L2-resident for this scene"}
         kernels = {names[i]: {"ms_per_step": kms[i] / K, "launches_per_step": kcnt[i] / K,

@@ -31,6 +31,12 @@ struct sptx_ctx {
     // descriptors to non-inlined device functions does not copy them to each thread's stack
     DScene *dS = nullptr;
     DSampler *dH = nullptr;
+    // pinned staging for film downloads, and the device pixel list of the last render region
+    float *hFilm = nullptr;
+    size_t hFilmFloats = 0;
+    int2 *dPixels = nullptr;
+    int64_t dPixelsCap = 0;
+    std::vector<int2> pixelsKey;  // host copy of what dPixels holds
     DFilm F;
     PathArrays A;
     sptx_integrator integ;
@@ -167,6 +173,8 @@ extern "C" void sptx_destroy(sptx_ctx *ctx) {
     free_pool(ctx->pathAllocs);
     if (ctx->dCnt) cudaFree(ctx->dCnt);
     if (ctx->dS) cudaFree(ctx->dS);
+    if (ctx->hFilm) cudaFreeHost(ctx->hFilm);
+    if (ctx->dPixels) cudaFree(ctx->dPixels);
     if (ctx->dH) cudaFree(ctx->dH);
     cudaEventDestroy(ctx->ev0);
     cudaEventDestroy(ctx->ev1);
@@ -597,14 +605,23 @@ static int render_pixels(sptx_ctx *ctx, const std::vector<int2> &pixels, int s0,
     const int64_t chunkPix = dSampleList ? nPixAll : std::min<int64_t>(nPixAll, want);
     int S_pass = (int)std::max<int64_t>(1, std::min<int64_t>(s1 - s0, want / chunkPix));
     if ((rc = ensure_paths(ctx, chunkPix * S_pass))) return rc;
-    int2 *dPixels = nullptr;
-    CK(cudaMalloc((void **)&dPixels, (size_t)nPixAll * sizeof(int2)));
-    cudaError_t ce = cudaMemcpyAsync(dPixels, pixels.data(), (size_t)nPixAll * sizeof(int2),
-                                     cudaMemcpyHostToDevice, ctx->stream);
-    if (ce != cudaSuccess) {
-        cudaFree(dPixels);
-        return fail(ctx, SPTX_ECUDA, "pixel list upload: %s", cudaGetErrorString(ce));
+    // the device copy of the pixel list is kept between calls (same region, next samples)
+    if (ctx->pixelsKey.size() != pixels.size() ||
+        memcmp(ctx->pixelsKey.data(), pixels.data(), pixels.size() * sizeof(int2)) != 0) {
+        if (nPixAll > ctx->dPixelsCap) {
+            if (ctx->dPixels) cudaFree(ctx->dPixels);
+            ctx->dPixels = nullptr;
+            ctx->dPixelsCap = 0;
+            ctx->pixelsKey.clear();
+            CK(cudaMalloc((void **)&ctx->dPixels, (size_t)nPixAll * sizeof(int2)));
+            ctx->dPixelsCap = nPixAll;
+        }
+        CK(cudaMemcpyAsync(ctx->dPixels, pixels.data(), (size_t)nPixAll * sizeof(int2),
+                           cudaMemcpyHostToDevice, ctx->stream));
+        CK(cudaStreamSynchronize(ctx->stream));
+        ctx->pixelsKey = pixels;
     }
+    int2 *dPixels = ctx->dPixels;
     PathArrays &A = ctx->A;
     const int maxDepth = ctx->integ.max_depth;
     uint64_t launches = 0;
@@ -690,8 +707,7 @@ static int render_pixels(sptx_ctx *ctx, const std::vector<int2> &pixels, int s0,
         }
     }
     cudaEventRecord(ctx->ev1, ctx->stream);
-    ce = cudaStreamSynchronize(ctx->stream);
-    cudaFree(dPixels);
+    cudaError_t ce = cudaStreamSynchronize(ctx->stream);
     if (ce != cudaSuccess) return fail(ctx, SPTX_ECUDA, "render: %s", cudaGetErrorString(ce));
     CK(cudaGetLastError());
     float ms = 0.f;
@@ -801,12 +817,22 @@ extern "C" int sptx_film_download(sptx_ctx *ctx, float *contrib, float *weight) 
     if (!ctx->haveScene) return fail(ctx, SPTX_ESTATE, "sptx_film_download: no scene uploaded");
     CK(cudaSetDevice(ctx->device));
     const size_t nPix = (size_t)ctx->F.width * ctx->F.height;
-    std::vector<float> tmp(nPix * SPTX_SPECTRUM_STRIDE);
-    CK(cudaStreamSynchronize(ctx->stream));
-    if (nPix) CK(cudaMemcpy(tmp.data(), ctx->F.pixels, tmp.size() * sizeof(float), cudaMemcpyDeviceToHost));
+    const size_t nFloats = nPix * SPTX_SPECTRUM_STRIDE;
+    if (nFloats > ctx->hFilmFloats) {
+        if (ctx->hFilm) cudaFreeHost(ctx->hFilm);
+        ctx->hFilm = nullptr;
+        ctx->hFilmFloats = 0;
+        CK(cudaMallocHost((void **)&ctx->hFilm, nFloats * sizeof(float)));
+        ctx->hFilmFloats = nFloats;
+    }
+    const float *tmp = ctx->hFilm;
+    if (nPix) {
+        CK(cudaMemcpyAsync(ctx->hFilm, ctx->F.pixels, nFloats * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+        CK(cudaStreamSynchronize(ctx->stream));
+    }
     for (size_t p = 0; p < nPix; ++p) {
         if (contrib)
-            memcpy(contrib + p * SPTX_NBINS, tmp.data() + p * SPTX_SPECTRUM_STRIDE, SPTX_NBINS * sizeof(float));
+            memcpy(contrib + p * SPTX_NBINS, tmp + p * SPTX_SPECTRUM_STRIDE, SPTX_NBINS * sizeof(float));
         if (weight) weight[p] = tmp[p * SPTX_SPECTRUM_STRIDE + SPTX_NBINS];
     }
     return SPTX_OK;
