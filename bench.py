@@ -201,11 +201,12 @@ def bench_ours(args):
     torch.cuda.synchronize()
     if dist:
         dist.barrier()
+    host_film = (np.zeros((h, w, 31), np.float32), np.zeros((h, w), np.float32))  # caller-owned result
     t0 = time.perf_counter()
     for k in range(e2e_steps):
         ctx.upload(sf)                      # host arrays -> HBM (also a fresh, cleared film)
         ctx.render(*step_range(k))
-        contrib, weight = ctx.film_download(w, h)  # device film -> host
+        contrib, weight = ctx.film_download(w, h, out=host_film)  # device film -> host
     e2e_s = time.perf_counter() - t0
     if dist:
         t = torch.tensor([e2e_s], device=f"cuda:{local}", dtype=torch.float64)

@@ -185,9 +185,16 @@ class Context:
     def film_clear(self):
         self._ck(lib().sptx_film_clear(self.h), "sptx_film_clear")
 
-    def film_download(self, width, height):
-        contrib = np.zeros((height, width, NBINS), dtype=np.float32)
-        weight = np.zeros((height, width), dtype=np.float32)
+    def film_download(self, width, height, out=None):
+        """contribSum [H][W][31] and filterWeightSum [H][W]; `out` = (contrib, weight) reuses
+        caller buffers (float32, C-contiguous) instead of allocating."""
+        if out is not None:
+            contrib, weight = out
+            assert contrib.dtype == np.float32 and contrib.flags.c_contiguous and contrib.size == height * width * NBINS
+            assert weight.dtype == np.float32 and weight.flags.c_contiguous and weight.size == height * width
+        else:
+            contrib = np.empty((height, width, NBINS), dtype=np.float32)
+            weight = np.empty((height, width), dtype=np.float32)
         self._ck(lib().sptx_film_download(self.h, _ptr(contrib), _ptr(weight)), "sptx_film_download")
         return contrib, weight
 

@@ -113,6 +113,22 @@ __global__ void k_halton_dims(const int32_t *primes, const int32_t *prime_sums, 
     tail[d] = invBase * (float)(int)perms[prime_sums[d]] / (1.f - invBase);
 }
 
+// Film rows [P][32] -> contrib [P][31] followed by weight [P] (the layout sptx_film_download
+// hands to the host), so that the host copy is two plain transfers.
+__global__ void k_film_split(const float *pixels, int64_t nPix, float *out) {
+    const int64_t n = nPix * SPTX_SPECTRUM_STRIDE;
+    for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < n;
+         k += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t p = k / SPTX_SPECTRUM_STRIDE;
+        const int b = (int)(k % SPTX_SPECTRUM_STRIDE);
+        const float v = pixels[k];
+        if (b < SPTX_NBINS)
+            out[p * SPTX_NBINS + b] = v;
+        else
+            out[nPix * SPTX_NBINS + p] = v;
+    }
+}
+
 __global__ void k_sampler_eval(DSampler H, const int *px, const int *py, const int *sample,
                                const int *dim, int64_t n, float *out) {
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;

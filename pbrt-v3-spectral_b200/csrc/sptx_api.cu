@@ -32,8 +32,8 @@ struct sptx_ctx {
     DScene *dS = nullptr;
     DSampler *dH = nullptr;
     // pinned staging for film downloads, and the device pixel list of the last render region
-    float *hFilm = nullptr;
-    size_t hFilmFloats = 0;
+    float *dFilmSplit = nullptr;  // [P][31] contrib + [P] weight, the download layout
+    size_t dFilmSplitFloats = 0;
     int2 *dPixels = nullptr;
     int64_t dPixelsCap = 0;
     std::vector<int2> pixelsKey;  // host copy of what dPixels holds
@@ -173,7 +173,7 @@ extern "C" void sptx_destroy(sptx_ctx *ctx) {
     free_pool(ctx->pathAllocs);
     if (ctx->dCnt) cudaFree(ctx->dCnt);
     if (ctx->dS) cudaFree(ctx->dS);
-    if (ctx->hFilm) cudaFreeHost(ctx->hFilm);
+    if (ctx->dFilmSplit) cudaFree(ctx->dFilmSplit);
     if (ctx->dPixels) cudaFree(ctx->dPixels);
     if (ctx->dH) cudaFree(ctx->dH);
     cudaEventDestroy(ctx->ev0);
@@ -818,23 +818,23 @@ extern "C" int sptx_film_download(sptx_ctx *ctx, float *contrib, float *weight) 
     CK(cudaSetDevice(ctx->device));
     const size_t nPix = (size_t)ctx->F.width * ctx->F.height;
     const size_t nFloats = nPix * SPTX_SPECTRUM_STRIDE;
-    if (nFloats > ctx->hFilmFloats) {
-        if (ctx->hFilm) cudaFreeHost(ctx->hFilm);
-        ctx->hFilm = nullptr;
-        ctx->hFilmFloats = 0;
-        CK(cudaMallocHost((void **)&ctx->hFilm, nFloats * sizeof(float)));
-        ctx->hFilmFloats = nFloats;
+    if (nPix == 0) return SPTX_OK;
+    if (nFloats > ctx->dFilmSplitFloats) {
+        if (ctx->dFilmSplit) cudaFree(ctx->dFilmSplit);
+        ctx->dFilmSplit = nullptr;
+        ctx->dFilmSplitFloats = 0;
+        CK(cudaMalloc((void **)&ctx->dFilmSplit, nFloats * sizeof(float)));
+        ctx->dFilmSplitFloats = nFloats;
     }
-    const float *tmp = ctx->hFilm;
-    if (nPix) {
-        CK(cudaMemcpyAsync(ctx->hFilm, ctx->F.pixels, nFloats * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
-        CK(cudaStreamSynchronize(ctx->stream));
-    }
-    for (size_t p = 0; p < nPix; ++p) {
-        if (contrib)
-            memcpy(contrib + p * SPTX_NBINS, tmp + p * SPTX_SPECTRUM_STRIDE, SPTX_NBINS * sizeof(float));
-        if (weight) weight[p] = tmp[p * SPTX_SPECTRUM_STRIDE + SPTX_NBINS];
-    }
+    k_film_split<<<grid_for(ctx, (int64_t)nFloats), kBlock, 0, ctx->stream>>>(ctx->F.pixels, (int64_t)nPix,
+                                                                              ctx->dFilmSplit);
+    if (contrib)
+        CK(cudaMemcpyAsync(contrib, ctx->dFilmSplit, nPix * SPTX_NBINS * sizeof(float),
+                           cudaMemcpyDeviceToHost, ctx->stream));
+    if (weight)
+        CK(cudaMemcpyAsync(weight, ctx->dFilmSplit + nPix * SPTX_NBINS, nPix * sizeof(float),
+                           cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
     return SPTX_OK;
 }
 
