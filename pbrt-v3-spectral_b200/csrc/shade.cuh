@@ -133,6 +133,11 @@ k_shade(const DScene *__restrict__ Sp, const DSampler *__restrict__ Hp, PathArra
             st.index = A.sindex[i];
             st.dim = (int)(info >> 16);
             const int prim = __float_as_int(ha.x), inst = __float_as_int(ha.y);
+#ifdef SPTX_TRACE_PATH  // diagnosis build: the vertices of path 0 of a sptx_debug_radiance call
+            if (R.sampleList && i == 0)
+                printf("TRACE b%d ray o %.9g %.9g %.9g d %.9g %.9g %.9g | prim %d inst %d t %.9g dim %d\n", bounces,
+                       ray.o.x, ray.o.y, ray.o.z, ray.d.x, ray.d.y, ray.d.z, prim, inst, hb.y, st.dim);
+#endif
             bool haveIsect = false;
             if (prim >= 0) {
                 haveIsect = build_interaction(S, ray, prim, inst, ha.z, ha.w, hb.x, &it);
@@ -322,6 +327,12 @@ k_shade(const DScene *__restrict__ Sp, const DSampler *__restrict__ Hp, PathArra
                         }
                     }
                 }
+#ifdef SPTX_TRACE_PATH
+                if (R.sampleList && i == 0)
+                    printf("TRACE b%d sampled flags %d pdf %.9g wi %.9g %.9g %.9g alive %d p %.9g %.9g %.9g n %.9g %.9g %.9g\n",
+                           bounces, flags, pdf, wi.x, wi.y, wi.z, (int)alive, it.p.x, it.p.y, it.p.z, it.n.x,
+                           it.n.y, it.n.z);
+#endif
                 if (alive) {
                     V3 o = offset_ray_origin(it.p, it.pError, it.n, wi);
                     A.rayA[i] = make_float4(o.x, o.y, o.z, wi.x);

@@ -6,6 +6,7 @@
 names:  cornell       C2: spectral Cornell box (diffuse + glass + metal), perspective camera
         cornell_lens  C3: the same scene through Camera "realistic" (double-Gauss lens)
         instanced     C4: N x N displaced grid mesh, instanced on a lattice
+        zoo           one of every supported material / shape / light / camera feature (parity)
         furnace_point / furnace_area   the known-answer scenes of the reference's
                       src/tests/analytic_scenes.cpp:68-165 written as scene files
 keys:   res=<w>[x<h>] spp=<n> maxdepth=<n> strategy=<uniform|power|spatial>
@@ -132,6 +133,76 @@ def instanced(opts, out):
     return s
 
 
+def zoo(opts, out):
+    """One of everything the device path supports, for parity: thin-lens perspective camera,
+    crop window, Oren-Nayar / mirror / rough plastic / anisotropic metal / glass, mesh with
+    normals + uv + tangents, partial sphere, sphere and two-sided quad area lights, a point
+    light, a reversed-orientation instance, power light sampling, optional wide filter."""
+    w, h = opts["res"]
+    name = os.path.splitext(os.path.basename(out))[0]
+    s = 'LookAt 0 1.2 4.2  0 0.2 0  0 1 0\n'
+    s += 'Camera "perspective" "float fov" [40] "float lensradius" [0.03] "float focaldistance" [4.2]\n'
+    if opts.get("filter", "box") == "gaussian":
+        s += 'PixelFilter "gaussian" "float xwidth" [1.5] "float ywidth" [1.5]\n'
+    s += (f'Film "image" "integer xresolution" [{w}] "integer yresolution" [{h}] '
+          f'"float cropwindow" [0.1 0.95 0.05 0.9] "string filename" "{name}.exr"\n')
+    s += f'Sampler "halton" "integer pixelsamples" [{opts["spp"]}]\n'
+    s += (f'Integrator "path" "integer maxdepth" [{opts["maxdepth"]}] '
+          f'"string lightsamplestrategy" "{opts["strategy"]}"\n')
+    s += "WorldBegin\n"
+    s += 'LightSource "point" "point from" [-1.5 2.5 1.5] "blackbody I" [4000 6]\n'
+    # sphere area light
+    s += ('AttributeBegin\n  AreaLightSource "diffuse" "blackbody L" [6500 8]\n  Translate 1.2 1.8 -0.5\n'
+          '  Shape "sphere" "float radius" [0.25]\nAttributeEnd\n')
+    # two-sided quad light
+    s += ('AttributeBegin\n  AreaLightSource "diffuse" "spectrum L" [400 2 550 4 700 6] "bool twosided" "true"\n  '
+          + quad((-0.4, 2.2, -1.2), (0.4, 2.2, -1.2), (0.4, 1.7, -1.0), (-0.4, 1.7, -1.0)) + "AttributeEnd\n")
+    # floor: Oren-Nayar, mesh with uv and normals
+    s += ('AttributeBegin\n  Material "matte" "spectrum Kd" [400 .3 700 .7] "float sigma" [25]\n'
+          '  Shape "trianglemesh" "integer indices" [0 1 2 0 2 3] "point P" [-3 0 -3 3 0 -3 3 0 3 -3 0 3]\n'
+          '    "float uv" [0 0 1 0 1 1 0 1] "normal N" [0 1 0 0 1 0 0 1 0 0 1 0]\nAttributeEnd\n')
+    # back wall: plain matte
+    s += f'AttributeBegin\n  Material "matte" "spectrum Kd" {GREEN}\n  ' + \
+        quad((-3, 0, -2), (3, 0, -2), (3, 3, -2), (-3, 3, -2)) + "AttributeEnd\n"
+    # mirror sphere
+    s += ('AttributeBegin\n  Material "mirror" "spectrum Kr" [400 .9 700 .8]\n  Translate -1.3 0.45 0\n'
+          '  Shape "sphere" "float radius" [0.45]\nAttributeEnd\n')
+    # rough plastic sphere
+    s += ('AttributeBegin\n  Material "plastic" "spectrum Kd" [400 .1 700 .6] "spectrum Ks" [400 .4 700 .4] '
+          '"float roughness" [0.15]\n  Translate -0.3 0.4 0.6\n  Shape "sphere" "float radius" [0.4]\nAttributeEnd\n')
+    # glass partial sphere (clipped in z and phi), rotated
+    s += ('AttributeBegin\n  Material "glass" "float index" [1.45]\n  Translate 0.7 0.5 0.2\n  Rotate 35 1 0 0\n'
+          '  Shape "sphere" "float radius" [0.5] "float zmin" [-0.3] "float zmax" [0.4] "float phimax" [300]\n'
+          'AttributeEnd\n')
+    # anisotropic metal on a curved mesh with normals, uv and tangents
+    n = 9
+    us = np.linspace(0, 1, n)
+    P, N, S, UV, idx = [], [], [], [], []
+    for j in range(n):
+        for i in range(n):
+            a = (us[i] - 0.5) * 1.6
+            P += [1.9 + 0.45 * math.sin(a), 0.15 + us[j] * 0.9, -0.4 + 0.45 * math.cos(a) - 0.45]
+            N += [math.sin(a), 0, math.cos(a)]
+            S += [math.cos(a), 0, -math.sin(a)]
+            UV += [us[i], us[j]]
+    for j in range(n - 1):
+        for i in range(n - 1):
+            a = j * n + i
+            idx += [a, a + 1, a + n + 1, a, a + n + 1, a + n]
+    fmt = lambda v: " ".join(f"{x:.6g}" for x in v)
+    s += ('AttributeBegin\n  Material "metal" "float uroughness" [0.05] "float vroughness" [0.25]\n'
+          f'  Shape "trianglemesh" "integer indices" [{" ".join(map(str, idx))}]\n    "point P" [{fmt(P)}]\n'
+          f'    "normal N" [{fmt(N)}]\n    "vector S" [{fmt(S)}]\n    "float uv" [{fmt(UV)}]\nAttributeEnd\n')
+    # an instanced, reversed-orientation object
+    s += ('ObjectBegin "blob"\n  Material "matte" "spectrum Kd" ' + RED + '\n  ReverseOrientation\n'
+          '  Shape "trianglemesh" "integer indices" [0 1 2 0 2 3 0 3 1 1 3 2]\n'
+          '    "point P" [0 0 0 .4 0 0 .2 0 .35 .2 .5 .12]\nObjectEnd\n')
+    for k, (x, z, r) in enumerate([(-2.2, 0.8, 20), (2.3, 1.0, -50)]):
+        s += f'AttributeBegin\n  Translate {x} 0.001 {z}\n  Rotate {r} 0 1 0\n  Scale 1.5 1.5 1.5\n  ObjectInstance "blob"\nAttributeEnd\n'
+    s += "WorldEnd\n"
+    return s
+
+
 def furnace(opts, out, area):
     # src/tests/analytic_scenes.cpp:71-98 (point light, Kd = 0.5) and :135-165
     # (Kd = 0.5 sphere that also emits Le = 0.5): a camera inside a unit
@@ -167,6 +238,8 @@ def main(argv):
         text = cornell_lens(opts, out)
     elif name == "instanced":
         text = instanced(opts, out)
+    elif name == "zoo":
+        text = zoo(opts, out)
     elif name == "furnace_point":
         text = furnace(opts, out, False)
     elif name == "furnace_area":

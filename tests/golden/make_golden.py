@@ -43,6 +43,10 @@ SCENES = {
     "furnace_point": dict(gen=["furnace_point", "res=10", "spp=256", "maxdepth=8"], res=(10, 10), spp=256),
     "furnace_area": dict(gen=["furnace_area", "res=10", "spp=256", "maxdepth=8"], res=(10, 10), spp=256),
     "killeroo128": dict(ref="killeroo-simple.pbrt", res=(128, 128), spp=8),
+    # crop = croppedPixelBounds (ceil(res * cropwindow), core/film.cpp:57-63): the film / .dat size
+    "zoo": dict(gen=["zoo", "res=96x64", "spp=8", "strategy=power"], res=(96, 64), spp=8, crop=(10, 4, 92, 58)),
+    "zoo_gauss": dict(gen=["zoo", "res=64x48", "spp=4", "strategy=uniform", "filter=gaussian"], res=(64, 48),
+                      spp=4, crop=(7, 3, 61, 44)),
 }
 
 
@@ -108,6 +112,7 @@ def make(name):
         blob = os.path.join(GEN, name + ".sptx")
         run([PBRT_B200, "--quiet", pbrt], env={"SPTX_DUMP_SCENE": blob, "SPTX_DUMP_ONLY": "1"}, cwd=work)
         w, h = spec["res"]
+        x0, y0, x1, y1 = spec.get("crop", (0, 0, w, h))
         spp = spec["spp"]
         # camera samples -> reference camera rays
         n_cam = 1024
@@ -118,13 +123,13 @@ def make(name):
         cs.tofile(os.path.join(work, "cs.bin"))
         # halton queries
         n_h = 4096
-        hq = np.stack([rng.randint(0, w, n_h), rng.randint(0, h, n_h), rng.randint(0, max(spp, 64), n_h),
+        hq = np.stack([rng.randint(x0, x1, n_h), rng.randint(y0, y1, n_h), rng.randint(0, max(spp, 64), n_h),
                        rng.randint(0, 45, n_h)], -1).astype(np.int32)
         hq[:64, 3] = np.arange(64) % 2  # make sure dims 0/1 are covered
         hq.tofile(os.path.join(work, "hq.bin"))
         # Li queries
         n_li = 2048
-        lq = np.stack([rng.randint(0, w, n_li), rng.randint(0, h, n_li), rng.randint(0, spp, n_li)], -1).astype(np.int32)
+        lq = np.stack([rng.randint(x0, x1, n_li), rng.randint(y0, y1, n_li), rng.randint(0, spp, n_li)], -1).astype(np.int32)
         lq.tofile(os.path.join(work, "lq.bin"))
         env = {"ORACLE_CAMSAMPLES_IN": "cs.bin", "ORACLE_CAMRAYS_OUT": "cr.bin",
                "ORACLE_HALTON_IN": "hq.bin", "ORACLE_HALTON_OUT": "hv.bin",
@@ -150,10 +155,32 @@ def make(name):
         run([ORACLE, "--quiet", "--nthreads", "8", pbrt], env=env, cwd=work)
         hits = np.fromfile(os.path.join(work, "hits.bin"), dtype=HIT)
         anyh = np.fromfile(os.path.join(work, "any.bin"), np.int32)
+        # secondary rays: leave from the hit points of the first batch in fresh directions (the
+        # rays a path tracer really traces: origins on and inside shapes, grazing directions)
+        hp = np.nonzero(hits["prim"] >= 0)[0]
+        if len(hp):
+            pick = hp[rng.randint(0, len(hp), 4096)]
+            p = rays["o"][pick] + rays["d"][pick] * hits["t"][pick][:, None]
+            u = rng.rand(4096, 2).astype(np.float32)
+            z = 1 - 2 * u[:, 0]
+            r = np.sqrt(np.maximum(0, 1 - z * z))
+            phi = 2 * np.pi * u[:, 1]
+            d2 = np.stack([r * np.cos(phi), r * np.sin(phi), z], -1).astype(np.float32)
+            sec = np.zeros(4096, dtype=RAY)
+            sec["o"] = (p + np.float32(1e-3) * d2).astype(np.float32)
+            sec["d"] = d2
+            sec["t_max"] = np.inf
+            sec["t_max"][::4] = np.float32(0.75)   # some bounded segments
+            sec.tofile(os.path.join(work, "rays2.bin"))
+            env = {"ORACLE_RAYS_IN": "rays2.bin", "ORACLE_HITS_OUT": "hits2.bin", "ORACLE_ANYHIT_OUT": "any2.bin"}
+            run([ORACLE, "--quiet", "--nthreads", "8", pbrt], env=env, cwd=work)
+            rays = np.concatenate([rays, sec])
+            hits = np.concatenate([hits, np.fromfile(os.path.join(work, "hits2.bin"), dtype=HIT)])
+            anyh = np.concatenate([anyh, np.fromfile(os.path.join(work, "any2.bin"), np.int32)])
         # the reference's own render
         run([PBRT_REF, "--quiet", "--nthreads", "8", pbrt], cwd=work)
         dat = capi.read_dat(os.path.join(work, name + ".dat")).astype(np.float32)
-        np.savez_compressed(os.path.join(GOLD, name + ".npz"), res=np.array([w, h]), spp=np.array(spp),
+        np.savez_compressed(os.path.join(GOLD, name + ".npz"), res=np.array([x1 - x0, y1 - y0]), spp=np.array(spp),
                             cam_samples=cs, cam_rays=cr, halton_q=hq, halton_v=hv, li_q=lq, li_v=lv,
                             rays=rays, hit_prim=hits["prim"], hit_inst=hits["instance"], hit_t=hits["t"],
                             anyhit=anyh.astype(np.int8), dat=dat)
