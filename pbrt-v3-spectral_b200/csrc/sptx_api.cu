@@ -11,6 +11,7 @@
 #include <vector>
 
 #include "setup.cuh"
+#include "serial.cuh"
 
 using namespace sptx;
 
@@ -293,10 +294,10 @@ static int validate_scene(sptx_ctx *ctx, const sptx_scene_desc *sc) {
             "Halton tables missing");
         const int last = sc->sampler.n_dims - 1;
         REQ((int64_t)sc->prime_sums[last] + sc->primes[last] <= sc->n_perms, "Halton permutations short");
+    } else if (sc->sampler.type == SPTX_SAMPLER_RANDOM) {
+        REQ(sc->sampler.spp > 0, "RandomSampler needs samplesPerPixel");
     } else
-        return fail(ctx, SPTX_EUNSUPPORTED,
-                    "sptx_upload_scene: only the Halton sampler is reproduced on the device "
-                    "(RandomSampler is one serial PCG32 stream per tile, SURVEY.md 0.5)");
+        return fail(ctx, SPTX_EUNSUPPORTED, "sptx_upload_scene: sampler type %d", sc->sampler.type);
     if (sc->camera.type == SPTX_CAMERA_REALISTIC)
         REQ(sc->camera.n_elements > 0 && sc->n_lens_floats >= 4 * sc->camera.n_elements &&
                 sc->camera.n_pupil_bounds > 0 && sc->n_pupil_floats >= 4 * sc->camera.n_pupil_bounds,
@@ -492,6 +493,7 @@ extern "C" int sptx_upload_scene(sptx_ctx *ctx, const sptx_scene_desc *sc) {
     memset(&H, 0, sizeof(H));
     H.s = sc->sampler;
     for (int i = 0; i < 4; ++i) H.sb[i] = sc->film.sample_bounds[i];
+    if (sc->sampler.type == SPTX_SAMPLER_HALTON) {
     if ((rc = upload(ctx, pool, sc->primes, (int64_t)sc->sampler.n_dims, &H.primes))) return rc;
     if ((rc = upload(ctx, pool, sc->prime_sums, (int64_t)sc->sampler.n_dims, &H.prime_sums))) return rc;
     if ((rc = upload(ctx, pool, sc->perms, sc->n_perms, &H.perms))) return rc;
@@ -516,6 +518,7 @@ extern "C" int sptx_upload_scene(sptx_ctx *ctx, const sptx_scene_desc *sc) {
                 H.s, H.sb[0], H.sb[1], w, h, off);
         H.pixel_offset = off;
     }
+    }  // Halton
 
     // ---- film ----
     DFilm &F = ctx->F;
@@ -592,6 +595,44 @@ static int ensure_paths(sptx_ctx *ctx, int64_t P) {
 #undef DA
     CK(cudaMemsetAsync(A.counters, 0, 16 * sizeof(int), ctx->stream));
     ctx->allocatedPaths = P;
+    return SPTX_OK;
+}
+
+// RandomSampler: the tiles of SamplerIntegrator::Render, one single-lane warp each (serial.cuh).
+// The stream of a tile is stateful, so only the scene's whole sample range can be rendered.
+static int render_serial(sptx_ctx *ctx, const int32_t *bounds, int part, int nParts, int s0, int s1) {
+    if (s0 != 0 || s1 != ctx->H.s.spp)
+        return fail(ctx, SPTX_EUNSUPPORTED,
+                    "render: RandomSampler streams run through all %d samples of a tile; sample range "
+                    "[%d,%d) cannot be rendered on its own", ctx->H.s.spp, s0, s1);
+    SerialParams P;
+    for (int i = 0; i < 4; ++i) {
+        P.sb[i] = ctx->F.f.sample_bounds[i];
+        P.pb[i] = ctx->integ.pixel_bounds[i];
+    }
+    if (bounds) {
+        P.pb[0] = std::max(P.pb[0], bounds[0]);
+        P.pb[1] = std::max(P.pb[1], bounds[1]);
+        P.pb[2] = std::min(P.pb[2], bounds[2]);
+        P.pb[3] = std::min(P.pb[3], bounds[3]);
+    }
+    P.nTilesX = (P.sb[2] - P.sb[0] + 15) / 16;
+    P.nTilesY = (P.sb[3] - P.sb[1] + 15) / 16;
+    P.spp = ctx->H.s.spp;
+    P.maxDepth = ctx->integ.max_depth;
+    P.rrThreshold = ctx->integ.rr_threshold;
+    P.wavelength = 550.f;
+    const int nTiles = P.nTilesX * P.nTilesY;
+    if (nTiles <= 0) return SPTX_OK;
+    cudaEventRecord(ctx->ev0, ctx->stream);
+    k_render_serial<<<nTiles, 32, 0, ctx->stream>>>(ctx->dS, ctx->C, ctx->F, P, ctx->dCnt, part, nParts);
+    cudaEventRecord(ctx->ev1, ctx->stream);
+    CK(cudaStreamSynchronize(ctx->stream));
+    CK(cudaGetLastError());
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
+    ctx->counters.render_ms += ms;
+    ctx->counters.kernel_launches += 1;
     return SPTX_OK;
 }
 
@@ -760,6 +801,7 @@ extern "C" int sptx_render(sptx_ctx *ctx, const int32_t *pixel_bounds, int sampl
     if (sample_begin < 0 || sample_end < sample_begin)
         return fail(ctx, SPTX_EINVAL, "sptx_render: bad sample range [%d,%d)", sample_begin, sample_end);
     CK(cudaSetDevice(ctx->device));
+    if (ctx->H.s.type == SPTX_SAMPLER_RANDOM) return render_serial(ctx, pixel_bounds, 0, 1, sample_begin, sample_end);
     std::vector<int2> pixels;
     region_pixels(ctx, pixel_bounds, &pixels);
     return render_pixels(ctx, pixels, sample_begin, sample_end);
@@ -772,6 +814,7 @@ extern "C" int sptx_render_tiles(sptx_ctx *ctx, int part, int n_parts, int sampl
     if (n_parts < 1 || part < 0 || part >= n_parts)
         return fail(ctx, SPTX_EINVAL, "sptx_render_tiles: part %d of %d", part, n_parts);
     CK(cudaSetDevice(ctx->device));
+    if (ctx->H.s.type == SPTX_SAMPLER_RANDOM) return render_serial(ctx, nullptr, part, n_parts, sample_begin, sample_end);
     // Tiles as SamplerIntegrator::Render cuts them (core/integrator.cpp:232-257).
     const int *sb = ctx->F.f.sample_bounds;
     const int *pb = ctx->integ.pixel_bounds;
@@ -969,6 +1012,8 @@ extern "C" int sptx_sampler_eval(sptx_ctx *ctx, const int32_t *px, const int32_t
     if (!ctx) return fail(nullptr, SPTX_EINVAL, "sptx_sampler_eval: ctx is NULL");
     if (!ctx->haveScene) return fail(ctx, SPTX_ESTATE, "sptx_sampler_eval: no scene uploaded");
     if (n <= 0) return SPTX_OK;
+    if (ctx->H.s.type != SPTX_SAMPLER_HALTON)
+        return fail(ctx, SPTX_EUNSUPPORTED, "sptx_sampler_eval: only for the Halton sampler (a RandomSampler value depends on the whole tile before it)");
     CK(cudaSetDevice(ctx->device));
     std::vector<void *> pool;
     const int32_t *dpx, *dpy, *ds, *dd;
@@ -1021,6 +1066,8 @@ extern "C" int sptx_debug_radiance(sptx_ctx *ctx, const int32_t *px, const int32
     if (!ctx) return fail(nullptr, SPTX_EINVAL, "sptx_debug_radiance: ctx is NULL");
     if (!ctx->haveScene) return fail(ctx, SPTX_ESTATE, "sptx_debug_radiance: no scene uploaded");
     if (n <= 0) return SPTX_OK;
+    if (ctx->H.s.type != SPTX_SAMPLER_HALTON)
+        return fail(ctx, SPTX_EUNSUPPORTED, "sptx_debug_radiance: only for the Halton sampler (a RandomSampler value depends on the whole tile before it)");
     CK(cudaSetDevice(ctx->device));
     std::vector<int2> pixels((size_t)n);
     for (int64_t i = 0; i < n; ++i) pixels[i] = make_int2(px[i], py[i]);

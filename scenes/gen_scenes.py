@@ -9,7 +9,7 @@ names:  cornell       C2: spectral Cornell box (diffuse + glass + metal), perspe
         zoo           one of every supported material / shape / light / camera feature (parity)
         furnace_point / furnace_area   the known-answer scenes of the reference's
                       src/tests/analytic_scenes.cpp:68-165 written as scene files
-keys:   res=<w>[x<h>] spp=<n> maxdepth=<n> strategy=<uniform|power|spatial>
+keys:   res=<w>[x<h>] spp=<n> maxdepth=<n> strategy=<uniform|power|spatial> sampler=<halton|random>
         grid=<N> inst=<k> (instanced: k x k instances)
 The files only use directives the reference's parser accepts, so the same file
 feeds the reference CLI (oracle/_ref/pbrt) and the GPU host binary
@@ -56,7 +56,7 @@ def header(opts, camera, name):
     s.append(camera)
     s.append(f'Film "image" "integer xresolution" [{w}] "integer yresolution" [{h}] '
              f'"string filename" "{name}.exr"')
-    s.append(f'Sampler "halton" "integer pixelsamples" [{opts["spp"]}]')
+    s.append(f'Sampler "{opts.get("sampler", "halton")}" "integer pixelsamples" [{opts["spp"]}]')
     s.append(f'Integrator "path" "integer maxdepth" [{opts["maxdepth"]}] '
              f'"string lightsamplestrategy" "{opts["strategy"]}"')
     return "\n".join(s) + "\n"

@@ -188,6 +188,25 @@ def make(name):
               f"{int(ok.sum())}/{n_cam} camera rays, Li mean {lv[:, :31].mean():.4f}, dat mean {dat.mean():.4f}")
 
 
+def make_random(name="cornell_random"):
+    """RandomSampler fixture: the reference's render only (its values are not a function of
+    (pixel, sample, dimension), so there is nothing else to query)."""
+    gen = ["cornell", "res=48x40", "spp=4", "sampler=random"]
+    with tempfile.TemporaryDirectory() as work:
+        pbrt = os.path.join(work, name + ".pbrt")
+        run([sys.executable, os.path.join(ROOT, "scenes", "gen_scenes.py"), gen[0], pbrt] + gen[1:])
+        blob = os.path.join(GEN, name + ".sptx")
+        run([PBRT_B200, "--quiet", pbrt], env={"SPTX_DUMP_SCENE": blob, "SPTX_DUMP_ONLY": "1"}, cwd=work)
+        # one thread: the merge order of the tiles is then fixed too (the streams do not depend on it)
+        run([PBRT_REF, "--quiet", "--nthreads", "1", pbrt], cwd=work)
+        sys.path.insert(0, ROOT)
+        import importlib
+        capi = importlib.import_module("pbrt-v3-spectral_b200.capi")
+        dat = capi.read_dat(os.path.join(work, name + ".dat")).astype(np.float32)
+    np.savez_compressed(os.path.join(GOLD, name + ".npz"), res=np.array([48, 40]), spp=np.array(4), dat=dat)
+    print(f"{name}: dat mean {dat.mean():.4f}")
+
+
 def read_root_bounds(blob):
     """Root node bounds of the scene aggregate, read straight from the scene file."""
     import ctypes as C
@@ -207,6 +226,6 @@ def read_root_bounds(blob):
 
 
 if __name__ == "__main__":
-    names = sys.argv[1:] or list(SCENES)
+    names = sys.argv[1:] or list(SCENES) + ["cornell_random"]
     for n in names:
-        make(n)
+        make_random(n) if n == "cornell_random" else make(n)
