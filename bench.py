@@ -177,11 +177,20 @@ def bench_ours(args):
     dev_ms = c["render_ms"]
     reduce_ms = 0.0
     if dist:
-        ev0.record()
-        part.reduce_film(film, dist, dst=0)
-        ev1.record()
-        torch.cuda.synchronize()
-        reduce_ms = ev0.elapsed_time(ev1)
+        # the one exchange step of the path: per-rank films -> rank 0, summed in rank order by one
+        # kernel reading the peers over NVLink (sptx_film_merge_peers); NCCL reduce if asked for
+        f0 = ctx.counters()["film_ms"]
+        t_red = time.perf_counter()
+        if os.environ.get("SPTX_BENCH_NCCL_REDUCE"):
+            ev0.record()
+            part.reduce_film(film, dist, dst=0)
+            ev1.record()
+            torch.cuda.synchronize()
+            reduce_ms = ev0.elapsed_time(ev1)
+        else:
+            part.merge_films_over_peers(ctx, dist, dst=0)
+            reduce_ms = ctx.counters()["film_ms"] - f0 if rank == 0 else 0.0
+        reduce_wall_ms = (time.perf_counter() - t_red) * 1e3
         dev_ms += reduce_ms
     torch.cuda.synchronize()
     wall_ms = (time.perf_counter() - t0) * 1e3
@@ -276,6 +285,8 @@ def bench_ours(args):
             "gpu_launches": int(c["kernel_launches"]),
             "clocks": clk, "roofline": roof, "cpu_baseline": cpu, "kernels": kernels,
             "wall_ms_per_step": wall_ms / K, "film_reduce_ms": reduce_ms,
+            "film_reduce": ("nccl reduce" if os.environ.get("SPTX_BENCH_NCCL_REDUCE") else
+                            "one kernel over NVLink peer memory (sptx_film_merge_peers)") if world > 1 else None,
             "rays_per_sample": (c["closest_hit_rays"] + c["shadow_rays"]) / max(c["camera_rays"], 1),
             "mrays_per_s": (c["closest_hit_rays"] + c["shadow_rays"]) / (dev_ms * 1e-3) * 1e-6,
         }

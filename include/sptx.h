@@ -331,6 +331,20 @@ int sptx_film_clear(sptx_ctx *ctx);
  * slot 31) over croppedPixelBounds.  Exposed so the host can sum films across
  * GPUs with NCCL (the reference's MergeFilmTile, src/core/film.cpp:124-142). */
 int sptx_film_device_ptr(sptx_ctx *ctx, void **d_film, int64_t *n_floats);
+/* Multi-GPU film merge over NVLink peer memory (the reference's MergeFilmTile,
+ * src/core/film.cpp:124-142, across processes).  Every rank exports its film
+ * (a 64-byte CUDA IPC handle, to be passed to the merging rank by any host
+ * channel); the merging rank maps the peers' films and ONE kernel sums
+ * film[0] + film[1] + ... in rank order into its own film -- reading the peers
+ * straight over NVLink -- and, if `planes` is given, also writes the .dat
+ * payload of sptx_film_pack_dat from the same pass (float64 [31][H][W] on the
+ * host).  `handles` holds n_ranks handles of SPTX_IPC_HANDLE_BYTES each; slot
+ * `self` is ignored.  The caller synchronises the ranks around the call (all
+ * renders done before, peers keep their contexts alive until it returns). */
+#define SPTX_IPC_HANDLE_BYTES 64
+int sptx_film_export(sptx_ctx *ctx, void *handle);
+int sptx_film_merge_peers(sptx_ctx *ctx, const void *handles, int n_ranks, int self,
+                          double *planes);
 /* Film pixels to host: contrib [H][W][31] float32, weight [H][W] float32. */
 int sptx_film_download(sptx_ctx *ctx, float *contrib, float *weight);
 /* Film::WriteImage's spectral branch (src/core/film.cpp:226-306) up to the

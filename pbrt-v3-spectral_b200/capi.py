@@ -21,12 +21,14 @@ SYMBOLS = [
     "sptx_abi_version", "sptx_create", "sptx_destroy", "sptx_last_error",
     "sptx_upload_scene", "sptx_intersect_batch", "sptx_intersect_batch_device",
     "sptx_render", "sptx_render_tiles", "sptx_film_clear", "sptx_film_device_ptr",
+    "sptx_film_export", "sptx_film_merge_peers",
     "sptx_film_download", "sptx_film_pack_dat", "sptx_write_dat",
     "sptx_get_counters", "sptx_reset_counters", "sptx_set_wavefront_size", "sptx_set_option",
     "sptx_sampler_eval", "sptx_camera_rays", "sptx_debug_radiance",
     "sptx_scene_save", "sptx_scene_load", "sptx_scene_free", "sptx_io_last_error",
 ]
 
+IPC_HANDLE_BYTES = 64
 RAY_DTYPE = np.dtype([("o", "<f4", 3), ("t_max", "<f4"), ("d", "<f4", 3), ("time", "<f4")])
 HIT_DTYPE = np.dtype([("prim", "<i4"), ("instance", "<i4"), ("t", "<f4"), ("b0", "<f4"),
                       ("b1", "<f4"), ("b2", "<f4"), ("n_nodes", "<i4"), ("n_tests", "<i4")])
@@ -79,6 +81,8 @@ def lib():
     L.sptx_film_device_ptr.argtypes = [vp, C.POINTER(vp), C.POINTER(i64)]
     L.sptx_film_download.argtypes = [vp, vp, vp]
     L.sptx_film_pack_dat.argtypes = [vp, vp]
+    L.sptx_film_export.argtypes = [vp, vp]
+    L.sptx_film_merge_peers.argtypes = [vp, vp, i32, i32, vp]
     L.sptx_write_dat.argtypes = [C.c_char_p, i32, i32, vp]
     L.sptx_get_counters.argtypes = [vp, C.POINTER(Counters)]
     L.sptx_reset_counters.argtypes = [vp]
@@ -197,6 +201,26 @@ class Context:
             weight = np.empty((height, width), dtype=np.float32)
         self._ck(lib().sptx_film_download(self.h, _ptr(contrib), _ptr(weight)), "sptx_film_download")
         return contrib, weight
+
+    def film_export(self):
+        """64-byte CUDA IPC handle of the device film (for the merging rank)."""
+        buf = C.create_string_buffer(IPC_HANDLE_BYTES)
+        self._ck(lib().sptx_film_export(self.h, buf), "sptx_film_export")
+        return buf.raw
+
+    def film_merge_peers(self, handles, self_rank, pack=None):
+        """Sums the films of all ranks (rank order) into this rank's film with one kernel reading
+        the peers over NVLink; `handles` = list of film_export() results indexed by rank.  With
+        pack=(width, height) also returns the .dat planes [31][H][W] float64 of the merged film."""
+        blob = b"".join(bytes(h) for h in handles)
+        assert len(blob) == IPC_HANDLE_BYTES * len(handles)
+        planes = None
+        if pack is not None:
+            planes = np.empty((NBINS, pack[1], pack[0]), dtype=np.float64)
+        self._ck(lib().sptx_film_merge_peers(self.h, blob, len(handles), int(self_rank),
+                                             _ptr(planes) if planes is not None else None),
+                 "sptx_film_merge_peers")
+        return planes
 
     def film_pack_dat(self, width, height):
         planes = np.zeros((NBINS, height, width), dtype=np.float64)

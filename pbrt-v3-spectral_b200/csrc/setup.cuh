@@ -129,6 +129,43 @@ __global__ void k_film_split(const float *pixels, int64_t nPix, float *out) {
     }
 }
 
+// Film merge across GPUs fused with the .dat pack: film[self] = sum over ranks (rank order) of
+// film[r], peers read through their NVLink-mapped pointers; one warp per 32 pixels: lane = bin
+// for the sums (one 128-byte line per pixel and rank), lane = pixel for the transposed float64
+// planes (256-byte runs), through a padded shared-memory tile.
+struct PeerFilms {
+    const float *film[8];
+    int n;
+};
+__global__ void __launch_bounds__(256)
+k_film_merge_pack(PeerFilms P, float *own, int64_t nPix, float scale, double *planes) {
+    __shared__ float tile[8][32][33];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int64_t nGroups = (nPix + 31) / 32;
+    for (int64_t g = (int64_t)blockIdx.x * 8 + warp; g < nGroups; g += (int64_t)gridDim.x * 8) {
+        const int64_t p0 = g * 32;
+        for (int k = 0; k < 32; ++k) {
+            const int64_t p = p0 + k;
+            float acc = 0.f;
+            if (p < nPix) {
+                const int64_t at = p * SPTX_SPECTRUM_STRIDE + lane;
+                acc = P.film[0][at];
+                for (int r = 1; r < P.n; ++r) acc += P.film[r][at];
+                own[at] = acc;
+            }
+            tile[warp][k][lane] = acc;
+        }
+        __syncwarp();
+        if (planes && p0 + lane < nPix)
+            for (int b = 0; b < SPTX_NBINS; ++b) {
+                    float v = tile[warp][lane][b] + 0.f;  // as k_pack_dat
+                    v = v * scale;
+                    planes[(int64_t)b * nPix + p0 + lane] = (double)v;
+                }
+        __syncwarp();
+    }
+}
+
 __global__ void k_sampler_eval(DSampler H, const int *px, const int *py, const int *sample,
                                const int *dim, int64_t n, float *out) {
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;

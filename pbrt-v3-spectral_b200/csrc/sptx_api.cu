@@ -881,6 +881,70 @@ extern "C" int sptx_film_download(sptx_ctx *ctx, float *contrib, float *weight) 
     return SPTX_OK;
 }
 
+extern "C" int sptx_film_export(sptx_ctx *ctx, void *handle) {
+    if (!ctx || !handle) return fail(ctx, SPTX_EINVAL, "sptx_film_export: NULL argument");
+    if (!ctx->haveScene) return fail(ctx, SPTX_ESTATE, "sptx_film_export: no scene uploaded");
+    static_assert(sizeof(cudaIpcMemHandle_t) == SPTX_IPC_HANDLE_BYTES, "IPC handle size");
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(ctx->stream));
+    cudaIpcMemHandle_t h;
+    CK(cudaIpcGetMemHandle(&h, ctx->F.pixels));
+    memcpy(handle, &h, sizeof(h));
+    return SPTX_OK;
+}
+
+extern "C" int sptx_film_merge_peers(sptx_ctx *ctx, const void *handles, int n_ranks, int self,
+                                     double *planes) {
+    if (!ctx || !handles) return fail(ctx, SPTX_EINVAL, "sptx_film_merge_peers: NULL argument");
+    if (!ctx->haveScene) return fail(ctx, SPTX_ESTATE, "sptx_film_merge_peers: no scene uploaded");
+    if (n_ranks < 1 || n_ranks > 8 || self < 0 || self >= n_ranks)
+        return fail(ctx, SPTX_EINVAL, "sptx_film_merge_peers: rank %d of %d (at most 8 ranks)", self, n_ranks);
+    CK(cudaSetDevice(ctx->device));
+    const int64_t nPix = (int64_t)ctx->F.width * ctx->F.height;
+    if (nPix == 0) return SPTX_OK;
+    PeerFilms P;
+    P.n = n_ranks;
+    void *mapped[8] = {nullptr};
+    int rc = SPTX_OK;
+    for (int r = 0; r < n_ranks && rc == SPTX_OK; ++r) {
+        if (r == self) {
+            P.film[r] = ctx->F.pixels;
+            continue;
+        }
+        cudaIpcMemHandle_t h;
+        memcpy(&h, (const char *)handles + (size_t)r * SPTX_IPC_HANDLE_BYTES, sizeof(h));
+        cudaError_t e = cudaIpcOpenMemHandle(&mapped[r], h, cudaIpcMemLazyEnablePeerAccess);
+        if (e != cudaSuccess)
+            rc = fail(ctx, SPTX_ECUDA, "sptx_film_merge_peers: mapping the film of rank %d: %s", r,
+                      cudaGetErrorString(e));
+        P.film[r] = (const float *)mapped[r];
+    }
+    double *dPlanes = nullptr;
+    if (rc == SPTX_OK && planes) {
+        cudaError_t e = cudaMalloc((void **)&dPlanes, (size_t)nPix * SPTX_NBINS * sizeof(double));
+        if (e != cudaSuccess) rc = fail(ctx, SPTX_ECUDA, "sptx_film_merge_peers: %s", cudaGetErrorString(e));
+    }
+    if (rc == SPTX_OK) {
+        cudaEventRecord(ctx->ev2, ctx->stream);
+        k_film_merge_pack<<<ctx->smCount * 4, 256, 0, ctx->stream>>>(P, ctx->F.pixels, nPix, ctx->F.f.scale, dPlanes);
+        cudaEventRecord(ctx->ev3, ctx->stream);
+        cudaError_t e = cudaSuccess;
+        if (planes)
+            e = cudaMemcpyAsync(planes, dPlanes, (size_t)nPix * SPTX_NBINS * sizeof(double),
+                                cudaMemcpyDeviceToHost, ctx->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+        if (e == cudaSuccess) e = cudaGetLastError();
+        if (e != cudaSuccess) rc = fail(ctx, SPTX_ECUDA, "sptx_film_merge_peers: %s", cudaGetErrorString(e));
+        float ms = 0.f;
+        if (rc == SPTX_OK && cudaEventElapsedTime(&ms, ctx->ev2, ctx->ev3) == cudaSuccess) ctx->counters.film_ms += ms;
+        ctx->counters.kernel_launches += 1;
+    }
+    if (dPlanes) cudaFree(dPlanes);
+    for (int r = 0; r < n_ranks; ++r)
+        if (mapped[r]) cudaIpcCloseMemHandle(mapped[r]);
+    return rc;
+}
+
 extern "C" int sptx_film_pack_dat(sptx_ctx *ctx, double *planes) {
     if (!ctx) return fail(nullptr, SPTX_EINVAL, "sptx_film_pack_dat: ctx is NULL");
     if (!ctx->haveScene) return fail(ctx, SPTX_ESTATE, "sptx_film_pack_dat: no scene uploaded");

@@ -52,3 +52,33 @@ def reduce_film(film, dist=None, dst=0):
     if dist is not None and dist.is_initialized() and dist.get_world_size() > 1:
         dist.reduce(film, dst=dst, op=dist.ReduceOp.SUM)
     return film
+
+
+def gather_handles(handle, dist=None):
+    """Every rank's film handle (bytes), indexed by rank, on every rank.  The handles are 64-byte
+    CUDA IPC tokens: a host-side exchange of a few bytes, so any backend does (a uint8 all_gather)."""
+    if dist is None or not dist.is_initialized() or dist.get_world_size() == 1:
+        return [bytes(handle)]
+    import torch
+    world = dist.get_world_size()
+    dev = torch.device("cuda", torch.cuda.current_device()) if dist.get_backend() == "nccl" else torch.device("cpu")
+    mine = torch.frombuffer(bytearray(handle), dtype=torch.uint8).to(dev)
+    out = [torch.empty_like(mine) for _ in range(world)]
+    dist.all_gather(out, mine)
+    return [bytes(t.cpu().numpy().tobytes()) for t in out]
+
+
+def merge_films_over_peers(ctx, dist=None, dst=0, pack=None):
+    """The exchange step of a sample-partitioned render: every rank exports its device film, rank
+    `dst` maps the peers and sums all films in rank order with ONE kernel reading them over NVLink
+    (sptx_film_merge_peers), optionally producing the .dat planes in the same pass.  Barriers keep
+    the peers' films alive and quiescent around the merge.  Returns the planes on `dst` (or None)."""
+    if dist is None or not dist.is_initialized() or dist.get_world_size() == 1:
+        return ctx.film_pack_dat(*pack) if pack is not None else None
+    handles = gather_handles(ctx.film_export(), dist)   # all renders of this rank are complete here
+    dist.barrier()
+    planes = None
+    if dist.get_rank() == dst:
+        planes = ctx.film_merge_peers(handles, dst, pack)
+    dist.barrier()
+    return planes

@@ -66,6 +66,11 @@ def _worker(rank, world, port, q):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
+    # the film-handle exchange of merge_films_over_peers: 64 opaque bytes per rank, rank order
+    handles = part.gather_handles(bytes([rank * 16 + (i % 16) for i in range(64)]), dist)
+    assert len(handles) == world
+    for r in range(world):
+        assert handles[r] == bytes([r * 16 + (i % 16) for i in range(64)])
     mine = []
     for k in range(STEPS):
         a, b = part.sample_block(k, rank, world, SPP_STEP)
