@@ -277,7 +277,7 @@ def bench_ours(args):
             "ms_per_step": dev_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
             "config": {"workload": WORKLOAD, "samples_per_step": RES * RES * SPP_STEP,
-                       "spp_per_step": SPP_STEP, "partition": "sample numbers across ranks + NCCL film reduce"
+                       "spp_per_step": SPP_STEP, "partition": "sample numbers across ranks + film merge on rank 0"
                        if world > 1 else "single GPU",
                        "l2": "path state of a pass (4.2 M paths, ~3.7 GB) exceeds L2 between launches"},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
