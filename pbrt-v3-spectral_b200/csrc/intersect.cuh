@@ -203,7 +203,21 @@ SPTX_NOINL bool sphere_test(const sptx_sphere &sp, const Ray &wr, SphereHit *h) 
         const float av = d.x * d.x + d.y * d.y + d.z * d.z;
         const float bv = 2.f * (d.x * o.x + d.y * o.y + d.z * o.z);
         const float cv = o.x * o.x + o.y * o.y + o.z * o.z - sp.radius * sp.radius;
-        if ((double)bv * (double)bv - 4. * (double)av * (double)cv < 0.) return false;
+        const double discrim = (double)bv * (double)bv - 4. * (double)av * (double)cv;
+        if (discrim < 0.) return false;
+        // The roots' value parts, with the float operations of Quadratic(EFloat...): an interval
+        // contains its value (lo <= v <= hi), so "t0.hi > tMax" holds whenever t0.v > tMax and
+        // "t1.lo <= 0" whenever t1.v <= 0 -- those rays are rejected before any interval work
+        // (every shadow ray aimed at a sphere light ends just short of it: t0.v > tMax).
+        const float rd = (float)sqrt(discrim);
+        const float q = (bv < 0) ? -.5f * (bv - rd) : -.5f * (bv + rd);
+        float t0v = q / av, t1v = cv / q;
+        if (t0v > t1v) {
+            const float t = t0v;
+            t0v = t1v;
+            t1v = t;
+        }
+        if (t0v > ray.tMax || t1v <= 0) return false;
     }
     EF ox = ef(ray.o.x, oErr.x), oy = ef(ray.o.y, oErr.y), oz = ef(ray.o.z, oErr.z);
     EF dx = ef(ray.d.x, dErr.x), dy = ef(ray.d.y, dErr.y), dz = ef(ray.d.z, dErr.z);
@@ -352,13 +366,17 @@ __device__ bool traverse_bvh(const DScene &S, int bvhIndex, Ray &ray, HitRec *hi
                     break;
                 }
                 int axis = (int)((meta >> 16) & 0xffu);
+                int far;
                 if (neg[axis]) {
-                    stack[sp++] = cur + 1;
+                    far = cur + 1;
                     cur = offset;
                 } else {
-                    stack[sp++] = offset;
+                    far = offset;
                     cur = cur + 1;
                 }
+                stack[sp++] = far;
+                // the far child is visited some iterations from now: have its node in L1 by then
+                asm volatile("prefetch.global.L1 [%0];" ::"l"(nodes + 2 * (size_t)far));
             } else {
                 if (sp == 0) {
                     done = true;

@@ -68,34 +68,36 @@ k_resolve(DScene S, PathArrays A, int betaIn, DeviceCounters *cnt) {
                 ++nShadow;
             }
         }
-        if (useA || useB) {
-            // Ld = Spectrum(0) + fa + fb in the order EstimateDirect adds them
-            const Row4 Lr = row4(A.L, i), fa = row4(A.fa, i), fb = row4(A.fb, i),
-                       br = row4(const_cast<float *>(beta), i);
-            for (int c = 0; c < 8; ++c) {
-                float4 Ld = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (useA) {
-                    const float4 v = fa.ld(c);
-                    Ld.x += v.x;
-                    Ld.y += v.y;
-                    Ld.z += v.z;
-                    Ld.w += v.w;
-                }
-                if (useB) {
-                    const float4 v = fb.ld(c);
-                    Ld.x += v.x;
-                    Ld.y += v.y;
-                    Ld.z += v.z;
-                    Ld.w += v.w;
-                }
-                const float4 bt = br.ld(c);
-                float4 l = Lr.ld(c);
-                l.x += bt.x * (Ld.x / lightPdfSel);
-                l.y += bt.y * (Ld.y / lightPdfSel);
-                l.z += bt.z * (Ld.z / lightPdfSel);
-                l.w += bt.w * (Ld.w / lightPdfSel);
-                Lr.st(c, l);
+        // bin phase: the warp walks its paths, lane = bin; four paths per round so that
+        // their rows are in flight together
+        const unsigned mA = __ballot_sync(0xffffffffu, useA);
+        const unsigned mB = __ballot_sync(0xffffffffu, useB);
+        unsigned m = mA | mB;
+        while (m) {
+            size_t at[4];
+            float sel[4], va[4], vb[4], bt[4], Lv[4];
+            bool on[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                on[j] = m != 0;
+                const int p = on[j] ? __ffs(m) - 1 : 0;
+                m &= m - 1;
+                const int ip = __shfl_sync(0xffffffffu, i, p);
+                sel[j] = __shfl_sync(0xffffffffu, lightPdfSel, p);
+                at[j] = (size_t)ip * SPTX_SPECTRUM_STRIDE + lane;
+                va[j] = (on[j] && ((mA >> p) & 1u)) ? A.fa[at[j]] : 0.f;
+                vb[j] = (on[j] && ((mB >> p) & 1u)) ? A.fb[at[j]] : 0.f;
+                bt[j] = on[j] ? beta[at[j]] : 0.f;
+                Lv[j] = on[j] ? A.L[at[j]] : 0.f;
+                // Ld = Spectrum(0) + fa + fb in the order EstimateDirect adds them
+                float Ld = 0.f;
+                if ((mA >> p) & 1u) Ld += va[j];
+                if ((mB >> p) & 1u) Ld += vb[j];
+                va[j] = Ld;
             }
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+                if (on[j]) A.L[at[j]] = Lv[j] + bt[j] * (va[j] / sel[j]);
         }
     }
     if (COUNT) {
