@@ -212,10 +212,16 @@ def bench_ours(args):
         dist.barrier()
     host_film = (np.zeros((h, w, 31), np.float32), np.zeros((h, w), np.float32))  # caller-owned result
     t0 = time.perf_counter()
+    e2e_parts = [0.0, 0.0, 0.0]
     for k in range(e2e_steps):
+        ta = time.perf_counter()
         ctx.upload(sf)                      # host arrays -> HBM (also a fresh, cleared film)
+        tb = time.perf_counter()
         ctx.render(*step_range(k))
+        tc = time.perf_counter()
         contrib, weight = ctx.film_download(w, h, out=host_film)  # device film -> host
+        td = time.perf_counter()
+        e2e_parts = [e2e_parts[0] + tb - ta, e2e_parts[1] + tc - tb, e2e_parts[2] + td - tc]
     e2e_s = time.perf_counter() - t0
     if dist:
         t = torch.tensor([e2e_s], device=f"cuda:{local}", dtype=torch.float64)
@@ -281,7 +287,9 @@ def bench_ours(args):
                        if world > 1 else "single GPU",
                        "l2": "path state of a pass (4.2 M paths, ~3.7 GB) exceeds L2 between launches"},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "steps": e2e_steps},
+                    "steps": e2e_steps,
+                    "ms_per_step": {n: 1e3 * v / e2e_steps
+                                    for n, v in zip(("upload", "render", "film_download"), e2e_parts)}},
             "gpu_launches": int(c["kernel_launches"]),
             "clocks": clk, "roofline": roof, "cpu_baseline": cpu, "kernels": kernels,
             "wall_ms_per_step": wall_ms / K, "film_reduce_ms": reduce_ms,

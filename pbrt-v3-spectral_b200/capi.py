@@ -11,7 +11,8 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libsptx.so")
+# SPTX_LIB_PATH: a diagnosis build of the same library (e.g. -DSPTX_STAGE_CLOCKS), tools/ only
+LIB_PATH = os.environ.get("SPTX_LIB_PATH") or os.path.join(HERE, "libsptx.so")
 
 NBINS = 31
 STRIDE = 32

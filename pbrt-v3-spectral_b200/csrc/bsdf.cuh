@@ -122,6 +122,10 @@ SPTX_DEV float fsum_bin(const DScene &S, const FSum &f, int b) {
 SPTX_DEV float4 spec4(const DScene &S, int row, int c) {
     return __ldg(reinterpret_cast<const float4 *>(S.spectra + (size_t)row * SPTX_SPECTRUM_STRIDE) + c);
 }
+// x / d for the .w word of chunk c: the last chunk's .w is the row's pad word (always 0), and
+// 0 / d (or a conductor Fresnel term of an all-zero bin) would run the IEEE division and
+// square-root slow paths for nothing
+SPTX_DEV float padless(int c, float x, float d) { return c < 7 ? x / d : 0.f; }
 SPTX_DEV float4 fterm4(const DScene &S, const FTerm &t, int c) {
     const float4 R = spec4(S, t.R, c);
     switch (t.kind) {
@@ -131,26 +135,27 @@ SPTX_DEV float4 fterm4(const DScene &S, const FTerm &t, int c) {
         return make_float4(R.x * t.s0 * t.s1, R.y * t.s0 * t.s1, R.z * t.s0 * t.s1, R.w * t.s0 * t.s1);
     case TERM_MICRO_S:
         return make_float4(R.x * t.s0 * t.s1 * t.s2 / t.s3, R.y * t.s0 * t.s1 * t.s2 / t.s3,
-                           R.z * t.s0 * t.s1 * t.s2 / t.s3, R.w * t.s0 * t.s1 * t.s2 / t.s3);
+                           R.z * t.s0 * t.s1 * t.s2 / t.s3, padless(c, R.w * t.s0 * t.s1 * t.s2, t.s3));
     case TERM_MICRO_COND: {
         const float4 ei = spec4(S, t.e0, c), et = spec4(S, t.e1, c), k = spec4(S, t.e2, c);
         return make_float4(R.x * t.s0 * t.s1 * fr_conductor_bin(t.s2, ei.x, et.x, k.x) / t.s3,
                            R.y * t.s0 * t.s1 * fr_conductor_bin(t.s2, ei.y, et.y, k.y) / t.s3,
                            R.z * t.s0 * t.s1 * fr_conductor_bin(t.s2, ei.z, et.z, k.z) / t.s3,
-                           R.w * t.s0 * t.s1 * fr_conductor_bin(t.s2, ei.w, et.w, k.w) / t.s3);
+                           c < 7 ? R.w * t.s0 * t.s1 * fr_conductor_bin(t.s2, ei.w, et.w, k.w) / t.s3 : 0.f);
     }
     case TERM_S_R_DIV:
-        return make_float4(t.s0 * R.x / t.s1, t.s0 * R.y / t.s1, t.s0 * R.z / t.s1, t.s0 * R.w / t.s1);
+        return make_float4(t.s0 * R.x / t.s1, t.s0 * R.y / t.s1, t.s0 * R.z / t.s1,
+                           padless(c, t.s0 * R.w, t.s1));
     case TERM_COND_R_DIV: {
         const float4 ei = spec4(S, t.e0, c), et = spec4(S, t.e1, c), k = spec4(S, t.e2, c);
         return make_float4(fr_conductor_bin(t.s0, ei.x, et.x, k.x) * R.x / t.s1,
                            fr_conductor_bin(t.s0, ei.y, et.y, k.y) * R.y / t.s1,
                            fr_conductor_bin(t.s0, ei.z, et.z, k.z) * R.z / t.s1,
-                           fr_conductor_bin(t.s0, ei.w, et.w, k.w) * R.w / t.s1);
+                           c < 7 ? fr_conductor_bin(t.s0, ei.w, et.w, k.w) * R.w / t.s1 : 0.f);
     }
     default:  // TERM_T_S_S_DIV
         return make_float4((R.x * t.s0) * t.s1 / t.s2, (R.y * t.s0) * t.s1 / t.s2,
-                           (R.z * t.s0) * t.s1 / t.s2, (R.w * t.s0) * t.s1 / t.s2);
+                           (R.z * t.s0) * t.s1 / t.s2, padless(c, (R.w * t.s0) * t.s1, t.s2));
     }
 }
 SPTX_DEV float4 fsum4(const DScene &S, const FSum &f, int c) {

@@ -97,7 +97,9 @@ k_resolve(DScene S, PathArrays A, int betaIn, DeviceCounters *cnt) {
             }
 #pragma unroll
             for (int j = 0; j < 4; ++j)
-                if (on[j]) A.L[at[j]] = Lv[j] + bt[j] * (va[j] / sel[j]);
+                // (lane 31 is the row's pad word: its 0 / sel would take the division's slow path
+                //  alone, with the other 31 lanes waiting)
+                if (on[j] && lane < SPTX_NBINS) A.L[at[j]] = Lv[j] + bt[j] * (va[j] / sel[j]);
         }
     }
     if (COUNT) {

@@ -54,6 +54,10 @@ SPTX_DEV bool any_nonzero4(float4 v, int c) {
     return v.x != 0.f || v.y != 0.f || v.z != 0.f || (c < 7 && v.w != 0.f);
 }
 
+// 128-byte line into L2 without tying up registers (the row is consumed a few thousand
+// instructions later, by which time it would otherwise be a DRAM round trip).
+SPTX_DEV void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+
 // The vertex is cut into stages with a block barrier between them.  The
 // barriers are not needed for correctness: they keep the SM's warps inside the
 // same few KB of code, so that the instruction cache serves all of them from
@@ -110,7 +114,7 @@ k_shade(const DScene *__restrict__ Sp, const DSampler *__restrict__ Hp, PathArra
         const int *queue = A.qc + (size_t)cls * A.capacity;
         const int k = first * (int)blockDim.x + (int)threadIdx.x;
         bool alive = k < classN[cls];
-        int i = 0;
+        int i = 0, iNext = -1;
         SampleStream st{0, 0};
         int bounces = 0, neeFlags = 0, lightNum = 0;
         float lightPdfSel = 0.f, etaScale = 1.f, rayWeight = 0.f;
@@ -121,6 +125,13 @@ k_shade(const DScene *__restrict__ Sp, const DSampler *__restrict__ Hp, PathArra
         // ---- stage 0: interaction, emission (path.cpp:91-112) ----
         if (alive) {
             i = queue[k];
+#ifndef SPTX_NO_PREFETCH
+            prefetch_l2(A.beta[betaIn] + (size_t)i * SPTX_SPECTRUM_STRIDE);
+            {   // the next chunk of this block: its path state is a scattered gather, start it now
+                const int kn = k + (int)(gridDim.x * blockDim.x);
+                if (kn < classN[cls]) iNext = queue[kn];  // (same class only)
+            }
+#endif
             const float4 ra = A.rayA[i], rb = A.rayB[i];
             const float4 ha = A.hitA[i], hb = A.hitB[i];
             ray.o = mk(ra.x, ra.y, ra.z);
@@ -182,6 +193,16 @@ k_shade(const DScene *__restrict__ Sp, const DSampler *__restrict__ Hp, PathArra
                 }
             }
         }
+#ifndef SPTX_NO_PREFETCH
+        if (iNext >= 0) {
+            prefetch_l2(A.rayA + iNext);
+            prefetch_l2(A.rayB + iNext);
+            prefetch_l2(A.hitA + iNext);
+            prefetch_l2(A.hitB + iNext);
+            prefetch_l2(A.info + iNext);
+            prefetch_l2(A.sindex + iNext);
+        }
+#endif
         SPTX_STAGE(2);
         // ---- stage 2: light sampling strategy (integrator.cpp:119-163) ----
         bool delta = false;
@@ -209,7 +230,7 @@ k_shade(const DScene *__restrict__ Sp, const DSampler *__restrict__ Hp, PathArra
                     li.x = li.x / ls.divisor;
                     li.y = li.y / ls.divisor;
                     li.z = li.z / ls.divisor;
-                    li.w = li.w / ls.divisor;
+                    li.w = padless(c, li.w, ls.divisor);
                 }
                 fv.x *= ad;
                 fv.y *= ad;
@@ -222,7 +243,7 @@ k_shade(const DScene *__restrict__ Sp, const DSampler *__restrict__ Hp, PathArra
                     o.z = o.z * weight;
                     o.w = o.w * weight;
                 }
-                fa.st(c, make_float4(o.x / ls.pdf, o.y / ls.pdf, o.z / ls.pdf, o.w / ls.pdf));
+                fa.st(c, make_float4(o.x / ls.pdf, o.y / ls.pdf, o.z / ls.pdf, padless(c, o.w, ls.pdf)));
                 fNon |= any_nonzero4(fv, c);
                 liNon |= any_nonzero4(li, c);
             }
@@ -264,7 +285,8 @@ k_shade(const DScene *__restrict__ Sp, const DSampler *__restrict__ Hp, PathArra
                         fv.z *= ad;
                         fv.w *= ad;
                         fb.st(c, make_float4(fv.x * le.x * weight / sPdf, fv.y * le.y * weight / sPdf,
-                                             fv.z * le.z * weight / sPdf, fv.w * le.w * weight / sPdf));
+                                             fv.z * le.z * weight / sPdf,
+                                             padless(c, fv.w * le.w * weight, sPdf)));
                         fNon |= any_nonzero4(fv, c);
                     }
                     if (fNon) {
@@ -299,7 +321,7 @@ k_shade(const DScene *__restrict__ Sp, const DSampler *__restrict__ Hp, PathArra
                 for (int c = 0; c < 8; ++c) {
                     const float4 fv = fsum4(S, f, c), b = bIn.ld(c);
                     const float4 nb = make_float4(b.x * (fv.x * ad / pdf), b.y * (fv.y * ad / pdf),
-                                                  b.z * (fv.z * ad / pdf), b.w * (fv.w * ad / pdf));
+                                                  b.z * (fv.z * ad / pdf), b.w * padless(c, fv.w * ad, pdf));
                     bOut.st(c, nb);
                     fNon |= any_nonzero4(fv, c);
                     // MaxComponentValue(beta * etaScale), std::max order (path.cpp:176-177)
@@ -323,7 +345,7 @@ k_shade(const DScene *__restrict__ Sp, const DSampler *__restrict__ Hp, PathArra
                         const float inv = 1.f - q;
                         for (int c = 0; c < 8; ++c) {
                             float4 b = bOut.ld(c);
-                            bOut.st(c, make_float4(b.x / inv, b.y / inv, b.z / inv, b.w / inv));
+                            bOut.st(c, make_float4(b.x / inv, b.y / inv, b.z / inv, padless(c, b.w, inv)));
                         }
                     }
                 }
