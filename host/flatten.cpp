@@ -636,7 +636,9 @@ bool FlattenScene(const Scene &scene, const Camera &camera, Sampler &sampler,
             return fail("sampler array requests are not on the path");
         // Dimensions a path can consume: 5 camera dims + per bounce at most
         // 1+2+2 (light pick, uLight, uScattering) + 2 (BSDF) + 1 (RR).
-        int dims = 5 + 8 * (std::max(params.maxDepth, 0) + 2);
+        // SpectralPathIntegrator runs one path per band off the same stream.
+        int dims = 5 + 8 * (std::max(params.maxDepth, 0) + 2) *
+                           std::max(params.numCABands, 1);
         dims = std::min(std::max(dims, 64), (int)PrimeTableSize);
         fsm.n_dims = dims;
         out->primes.assign(Primes, Primes + dims);
@@ -658,6 +660,11 @@ bool FlattenScene(const Scene &scene, const Camera &camera, Sampler &sampler,
     fi.max_depth = params.maxDepth;
     fi.rr_threshold = params.rrThreshold;
     for (int i = 0; i < 4; ++i) fi.pixel_bounds[i] = params.pixelBounds[i];
+    fi.num_ca_bands = params.numCABands;
+    if (params.numCABands > 1 && out->desc.sampler.type != SPTX_SAMPLER_HALTON)
+        return fail(
+            "spectralpath with numCABands > 1 is on the GPU hot path for the "
+            "halton sampler only");
     if (params.lightSampleStrategy == "uniform")
         fi.light_strategy = SPTX_LIGHTS_UNIFORM;
     else if (params.lightSampleStrategy == "power")

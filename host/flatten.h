@@ -28,6 +28,9 @@ struct PathParams {
     float rrThreshold = 1.f;
     int pixelBounds[4] = {0, 0, 0, 0};
     std::string lightSampleStrategy = "spatial";
+    // 0: Integrator "path".  >= 1: Integrator "spectralpath", numCABands
+    // (src/integrators/spectralpath.cpp:345-378)
+    int numCABands = 0;
 };
 
 // Owns the flattened arrays; desc points into them.

@@ -38,6 +38,7 @@
 #include "film.h"
 #include "integrator.h"
 #include "integrators/path.h"
+#include "integrators/spectralpath.h"
 #include "paramset.h"
 #include "sampler.h"
 #include "scene.h"
@@ -65,11 +66,18 @@ class GpuPathIntegrator : public Integrator {
     std::shared_ptr<Sampler> sampler;
 };
 
+// Leaves without running static destructors: pbrt's worker threads are still
+// parked on their condition variable, and std::exit() would wait for them.
+[[noreturn]] static void ExitNow() {
+    fflush(nullptr);
+    std::_Exit(1);
+}
+
 static void Die(sptx_ctx *ctx, const char *what) {
     // No CPU fallback (north star): a failed device path is fatal, reported
     // the way the reference reports unrecoverable errors.
     Error("GpuPathIntegrator: %s failed: %s", what, sptx_last_error(ctx));
-    std::exit(1);
+    ExitNow();
 }
 
 void GpuPathIntegrator::Render(const Scene &scene) {
@@ -79,7 +87,7 @@ void GpuPathIntegrator::Render(const Scene &scene) {
                                  &err)) {
         Error("GpuPathIntegrator: scene is outside the GPU hot path: %s",
               err.c_str());
-        std::exit(1);
+        ExitNow();
     }
     if (const char *dump = std::getenv("SPTX_DUMP_SCENE")) {
         if (sptx_scene_save(dump, &flat.desc) != 0) Die(nullptr, "scene save");
@@ -138,9 +146,9 @@ void GpuPathIntegrator::Render(const Scene &scene) {
 // (src/integrators/path.cpp:190-213).  The return type is dictated by the
 // declaration api.cpp was compiled against; api.cpp only ever converts the
 // result to Integrator* (a no-op for single inheritance).
-PathIntegrator *CreatePathIntegrator(const ParamSet &params,
-                                     std::shared_ptr<Sampler> sampler,
-                                     std::shared_ptr<const Camera> camera) {
+static sptx_host::PathParams ReadPathParams(const ParamSet &params,
+                                            const Camera &cameraRef) {
+    const Camera *camera = &cameraRef;
     sptx_host::PathParams pp;
     pp.maxDepth = params.FindOneInt("maxdepth", 5);
     int np;
@@ -164,8 +172,40 @@ PathIntegrator *CreatePathIntegrator(const ParamSet &params,
     pp.rrThreshold = params.FindOneFloat("rrthreshold", 1.);
     pp.lightSampleStrategy =
         params.FindOneString("lightsamplestrategy", "spatial");
+    return pp;
+}
+
+PathIntegrator *CreatePathIntegrator(const ParamSet &params,
+                                     std::shared_ptr<Sampler> sampler,
+                                     std::shared_ptr<const Camera> camera) {
+    sptx_host::PathParams pp = ReadPathParams(params, *camera);
     Integrator *gpu = new GpuPathIntegrator(pp, camera, sampler);
     return reinterpret_cast<PathIntegrator *>(gpu);
+}
+
+// Integrator "spectralpath" (RenderOptions::MakeIntegrator,
+// src/core/api.cpp: name == "spectralpath" -> CreateSpectralPathIntegrator;
+// factory src/integrators/spectralpath.cpp:345-378): the same parameters plus
+// numCABands (default 4), the number of wavelength bands traced per camera
+// sample.  Bound like CreatePathIntegrator: defined here, linked ahead of the
+// archive, so the CPU SpectralPathIntegrator object is never pulled in.
+SpectralPathIntegrator *CreateSpectralPathIntegrator(
+    const ParamSet &params, std::shared_ptr<Sampler> sampler,
+    std::shared_ptr<const Camera> camera) {
+    sptx_host::PathParams pp = ReadPathParams(params, *camera);
+    pp.numCABands = params.FindOneInt("numCABands", 4);
+    if (pp.numCABands != 1)
+        Warning(
+            "Using spectral rendering. For every pixel sample we will trace "
+            "%dx more rays. Rendering will be %d times slower.",
+            pp.numCABands, pp.numCABands);
+    if (pp.numCABands < 1) {
+        // the reference's band loop then runs zero times: every sample is black
+        Error("numCABands must be >= 1. Got %d.", pp.numCABands);
+        return nullptr;
+    }
+    Integrator *gpu = new GpuPathIntegrator(pp, camera, sampler);
+    return reinterpret_cast<SpectralPathIntegrator *>(gpu);
 }
 
 }  // namespace pbrt

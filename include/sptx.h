@@ -210,7 +210,11 @@ typedef struct sptx_integrator {
     int32_t pixel_bounds[4];
     int32_t light_strategy; /* as named in the scene file; the 1-light       */
                             /* fallback to uniform is applied by the core     */
-    int32_t pad;
+    int32_t num_ca_bands;   /* 0 or 1: Integrator "path".  >= 1 from Integrator  */
+                            /* "spectralpath" (numCABands): per camera sample  */
+                            /* one path per wavelength band, each band's bins   */
+                            /* taken from its own path, src/integrators/        */
+                            /* spectralpath.cpp:198-342                         */
 } sptx_integrator;
 
 /* Everything Render() needs, as flat host arrays.  The caller keeps ownership

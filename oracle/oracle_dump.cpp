@@ -244,6 +244,9 @@ void DumpIntegrator::Render(const Scene &scene) {
             s.time = cs[5 * i + 2];
             s.pLens = Point2f(cs[5 * i + 3], cs[5 * i + 4]);
             RayDifferential ray;
+            // SpectralPathIntegrator sets the wavelength before generating the ray
+            // (integrators/spectralpath.cpp:265-270); 550 is the Ray default
+            if (const char *wl = getenv("ORACLE_WAVELENGTH")) ray.wavelength = (Float)atof(wl);
             Float w = camera.GenerateRayDifferential(s, &ray);
             float *o = &out[8 * i];
             o[0] = ray.o.x; o[1] = ray.o.y; o[2] = ray.o.z; o[3] = ray.tMax;

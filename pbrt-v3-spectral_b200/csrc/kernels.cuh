@@ -36,7 +36,11 @@ __global__ void k_generate(DScene S, DCamera C, DSampler H, PathArrays A, Render
         A.rayA[i] = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.d.x);
         A.rayB[i] = make_float4(ray.d.y, ray.d.z, 1.f, w);
         A.sindex[i] = st.index;
-        A.info[i] = pack_info(0, 0, st.dim);
+        // SpectralPathIntegrator (integrators/spectralpath.cpp:262-283): the bands of a sample share
+        // its CameraSample and draw from ONE sampler stream, band after band -- a band starts at
+        // the dimension where the previous band's path stopped (left in `info` by K3)
+        const int startDim = R.band > 0 ? (int)(A.info[i] >> 16) : st.dim;
+        A.info[i] = pack_info(0, 0, startDim);
         A.pfilm[i] = make_float2(pFilm.x, pFilm.y);
         A.spill[i] = 0;
         // path-major spectra: 32 floats (one 128-byte line) per path

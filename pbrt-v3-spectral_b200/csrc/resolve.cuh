@@ -111,6 +111,46 @@ k_resolve(DScene S, PathArrays A, int betaIn, DeviceCounters *cnt) {
     if (lane == 0 && nShadow) atomicAdd(&cnt->shadowRays, nShadow);
 }
 
+// ---- band merge of SpectralPathIntegrator --------------------------------------
+// integrators/spectralpath.cpp:284-318: the radiance of a band's path goes through the
+// NaN / negative / infinite-luminance guard, then only the band's bins [lo, hi) are copied into
+// the sample's spectrum.  One thread per path; after the last band the merged row replaces the
+// path's L, which is what the film kernels add.
+__global__ void k_band_commit(DScene S, PathArrays A, float *Lacc, int64_t nPaths, int lo, int hi,
+                              int first, int last) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nPaths;
+         i += (int64_t)gridDim.x * blockDim.x) {
+        float4 *Lp = reinterpret_cast<float4 *>(A.L + i * SPTX_SPECTRUM_STRIDE);
+        float4 *Ap = reinterpret_cast<float4 *>(Lacc + i * SPTX_SPECTRUM_STRIDE);
+        float Lv[SPTX_SPECTRUM_STRIDE], acc[SPTX_SPECTRUM_STRIDE];
+#pragma unroll
+        for (int c = 0; c < SPTX_SPECTRUM_STRIDE / 4; ++c) {
+            const float4 v = Lp[c];
+            const float4 a = first ? make_float4(0.f, 0.f, 0.f, 0.f) : Ap[c];
+            Lv[4 * c] = v.x, Lv[4 * c + 1] = v.y, Lv[4 * c + 2] = v.z, Lv[4 * c + 3] = v.w;
+            acc[4 * c] = a.x, acc[4 * c + 1] = a.y, acc[4 * c + 2] = a.z, acc[4 * c + 3] = a.w;
+        }
+        float yy = 0.f;
+        bool nan = false;
+#pragma unroll
+        for (int b = 0; b < SPTX_NBINS; ++b) {
+            if (isnan(Lv[b])) nan = true;
+            yy += S.cie_y[b] * Lv[b];
+        }
+        const float y = y_finish(S, yy);
+        const bool black = nan || y < -1e-5f || isinf(y);
+#pragma unroll
+        for (int b = 0; b < SPTX_NBINS; ++b)
+            if (b >= lo && b < hi) acc[b] = black ? 0.f : Lv[b];
+#pragma unroll
+        for (int c = 0; c < SPTX_SPECTRUM_STRIDE / 4; ++c) {
+            const float4 a = make_float4(acc[4 * c], acc[4 * c + 1], acc[4 * c + 2], acc[4 * c + 3]);
+            Ap[c] = a;
+            if (last) Lp[c] = a;
+        }
+    }
+}
+
 // ---- K5: film accumulation, one thread per pixel ------------------------------
 // The NaN / infinite-luminance guard of SamplerIntegrator::Render
 // (core/integrator.cpp:295-316) and FilmTile::AddSample (core/film.h:123-163).

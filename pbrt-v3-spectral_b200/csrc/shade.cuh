@@ -114,6 +114,7 @@ k_shade(const DScene *__restrict__ Sp, const DSampler *__restrict__ Hp, PathArra
         const int *queue = A.qc + (size_t)cls * A.capacity;
         const int k = first * (int)blockDim.x + (int)threadIdx.x;
         bool alive = k < classN[cls];
+        const bool valid = alive;
         int i = 0, iNext = -1;
         SampleStream st{0, 0};
         int bounces = 0, neeFlags = 0, lightNum = 0;
@@ -364,6 +365,8 @@ k_shade(const DScene *__restrict__ Sp, const DSampler *__restrict__ Hp, PathArra
                 }
             }
         }
+        // the next band of the sample continues the sampler stream where this path stopped
+        if (R.nBands > 1 && valid && !alive) A.info[i] = pack_info(bounces, 0, st.dim);
         SPTX_TICK(10);
         queue_push(A.qNee, A.counters + 2, i, neeFlags != 0);
         queue_push(A.qMis, A.counters + 4, i, (neeFlags & NEE_HAS_MIS) != 0);

@@ -35,6 +35,8 @@ struct sptx_ctx {
     // pinned staging for film downloads, and the device pixel list of the last render region
     float *dFilmSplit = nullptr;  // [P][31] contrib + [P] weight, the download layout
     size_t dFilmSplitFloats = 0;
+    float *dLacc = nullptr;       // [P][32] merged spectrum of a sample's bands (num_ca_bands > 1)
+    int64_t dLaccPaths = 0;
     int2 *dPixels = nullptr;
     int64_t dPixelsCap = 0;
     std::vector<int2> pixelsKey;  // host copy of what dPixels holds
@@ -175,6 +177,7 @@ extern "C" void sptx_destroy(sptx_ctx *ctx) {
     if (ctx->dCnt) cudaFree(ctx->dCnt);
     if (ctx->dS) cudaFree(ctx->dS);
     if (ctx->dFilmSplit) cudaFree(ctx->dFilmSplit);
+    if (ctx->dLacc) cudaFree(ctx->dLacc);
     if (ctx->dPixels) cudaFree(ctx->dPixels);
     if (ctx->dH) cudaFree(ctx->dH);
     cudaEventDestroy(ctx->ev0);
@@ -605,6 +608,10 @@ static int render_serial(sptx_ctx *ctx, const int32_t *bounds, int part, int nPa
         return fail(ctx, SPTX_EUNSUPPORTED,
                     "render: RandomSampler streams run through all %d samples of a tile; sample range "
                     "[%d,%d) cannot be rendered on its own", ctx->H.s.spp, s0, s1);
+    if (ctx->integ.num_ca_bands > 1)
+        return fail(ctx, SPTX_EUNSUPPORTED,
+                    "render: SpectralPathIntegrator bands (numCABands = %d) with the RandomSampler are "
+                    "not on the device path", (int)ctx->integ.num_ca_bands);
     SerialParams P;
     for (int i = 0; i < 4; ++i) {
         P.sb[i] = ctx->F.f.sample_bounds[i];
@@ -686,6 +693,18 @@ static int render_pixels(sptx_ctx *ctx, const std::vector<int2> &pixels, int s0,
         ++launches;
     };
     const bool cv = ctx->countVisits;
+    // SpectralPathIntegrator's bands (the per-sample Li hook always traces the 550 nm path)
+    const int nBands = dSampleList ? 1 : std::max(1, (int)ctx->integ.num_ca_bands);
+    const int deltaIndex = (int)std::round((float)SPTX_NBINS / (float)nBands);
+    const float deltaWave = (float)((705 - 395) / SPTX_NBINS);  // integer division, as in the reference
+    const float deltaWaveCA = deltaWave * deltaIndex;
+    if (nBands > 1 && ctx->dLaccPaths < A.capacity) {
+        if (ctx->dLacc) cudaFree(ctx->dLacc);
+        ctx->dLacc = nullptr;
+        ctx->dLaccPaths = 0;
+        CK(cudaMalloc((void **)&ctx->dLacc, (size_t)A.capacity * SPTX_SPECTRUM_STRIDE * sizeof(float)));
+        ctx->dLaccPaths = A.capacity;
+    }
     cudaEventRecord(ctx->ev0, ctx->stream);
     for (int64_t p0 = 0; p0 < nPixAll; p0 += chunkPix) {
         const int nPix = (int)std::min<int64_t>(chunkPix, nPixAll - p0);
@@ -697,45 +716,60 @@ static int render_pixels(sptx_ctx *ctx, const std::vector<int2> &pixels, int s0,
             R.maxDepth = maxDepth;
             R.rrThreshold = ctx->integ.rr_threshold;
             R.pixels = dPixels + p0;
-            R.wavelength = 550.f;
             R.sampleList = dSampleList;
             const int64_t nPaths = (int64_t)nPix * R.samplesInPass;
             const int g = grid_for(ctx, nPaths);
             // one resident block per SM; chunks = class queues in block-sized pieces
             const int gShade = (int)std::min<int64_t>((nPaths + kShadeBlock - 1) / kShadeBlock + kShadeClasses,
                                                      (int64_t)ctx->smCount);
-            k_set_counters<<<1, 1, 0, ctx->stream>>>(A.counters, 0, 0, 1, 0);
-            ++launches;
-            tic(0);
-            k_generate<<<g, kBlock, 0, ctx->stream>>>(ctx->S, ctx->C, ctx->H, A, R, ctx->dCnt);
-            toc();
-            int qi = 0, betaIn = 0;
-            for (int bounce = 0; bounce <= maxDepth; ++bounce) {
-                k_reset_bounce<<<1, 32, 0, ctx->stream>>>(A.counters, qi ^ 1);
+            for (int band = 0; band < nBands; ++band) {
+                // ray.wavelength = middle of the band (integrators/spectralpath.cpp:240-268);
+                // one band = PathIntegrator at 550 nm
+                R.band = band;
+                R.nBands = nBands;
+                R.wavelength = nBands > 1 ? 395.f + deltaWaveCA * band + (deltaWaveCA / 2) : 550.f;
+                k_set_counters<<<1, 1, 0, ctx->stream>>>(A.counters, 0, 0, 1, 0);
                 ++launches;
-                tic(1);
-                if (cv)
-                    k_intersect<true><<<g, kBlock, 0, ctx->stream>>>(ctx->S, A, qi, ctx->dCnt);
-                else
-                    k_intersect<false><<<g, kBlock, 0, ctx->stream>>>(ctx->S, A, qi, ctx->dCnt);
+                tic(0);
+                k_generate<<<g, kBlock, 0, ctx->stream>>>(ctx->S, ctx->C, ctx->H, A, R, ctx->dCnt);
                 toc();
-                tic(2);
-                k_shade<<<gShade, kShadeBlock, 0, ctx->stream>>>(ctx->dS, ctx->dH, A, R, qi, betaIn, ctx->dCnt);
-                toc();
-                if (bounce < maxDepth) {
-                    tic(3);
-                    if (cv) {
-                        k_mis<true><<<g, kBlock, 0, ctx->stream>>>(ctx->S, A, ctx->dCnt);
-                        k_resolve<true><<<g, kBlock, 0, ctx->stream>>>(ctx->S, A, betaIn, ctx->dCnt);
-                    } else {
-                        k_mis<false><<<g, kBlock, 0, ctx->stream>>>(ctx->S, A, ctx->dCnt);
-                        k_resolve<false><<<g, kBlock, 0, ctx->stream>>>(ctx->S, A, betaIn, ctx->dCnt);
-                    }
+                int qi = 0, betaIn = 0;
+                for (int bounce = 0; bounce <= maxDepth; ++bounce) {
+                    k_reset_bounce<<<1, 32, 0, ctx->stream>>>(A.counters, qi ^ 1);
                     ++launches;
+                    tic(1);
+                    if (cv)
+                        k_intersect<true><<<g, kBlock, 0, ctx->stream>>>(ctx->S, A, qi, ctx->dCnt);
+                    else
+                        k_intersect<false><<<g, kBlock, 0, ctx->stream>>>(ctx->S, A, qi, ctx->dCnt);
+                    toc();
+                    tic(2);
+                    k_shade<<<gShade, kShadeBlock, 0, ctx->stream>>>(ctx->dS, ctx->dH, A, R, qi, betaIn,
+                                                                     ctx->dCnt);
+                    toc();
+                    if (bounce < maxDepth) {
+                        tic(3);
+                        if (cv) {
+                            k_mis<true><<<g, kBlock, 0, ctx->stream>>>(ctx->S, A, ctx->dCnt);
+                            k_resolve<true><<<g, kBlock, 0, ctx->stream>>>(ctx->S, A, betaIn, ctx->dCnt);
+                        } else {
+                            k_mis<false><<<g, kBlock, 0, ctx->stream>>>(ctx->S, A, ctx->dCnt);
+                            k_resolve<false><<<g, kBlock, 0, ctx->stream>>>(ctx->S, A, betaIn, ctx->dCnt);
+                        }
+                        ++launches;
+                        toc();
+                    }
+                    qi ^= 1;
+                    betaIn ^= 1;
+                }
+                if (nBands > 1) {
+                    const int lo = deltaIndex * band;
+                    const int hi = std::min(deltaIndex * (band + 1), (int)SPTX_NBINS);
+                    tic(4);
+                    k_band_commit<<<g, kBlock, 0, ctx->stream>>>(ctx->S, A, ctx->dLacc, nPaths, lo, hi,
+                                                                 band == 0, band == nBands - 1);
                     toc();
                 }
-                qi ^= 1;
-                betaIn ^= 1;
             }
             if (!dSampleList) {
                 tic(4);

@@ -53,6 +53,7 @@ struct RenderParams {
     float rrThreshold;
     const int2 *pixels;  // [nPix] pixel coordinates
     float wavelength;    // ray.wavelength (550 for PathIntegrator)
+    int band, nBands;    // SpectralPathIntegrator: this launch traces band `band` of `nBands`
     const int *sampleList;  // debug: explicit sample number per path (or NULL)
 };
 

@@ -57,7 +57,10 @@ def header(opts, camera, name):
     s.append(f'Film "image" "integer xresolution" [{w}] "integer yresolution" [{h}] '
              f'"string filename" "{name}.exr"')
     s.append(f'Sampler "{opts.get("sampler", "halton")}" "integer pixelsamples" [{opts["spp"]}]')
-    s.append(f'Integrator "path" "integer maxdepth" [{opts["maxdepth"]}] '
+    integ = 'Integrator "path"'
+    if "bands" in opts:  # SpectralPathIntegrator: one path per wavelength band
+        integ = f'Integrator "spectralpath" "integer numCABands" [{int(opts["bands"])}]'
+    s.append(f'{integ} "integer maxdepth" [{opts["maxdepth"]}] '
              f'"string lightsamplestrategy" "{opts["strategy"]}"')
     return "\n".join(s) + "\n"
 
@@ -102,6 +105,8 @@ def cornell_lens(opts, out):
         f.write(DGAUSS_50MM)
     cam = ('LookAt 0 0 3.8  0 0 0  0 1 0\nCamera "realistic" "string lensfile" "dgauss.50mm.dat" '
            '"float aperturediameter" [8] "float focusdistance" [3.8] "bool simpleweighting" "true"')
+    if opts.get("ca") == "true":  # wavelength-dependent lens refraction (cameras/realistic.cpp:352-358)
+        cam += ' "bool chromaticAberrationEnabled" "true"'
     return header(opts, cam, os.path.splitext(os.path.basename(out))[0]) + cornell_world()
 
 

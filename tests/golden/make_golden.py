@@ -207,6 +207,70 @@ def make_random(name="cornell_random"):
     print(f"{name}: dat mean {dat.mean():.4f}")
 
 
+# SpectralPathIntegrator fixtures: name -> gen_scenes arguments
+BAND_SCENES = {
+    # double-Gauss lens with wavelength-dependent refraction, 4 bands (the fork's default)
+    "cornell_lens_ca": dict(gen=["cornell_lens", "res=48", "spp=8", "bands=4", "ca=true"], res=(48, 48), spp=8,
+                            bands=4),
+    # perspective camera, 3 bands: round(31/3) = 10 bins per band leaves bin 30 unassigned (black)
+    "cornell_bands3": dict(gen=["cornell", "res=40x32", "spp=4", "bands=3"], res=(40, 32), spp=4, bands=3),
+    # one band at 550 nm == Integrator "path" (cornell_bands1_path: the same file with "path")
+    "cornell_bands1": dict(gen=["cornell", "res=40x32", "spp=4", "bands=1"], res=(40, 32), spp=4, bands=1),
+}
+
+
+def band_wavelengths(n_bands):
+    """ray.wavelength of each band, integrators/spectralpath.cpp:240-268 (float arithmetic)."""
+    delta_index = int(np.floor(np.float32(31) / np.float32(n_bands) + 0.5))  # round(), positive argument
+    dw_ca = np.float32((705 - 395) // 31) * np.float32(delta_index)
+    return [float(np.float32(395) + dw_ca * np.float32(s) + dw_ca / np.float32(2)) for s in range(n_bands)]
+
+
+def make_bands(name):
+    """Integrator "spectralpath": the reference's render, and the reference camera's rays at every
+    band's wavelength (through a sibling Integrator "path" file with the same camera, which is
+    what oracle_dump hooks)."""
+    spec = BAND_SCENES[name]
+    gen = spec["gen"]
+    with tempfile.TemporaryDirectory() as work:
+        pbrt = os.path.join(work, name + ".pbrt")
+        run([sys.executable, os.path.join(ROOT, "scenes", "gen_scenes.py"), gen[0], pbrt] + gen[1:])
+        blob = os.path.join(GEN, name + ".sptx")
+        run([PBRT_B200, "--quiet", pbrt], env={"SPTX_DUMP_SCENE": blob, "SPTX_DUMP_ONLY": "1"}, cwd=work)
+        run([PBRT_REF, "--quiet", "--nthreads", "8", pbrt], cwd=work)
+        sys.path.insert(0, ROOT)
+        import importlib
+        capi = importlib.import_module("pbrt-v3-spectral_b200.capi")
+        dat = capi.read_dat(os.path.join(work, name + ".dat")).astype(np.float32)
+        sib = os.path.join(work, name + "_path.pbrt")
+        run([sys.executable, os.path.join(ROOT, "scenes", "gen_scenes.py"), gen[0], sib] +
+            [a for a in gen[1:] if not a.startswith("bands=")])
+        rng = np.random.RandomState(sum(map(ord, name)))
+        w, h = spec["res"]
+        n_cam = 1024
+        cs = np.zeros((n_cam, 5), np.float32)
+        cs[:, 0] = rng.rand(n_cam) * w
+        cs[:, 1] = rng.rand(n_cam) * h
+        cs[:, 2:] = rng.rand(n_cam, 3)
+        cs.tofile(os.path.join(work, "cs.bin"))
+        if name == "cornell_bands1":
+            run([PBRT_REF, "--quiet", "--nthreads", "8", sib], cwd=work)
+            dat_path = capi.read_dat(os.path.join(work, name + "_path.dat")).astype(np.float32)
+            np.savez_compressed(os.path.join(GOLD, name + "_path.npz"), res=np.array(spec["res"]),
+                                spp=np.array(spec["spp"]), dat=dat_path)
+        lams = band_wavelengths(spec["bands"])
+        crs = []
+        for lam in lams:
+            run([ORACLE, "--quiet", "--nthreads", "8", sib], cwd=work,
+                env={"ORACLE_CAMSAMPLES_IN": "cs.bin", "ORACLE_CAMRAYS_OUT": "cr.bin", "ORACLE_WAVELENGTH": repr(lam)})
+            crs.append(np.fromfile(os.path.join(work, "cr.bin"), np.float32).reshape(-1, 8))
+    np.savez_compressed(os.path.join(GOLD, name + ".npz"), res=np.array(spec["res"]), spp=np.array(spec["spp"]),
+                        bands=np.array(spec["bands"]), wavelengths=np.array(lams, np.float32), cam_samples=cs,
+                        cam_rays=np.stack(crs), dat=dat)
+    print(f"{name}: bands at {lams} nm, dat mean {dat.mean():.4f}, per-bin means "
+          f"{np.array2string(dat.mean(axis=(1, 2))[[0, 7, 8, 15, 16, 23, 24, 29, 30]], precision=4)}")
+
+
 def read_root_bounds(blob):
     """Root node bounds of the scene aggregate, read straight from the scene file."""
     import ctypes as C
@@ -226,6 +290,11 @@ def read_root_bounds(blob):
 
 
 if __name__ == "__main__":
-    names = sys.argv[1:] or list(SCENES) + ["cornell_random"]
+    names = sys.argv[1:] or list(SCENES) + ["cornell_random"] + list(BAND_SCENES)
     for n in names:
-        make_random(n) if n == "cornell_random" else make(n)
+        if n == "cornell_random":
+            make_random(n)
+        elif n in BAND_SCENES:
+            make_bands(n)
+        else:
+            make(n)

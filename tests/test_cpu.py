@@ -82,3 +82,48 @@ def test_write_dat_matches_reference_layout(capi, tmp_path):
     assert raw.startswith(b"2 3 31\nv3 \n")
     assert len(raw) == len(b"2 3 31\nv3 \n") + 31 * 3 * 2 * 8
     assert np.array_equal(capi.read_dat(p), planes)
+
+
+# ---- Integrator "spectralpath"  ----------------------------------------
+
+BAND_SCENES = ["cornell_lens_ca", "cornell_bands3", "cornell_bands1"]
+
+
+@pytest.mark.parametrize("name", BAND_SCENES)
+def test_band_fixture_follows_the_reference_band_layout(name):
+    """integrators/spectralpath.cpp:240-318: deltaIndex = round(31 / numCABands) bins per band,
+    ray.wavelength = 395 + 10 * deltaIndex * (s + 1/2); bins past the last band stay black."""
+    g = golden(name)
+    n = int(g["bands"])
+    di = int(np.floor(31 / n + 0.5))
+    lam = [395 + 10 * di * s + 10 * di / 2 for s in range(n)]
+    assert np.allclose(g["wavelengths"], lam)
+    owned = np.zeros(31, bool)
+    for s in range(n):
+        owned[di * s:min(di * (s + 1), 31)] = True
+    means = g["dat"].mean(axis=(1, 2))
+    assert (means[owned] > 0).all() and (means[~owned] == 0).all()
+    assert g["cam_rays"].shape == (n, g["cam_samples"].shape[0], 8)
+
+
+def test_one_band_is_the_path_integrator():
+    """numCABands = 1 traces one 550 nm path per sample from the same Halton stream: the
+    reference's two integrators then write the same image."""
+    a, b = golden("cornell_bands1"), golden("cornell_bands1_path")
+    assert np.array_equal(a["dat"], b["dat"])
+
+
+def test_flattener_rejects_bands_with_random_sampler(tmp_path):
+    """No silent approximation: the tile-serial RandomSampler path does not run bands."""
+    import subprocess
+    import sys
+    exe = os.path.join(ROOT, "host", "_build", "pbrt_b200")
+    if not os.path.exists(exe):
+        pytest.skip("host binary is built only where the reference sources are")
+    scene = str(tmp_path / "s.pbrt")
+    subprocess.check_call([sys.executable, os.path.join(ROOT, "scenes", "gen_scenes.py"), "cornell", scene,
+                           "res=16", "spp=1", "sampler=random", "bands=2"])
+    env = dict(os.environ, SPTX_DUMP_SCENE=str(tmp_path / "s.sptx"), SPTX_DUMP_ONLY="1")
+    r = subprocess.run([exe, "--quiet", scene], cwd=str(tmp_path), env=env, capture_output=True, text=True)
+    assert r.returncode != 0 and "halton sampler only" in (r.stdout + r.stderr)
+    assert not os.path.exists(str(tmp_path / "s.sptx"))
