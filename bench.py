@@ -34,15 +34,38 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 GEN = os.path.join(ROOT, "scenes", "_gen")
-RES = 1024
+RES_W = RES_H = 1024   # --workload c2 (default); c5 = 3840 x 2160, 4096 spp (set_workload)
 SPP_TOTAL = 1024
 SPP_STEP = 64
 REF_SPP_STEP = 2       # reference arm: sample numbers per step (bounded sample)
 CPU_BASELINE_SPP = 8   # cpu_baseline leg of our arm
 METRIC = "spectral_msamples_per_s"
 UNIT = "Msamples/s"
-WORKLOAD = (f"procedural spectral Cornell box (diffuse+glass+metal), 31 bins, {RES}x{RES}, Halton, "
-            f"maxdepth 5, {SPP_TOTAL} spp")
+WORKLOAD = ""
+
+
+def set_workload(name):
+    """c2 = BASELINE.json configs[1] (the metric's single-GPU configuration, the default);
+    c5 = configs[4], the 4K render at 4096 spp partitioned across GPUs."""
+    global RES_W, RES_H, SPP_TOTAL, WORKLOAD
+    RES_W, RES_H, SPP_TOTAL = {"c2": (1024, 1024, 1024), "c5": (3840, 2160, 4096)}[name]
+    WORKLOAD = (f"procedural spectral Cornell box (diffuse+glass+metal), 31 bins, {RES_W}x{RES_H}, Halton, "
+                f"maxdepth 5, {SPP_TOTAL} spp")
+
+
+def res_arg():
+    return f"res={RES_W}x{RES_H}"
+
+
+def blob_name():
+    return f"cornell{RES_W}" if RES_W == RES_H else f"cornell{RES_W}x{RES_H}"
+
+
+set_workload("c2")
+
+
+def emit(text):  # rebound by main() to the process's original stdout
+    print(text)
 
 
 def peaks():
@@ -54,14 +77,14 @@ def peaks():
 
 def scene_pbrt(path, spp):
     subprocess.check_call([sys.executable, os.path.join(ROOT, "scenes", "gen_scenes.py"), "cornell", path,
-                           f"res={RES}", f"spp={spp}"])
+                           res_arg(), f"spp={spp}"])
 
 
 def scene_blob():
-    blob = os.path.join(GEN, f"cornell{RES}.sptx")
+    blob = os.path.join(GEN, blob_name() + ".sptx")
     if not os.path.exists(blob):
         entry = importlib.import_module("__graft_entry__")
-        entry.make_scene_blob(f"cornell{RES}", ["cornell", f"res={RES}", f"spp={SPP_TOTAL}"], blob)
+        entry.make_scene_blob(blob_name(), ["cornell", res_arg(), f"spp={SPP_TOTAL}"], blob)
     return blob
 
 
@@ -121,7 +144,7 @@ def reference_rate(spp_lo, spp_hi, threads=None):
             if out.returncode != 0:
                 raise RuntimeError("reference renderer failed:\n" + out.stdout[-2000:])
     dt = max(times[1] - times[0], 1e-6)
-    return RES * RES * (spp_hi - spp_lo) / dt * 1e-6, dt, cores, times
+    return RES_W * RES_H * (spp_hi - spp_lo) / dt * 1e-6, dt, cores, times
 
 
 class CudaArray:
@@ -148,7 +171,7 @@ def bench_ours(args):
     blob = scene_blob() if rank == 0 else None
     if world > 1:
         dist.barrier()
-        blob = os.path.join(GEN, f"cornell{RES}.sptx")
+        blob = os.path.join(GEN, blob_name() + ".sptx")
     ctx = capi.Context(local)
     sf = capi.SceneFile(blob)
     ctx.upload(sf)
@@ -199,11 +222,11 @@ def bench_ours(args):
         t = torch.tensor([dev_ms, wall_ms], device=f"cuda:{local}", dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dev_ms, wall_ms = float(t[0]), float(t[1])
-    samples_total = float(RES * RES * SPP_STEP * K * world)
+    samples_total = float(RES_W * RES_H * SPP_STEP * K * world)
     value = samples_total / (dev_ms * 1e-3) * 1e-6
 
     # ---- e2e through the C ABI with host buffers (every rank; max over ranks) ----
-    w = h = RES
+    w, h = RES_W, RES_H
     e2e_steps = max(1, min(K, 4))
     h2d = os.path.getsize(blob)
     d2h = w * h * 32 * 4
@@ -227,7 +250,7 @@ def bench_ours(args):
         t = torch.tensor([e2e_s], device=f"cuda:{local}", dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_s = float(t[0])
-    e2e_value = RES * RES * SPP_STEP * e2e_steps * world / e2e_s * 1e-6
+    e2e_value = RES_W * RES_H * SPP_STEP * e2e_steps * world / e2e_s * 1e-6
 
     line = None
     if rank == 0:
@@ -282,7 +305,7 @@ def bench_ours(args):
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": dev_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "samples_per_step": RES * RES * SPP_STEP,
+            "config": {"workload": WORKLOAD, "samples_per_step": RES_W * RES_H * SPP_STEP,
                        "spp_per_step": SPP_STEP, "partition": "sample numbers across ranks + film merge on rank 0"
                        if world > 1 else "single GPU",
                        "l2": "path state of a pass (4.2 M paths, ~3.7 GB) exceeds L2 between launches"},
@@ -304,7 +327,7 @@ def bench_ours(args):
         dist.barrier()
         dist.destroy_process_group()
     if line:
-        print(json.dumps(line))
+        emit(json.dumps(line))
 
 
 def bench_reference(args):
@@ -314,7 +337,7 @@ def bench_reference(args):
     K, W = args.steps, args.warmup
     exe = os.path.join(ROOT, "oracle", "_ref", "pbrt")
     if not os.path.exists(exe):
-        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/pbrt was not built"}))
+        emit(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/pbrt was not built"}))
         return
     cores = os.cpu_count() or 1
     secs = []
@@ -323,18 +346,18 @@ def bench_reference(args):
         if k >= W:
             secs.append(dt)
     total = sum(secs)
-    samples = RES * RES * REF_SPP_STEP * K
+    samples = RES_W * RES_H * REF_SPP_STEP * K
     value = samples / total * 1e-6
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
             "steps": K, "warmup": W, "ms_per_step": total / K * 1e3, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "samples_per_step": RES * RES * REF_SPP_STEP,
+            "config": {"workload": WORKLOAD, "samples_per_step": RES_W * RES_H * REF_SPP_STEP,
                        "spp_per_step": REF_SPP_STEP},
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "reference",
                              "sample": f"{REF_SPP_STEP} spp of the same scene per step (difference of a "
                                        f"{1 + REF_SPP_STEP}-spp and a 1-spp run of oracle/_ref/pbrt)"},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line))
+    emit(json.dumps(line))
 
 
 def main():
@@ -343,7 +366,18 @@ def main():
     ap.add_argument("--steps", type=int, default=SPP_TOTAL // SPP_STEP)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="c2", choices=["c2", "c5"],
+                    help="c2: 1024x1024 at 1024 spp (default, the metric's configuration); "
+                         "c5: 3840x2160 at 4096 spp, for --gpus 2/4/8")
     args = ap.parse_args()
+    set_workload(args.workload)
+    # stdout carries exactly ONE JSON line: anything a library prints there while the benchmark
+    # runs (NCCL's version banner, for one) is sent to stderr instead
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    global emit
+    emit = lambda text: os.write(real_stdout, (text + "\n").encode())
     if args.impl == "reference":
         bench_reference(args)
     else:
