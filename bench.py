@@ -233,7 +233,9 @@ def bench_ours(args):
     torch.cuda.synchronize()
     if dist:
         dist.barrier()
-    host_film = (np.zeros((h, w, 31), np.float32), np.zeros((h, w), np.float32))  # caller-owned result
+    # caller-owned result buffers, page-locked (what a host integration registers once per film)
+    host_film = (torch.zeros((h, w, 31), dtype=torch.float32).pin_memory().numpy(),
+                 torch.zeros((h, w), dtype=torch.float32).pin_memory().numpy())
     t0 = time.perf_counter()
     e2e_parts = [0.0, 0.0, 0.0]
     for k in range(e2e_steps):

@@ -67,7 +67,11 @@ SPTX_DEV void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0]
 #ifndef SPTX_SHADE_BLOCK
 #define SPTX_SHADE_BLOCK 512
 #endif
+#ifndef SPTX_SHADE_BLOCKS_PER_SM
+#define SPTX_SHADE_BLOCKS_PER_SM 1
+#endif
 constexpr int kShadeBlock = SPTX_SHADE_BLOCK;
+constexpr int kShadeBlocksPerSM = SPTX_SHADE_BLOCKS_PER_SM;
 #ifdef SPTX_STAGE_CLOCKS  // diagnosis build: per-stage warp clocks, printed by k_film
 __device__ unsigned long long g_stageClocks[32];
 #define SPTX_TICK(slot)                 \
@@ -89,7 +93,7 @@ __device__ unsigned long long g_stageClocks[32];
         SPTX_TICK(slot + 1);                                   \
     } while (0)
 
-__global__ void __launch_bounds__(kShadeBlock, 1)
+__global__ void __launch_bounds__(kShadeBlock, kShadeBlocksPerSM)
 k_shade(const DScene *__restrict__ Sp, const DSampler *__restrict__ Hp, PathArrays A, RenderParams R,
         int qi, int betaIn, DeviceCounters *cnt) {
     const DScene &S = *Sp;

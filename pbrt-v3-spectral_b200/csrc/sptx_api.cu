@@ -8,6 +8,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <string>
+#include <chrono>
 #include <vector>
 
 #include "setup.cuh"
@@ -328,8 +329,20 @@ extern "C" int sptx_upload_scene(sptx_ctx *ctx, const sptx_scene_desc *sc) {
     if (rc) return rc;
     CK(cudaSetDevice(ctx->device));
     CK(cudaStreamSynchronize(ctx->stream));
+    // SPTX_TRACE_UPLOAD=1: wall time of each phase (stream drained at every mark), to stderr
+    const bool trace = getenv("SPTX_TRACE_UPLOAD") != nullptr;
+    auto tPrev = std::chrono::steady_clock::now();
+    auto mark = [&](const char *what) {
+        if (!trace) return;
+        cudaStreamSynchronize(ctx->stream);
+        auto now = std::chrono::steady_clock::now();
+        fprintf(stderr, "sptx_upload_scene: %-18s %8.3f ms\n", what,
+                std::chrono::duration<double, std::milli>(now - tPrev).count());
+        tPrev = now;
+    };
     free_pool(ctx->sceneAllocs);
     ctx->haveScene = false;
+    mark("free");
     std::vector<void *> &pool = ctx->sceneAllocs;
     DScene &S = ctx->S;
     memset(&S, 0, sizeof(S));
@@ -468,7 +481,9 @@ extern "C" int sptx_upload_scene(sptx_ctx *ctx, const sptx_scene_desc *sc) {
         float *tables;
         if ((rc = dalloc(ctx, pool, nVox * rowFloats, &tables))) return rc;
         S.voxel_tables = tables;
+        mark("arrays");
         k_voxel_tables<<<grid_for(ctx, nVox, 64), 64, 0, ctx->stream>>>(S, dH5, tables);
+        mark("voxel tables");
     }
 
     // ---- camera ----
@@ -540,6 +555,7 @@ extern "C" int sptx_upload_scene(sptx_ctx *ctx, const sptx_scene_desc *sc) {
     CK(cudaMemcpyAsync(ctx->dH, &ctx->H, sizeof(DSampler), cudaMemcpyHostToDevice, ctx->stream));
     CK(cudaGetLastError());
     CK(cudaStreamSynchronize(ctx->stream));
+    mark("sampler+film");
     ctx->haveScene = true;
     return SPTX_OK;
 }
@@ -721,7 +737,7 @@ static int render_pixels(sptx_ctx *ctx, const std::vector<int2> &pixels, int s0,
             const int g = grid_for(ctx, nPaths);
             // one resident block per SM; chunks = class queues in block-sized pieces
             const int gShade = (int)std::min<int64_t>((nPaths + kShadeBlock - 1) / kShadeBlock + kShadeClasses,
-                                                     (int64_t)ctx->smCount);
+                                                     (int64_t)ctx->smCount * kShadeBlocksPerSM);
             for (int band = 0; band < nBands; ++band) {
                 // ray.wavelength = middle of the band (integrators/spectralpath.cpp:240-268);
                 // one band = PathIntegrator at 550 nm
