@@ -1,4 +1,4 @@
-"""Parity at the full sizes of BASELINE.json's configurations (C1, C3, C4).
+"""Parity at the full sizes of BASELINE.json's configurations (C1 .. C5).
 
 The fixtures are reference outputs reduced to a committable size by tools/make_configs.py
 (block means of the reference's .dat; reference hits of a seeded sub-batch).  The large scene
@@ -54,6 +54,31 @@ def test_c1_killeroo_400x400_64spp(capi):
     """BASELINE config 1: the reference's own CPU-runnable case, at its full size."""
     ctx = _ctx(capi, "killeroo400")
     _check_render(ctx, golden("c1_killeroo400"), 0.005)
+    ctx.close()
+
+
+def test_c2_cornell_1024(capi):
+    """BASELINE config 2 (the bench workload) at its resolution, first 4 sample numbers of the same
+    Halton streams as the reference."""
+    ctx = _ctx(capi, "cornell1024")
+    _check_render(ctx, golden("c2_cornell1024"), 0.005)
+    ctx.close()
+
+
+def test_c5_cornell_4k_sample_partitions_sum_to_the_whole(capi):
+    """BASELINE config 5 geometry (3840x2160): the reference's 2-spp render, and partitioning B of
+    SURVEY 8(e) on one device -- two 'ranks' render one sample number each into their own film,
+    the films' sum is the whole render (what sptx_film_merge_peers adds up across GPUs)."""
+    ctx = _ctx(capi, "cornell3840x2160")
+    g = golden("c5_cornell4k")
+    w, h = [int(v) for v in g["res"]]
+    whole = _check_render(ctx, g, 0.005)
+    parts = []
+    for r in range(2):
+        ctx.film_clear()
+        ctx.render(r, r + 1)
+        parts.append(ctx.film_pack_dat(w, h))
+    np.testing.assert_allclose(parts[0] + parts[1], whole, rtol=1e-5, atol=1e-7)
     ctx.close()
 
 

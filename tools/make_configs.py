@@ -2,6 +2,8 @@
 """Scene blobs + reference fixtures for the full-size configurations of BASELINE.json.
 
     C1  killeroo400       scenes/killeroo-simple.pbrt, 400x400, 64 spp (the reference's own case)
+    C2  cornell1024       procedural spectral Cornell box, 1024x1024 (the bench workload)
+    C5  cornell3840x2160  the same scene at 4K (multi-GPU configuration)
     C3  cornell_lens2048  RealisticCamera double-Gauss, 2048x2048, 256 spp (lens-tracing path)
     C4  instanced_c4      100 instances of a 199,712-triangle mesh (2.0e7 instanced triangles)
 
@@ -10,6 +12,8 @@ Blobs go to scenes/_gen/ (git-ignored for the large ones; they travel to the GPU
 tree).  Fixtures are reference outputs reduced to a committable size:
     c1: the reference's 64-spp .dat as 8x8 block means          -> tests/golden/c1_killeroo400.npz
     c3: the reference's 2-spp .dat as 16x16 block means         -> tests/golden/c3_cornell_lens2048.npz
+    c2: the reference's 4-spp .dat as 8x8 block means           -> tests/golden/c2_cornell1024.npz
+    c5: the reference's 2-spp .dat as 16x16 block means         -> tests/golden/c5_cornell4k.npz
     c4: Scene::Intersect / IntersectP of the first 2^17 rays of the seeded incoherent batch
         (tools/config_rays.py)                                  -> tests/golden/c4_instanced.npz
 """
@@ -96,7 +100,35 @@ def c4():
           (n_sub, (hits["prim"] >= 0).mean(), hits["n_nodes"].mean(), hits["n_tests"].mean()))
 
 
+def cornell_config(tag, name, res, spp_full, spp_ref, block):
+    """C2 / C5: the procedural Cornell box at the configuration's resolution.  The blob carries the
+    configuration's spp; the reference renders the first `spp_ref` sample numbers of the same
+    Halton streams (the whole job would take the host cores of this container hours)."""
+    w, h = res
+    with tempfile.TemporaryDirectory() as work:
+        pbrt = os.path.join(work, name + ".pbrt")
+        mg.run([sys.executable, os.path.join(ROOT, "scenes", "gen_scenes.py"), "cornell", pbrt,
+                f"res={w}x{h}", f"spp={spp_full}"])
+        flatten(pbrt, os.path.join(mg.GEN, name + ".sptx"), work)
+        pbrt2 = os.path.join(work, name + "_ref.pbrt")
+        mg.run([sys.executable, os.path.join(ROOT, "scenes", "gen_scenes.py"), "cornell", pbrt2,
+                f"res={w}x{h}", f"spp={spp_ref}"])
+        mg.run([mg.PBRT_REF, "--quiet", "--nthreads", NT, pbrt2], cwd=work)
+        dat = capi.read_dat(os.path.join(work, name + "_ref.dat"))
+    np.savez_compressed(os.path.join(mg.GOLD, tag + ".npz"), res=np.array([w, h]), spp=np.array(spp_ref),
+                        block=np.array(block), means=block_means(dat, block), bin_sums=dat.sum(axis=(1, 2)))
+    print("%s: dat mean %.5f" % (tag, dat.mean()))
+
+
+def c2():
+    cornell_config("c2_cornell1024", "cornell1024", (1024, 1024), 1024, 4, 8)
+
+
+def c5():
+    cornell_config("c5_cornell4k", "cornell3840x2160", (3840, 2160), 4096, 2, 16)
+
+
 if __name__ == "__main__":
-    todo = sys.argv[1:] or ["c1", "c3", "c4"]
+    todo = sys.argv[1:] or ["c1", "c2", "c3", "c4", "c5"]
     for t in todo:
-        {"c1": c1, "c3": c3, "c4": c4}[t]()
+        {"c1": c1, "c2": c2, "c3": c3, "c4": c4, "c5": c5}[t]()
