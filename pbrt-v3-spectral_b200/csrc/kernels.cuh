@@ -6,6 +6,13 @@
 namespace sptx {
 
 constexpr int kBlock = 128;
+// resident blocks per SM the traversal kernels are compiled for (register budget = 65536 / (128 * n))
+#ifndef SPTX_TRAV_BLOCKS
+#define SPTX_TRAV_BLOCKS 6
+#endif
+#ifndef SPTX_ANYHIT_BLOCKS
+#define SPTX_ANYHIT_BLOCKS 8
+#endif
 
 // ---- K1: camera samples -> path state ---------------------------------------
 // Sampler::GetCameraSample (core/sampler.cpp:46-52) + GenerateRayDifferential +
@@ -57,7 +64,7 @@ __global__ void k_generate(DScene S, DCamera C, DSampler H, PathArrays A, Render
 
 // ---- K2: closest hit for the active queue ------------------------------------
 template <bool COUNT>
-__global__ void __launch_bounds__(kBlock, 6)
+__global__ void __launch_bounds__(kBlock, SPTX_TRAV_BLOCKS)
 k_intersect(DScene S, PathArrays A, int qi, DeviceCounters *cnt) {
     const int n = A.counters[qi];
     const int *queue = A.q[qi];
