@@ -47,6 +47,7 @@
 #include "materials/metal.h"
 #include "materials/mirror.h"
 #include "materials/plastic.h"
+#include "materials/uber.h"
 #include "memory.h"
 #include "microfacet.h"
 #include "primitive.h"
@@ -157,9 +158,22 @@ bool Builder::CheckMaterialTextures(const Material *m) {
             return Fail("mirror: only constant textures are supported");
         return true;
     }
+    if (auto *x = dynamic_cast<const UberMaterial *>(m)) {
+        // src/materials/uber.cpp:44-92: up to five lobes, all of types the
+        // device already evaluates (SpecularTransmission for 1 - opacity,
+        // Lambertian, Trowbridge-Reitz microfacet and specular reflection with
+        // a dielectric Fresnel term, SpecularTransmission for Kt)
+        if (x->bumpMap) return Fail("uber: bumpmap is not supported");
+        if (!IsConstant(x->Kd) || !IsConstant(x->Ks) || !IsConstant(x->Kr) ||
+            !IsConstant(x->Kt) || !IsConstant(x->opacity) ||
+            !IsConstant(x->roughness) || !IsConstant(x->roughnessu) ||
+            !IsConstant(x->roughnessv) || !IsConstant(x->eta))
+            return Fail("uber: only constant textures are supported");
+        return true;
+    }
     return Fail(
         "material type is outside the GPU hot path (supported: matte, "
-        "plastic, glass, metal, mirror)");
+        "plastic, glass, metal, mirror, uber)");
 }
 
 bool Builder::AddLobe(const BxDF *b) {

@@ -94,6 +94,44 @@ def cornell_world():
     return s
 
 
+def uber_world():
+    """The Cornell box with Material "uber" everywhere (src/materials/uber.cpp): diffuse + glossy
+    walls, a partly transparent wall (opacity < 1: the pass-through SpecularTransmission lobe), a
+    specular reflect + transmit sphere (Kr, Kt, index) and a default uber sphere."""
+    s = "WorldBegin\n"
+    s += 'AttributeBegin\n  Material "matte" "spectrum Kd" [400 0 700 0]\n'
+    s += '  AreaLightSource "diffuse" "blackbody L" [6500 15]\n'
+    s += "  " + quad((-.25, .99, -.25), (.25, .99, -.25), (.25, .99, .25), (-.25, .99, .25))
+    s += "AttributeEnd\n"
+    s += (f'AttributeBegin\n  Material "uber" "spectrum Kd" {WHITE} "spectrum Ks" [400 .2 700 .1] '
+          '"float roughness" [.2]\n')
+    s += "  " + quad((-1, -1, -1), (1, -1, -1), (1, 1, -1), (-1, 1, -1))      # back
+    s += "  " + quad((-1, -1, 1), (1, -1, 1), (1, -1, -1), (-1, -1, -1))      # floor
+    s += "  " + quad((-1, 1, -1), (1, 1, -1), (1, 1, 1), (-1, 1, 1))          # ceiling
+    s += "AttributeEnd\n"
+    # a matte wall behind the partly transparent one, so that what passes through lands somewhere
+    s += f'AttributeBegin\n  Material "matte" "spectrum Kd" {GREEN}\n'
+    s += "  " + quad((-1.4, -1, 1), (-1.4, -1, -1), (-1.4, 1, -1), (-1.4, 1, 1)) + "AttributeEnd\n"
+    s += (f'AttributeBegin\n  Material "uber" "spectrum Kd" {RED} "spectrum Ks" [400 0 700 0] '
+          '"spectrum opacity" [400 .7 550 .5 700 .3]\n')
+    s += "  " + quad((-1, -1, 1), (-1, -1, -1), (-1, 1, -1), (-1, 1, 1)) + "AttributeEnd\n"
+    s += (f'AttributeBegin\n  Material "uber" "spectrum Kd" {GREEN} "float uroughness" [.05] '
+          '"float vroughness" [.3] "bool remaproughness" "false"\n')
+    s += "  " + quad((1, -1, -1), (1, -1, 1), (1, 1, 1), (1, 1, -1)) + "AttributeEnd\n"
+    s += ('AttributeBegin\n  Material "uber" "spectrum Kd" [400 0 700 0] "spectrum Ks" [400 0 700 0] '
+          '"spectrum Kr" [400 .9 700 .7] "spectrum Kt" [400 .6 700 .9] "float index" [1.5]\n'
+          '  Translate .45 -.65 .3\n  Shape "sphere" "float radius" [.35]\nAttributeEnd\n')
+    s += ('AttributeBegin\n  Material "uber"\n  Translate -.45 -.6 -.3\n'
+          '  Shape "sphere" "float radius" [.4]\nAttributeEnd\n')
+    s += "WorldEnd\n"
+    return s
+
+
+def uber_box(opts, out):
+    cam = 'LookAt 0 0 3.8  0 0 0  0 1 0\nCamera "perspective" "float fov" [39]'
+    return header(opts, cam, os.path.splitext(os.path.basename(out))[0]) + uber_world()
+
+
 def cornell(opts, out):
     cam = 'LookAt 0 0 3.8  0 0 0  0 1 0\nCamera "perspective" "float fov" [39]'
     return header(opts, cam, os.path.splitext(os.path.basename(out))[0]) + cornell_world()
@@ -239,6 +277,8 @@ def main(argv):
             opts[k] = v
     if name == "cornell":
         text = cornell(opts, out)
+    elif name == "uber_box":
+        text = uber_box(opts, out)
     elif name == "cornell_lens":
         text = cornell_lens(opts, out)
     elif name == "instanced":
