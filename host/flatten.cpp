@@ -47,6 +47,8 @@
 #include "materials/metal.h"
 #include "materials/mirror.h"
 #include "materials/plastic.h"
+#include "materials/substrate.h"
+#include "materials/translucent.h"
 #include "materials/uber.h"
 #include "memory.h"
 #include "microfacet.h"
@@ -171,9 +173,27 @@ bool Builder::CheckMaterialTextures(const Material *m) {
             return Fail("uber: only constant textures are supported");
         return true;
     }
+    if (auto *x = dynamic_cast<const TranslucentMaterial *>(m)) {
+        // src/materials/translucent.cpp:45-83: Lambertian reflection and
+        // transmission, microfacet reflection and transmission
+        if (x->bumpMap) return Fail("translucent: bumpmap is not supported");
+        if (!IsConstant(x->Kd) || !IsConstant(x->Ks) ||
+            !IsConstant(x->roughness) || !IsConstant(x->reflect) ||
+            !IsConstant(x->transmit))
+            return Fail("translucent: only constant textures are supported");
+        return true;
+    }
+    if (auto *x = dynamic_cast<const SubstrateMaterial *>(m)) {
+        // src/materials/substrate.cpp:45-65: one FresnelBlend lobe
+        if (x->bumpMap) return Fail("substrate: bumpmap is not supported");
+        if (!IsConstant(x->Kd) || !IsConstant(x->Ks) || !IsConstant(x->nu) ||
+            !IsConstant(x->nv))
+            return Fail("substrate: only constant textures are supported");
+        return true;
+    }
     return Fail(
         "material type is outside the GPU hot path (supported: matte, "
-        "plastic, glass, metal, mirror, uber)");
+        "plastic, glass, metal, mirror, uber, translucent, substrate)");
 }
 
 bool Builder::AddLobe(const BxDF *b) {
@@ -234,6 +254,34 @@ bool Builder::AddLobe(const BxDF *b) {
         l.alpha_y = tr->alphay;
         l.sample_visible = tr->sampleVisibleArea ? 1 : 0;
         if (!setFresnel(x->fresnel)) return false;
+    } else if (auto *x = dynamic_cast<const LambertianTransmission *>(b)) {
+        l.type = SPTX_LOBE_LAMBERT_TRANS;
+        l.T = AddSpectrum(x->T);
+    } else if (auto *x = dynamic_cast<const MicrofacetTransmission *>(b)) {
+        l.type = SPTX_LOBE_MICROFACET_TRANS;
+        l.T = AddSpectrum(x->T);
+        l.eta_a = x->etaA;
+        l.eta_b = x->etaB;
+        auto *tr = dynamic_cast<const TrowbridgeReitzDistribution *>(
+            x->distribution);
+        if (!tr)
+            return Fail("only the Trowbridge-Reitz distribution is supported");
+        l.alpha_x = tr->alphax;
+        l.alpha_y = tr->alphay;
+        l.sample_visible = tr->sampleVisibleArea ? 1 : 0;
+        if (x->mode != TransportMode::Radiance)
+            return Fail("importance transport is not on the path");
+    } else if (auto *x = dynamic_cast<const FresnelBlend *>(b)) {
+        l.type = SPTX_LOBE_FRESNEL_BLEND;
+        l.R = AddSpectrum(x->Rd);
+        l.T = AddSpectrum(x->Rs);
+        auto *tr = dynamic_cast<const TrowbridgeReitzDistribution *>(
+            x->distribution);
+        if (!tr)
+            return Fail("only the Trowbridge-Reitz distribution is supported");
+        l.alpha_x = tr->alphax;
+        l.alpha_y = tr->alphay;
+        l.sample_visible = tr->sampleVisibleArea ? 1 : 0;
     } else
         return Fail("BxDF outside the GPU hot path: " + b->ToString());
     fs->lobes.push_back(l);

@@ -115,7 +115,12 @@ enum {
     SPTX_LOBE_SPECULAR_REFL = 2,   /* SpecularReflection                     */
     SPTX_LOBE_SPECULAR_TRANS = 3,  /* SpecularTransmission                   */
     SPTX_LOBE_FRESNEL_SPECULAR = 4,/* FresnelSpecular                        */
-    SPTX_LOBE_MICROFACET_REFL = 5  /* MicrofacetReflection + TrowbridgeReitz */
+    SPTX_LOBE_MICROFACET_REFL = 5, /* MicrofacetReflection + TrowbridgeReitz */
+    SPTX_LOBE_LAMBERT_TRANS = 6,   /* LambertianTransmission (T)             */
+    SPTX_LOBE_MICROFACET_TRANS = 7,/* MicrofacetTransmission + TrowbridgeReitz
+                                      (T, eta_a, eta_b, alphas)              */
+    SPTX_LOBE_FRESNEL_BLEND = 8    /* FresnelBlend + TrowbridgeReitz
+                                      (R = Rd, T = Rs, alphas)               */
 };
 enum { SPTX_FRESNEL_NOOP = 0, SPTX_FRESNEL_DIELECTRIC = 1, SPTX_FRESNEL_CONDUCTOR = 2 };
 

@@ -31,7 +31,17 @@ enum {
     TERM_S_R_DIV = 4,    // s0 * R[b] / s1                  (specular reflection / FresnelSpecular R)
     TERM_COND_R_DIV = 5, // FrCond[b](s0) * R[b] / s1       (specular reflection, conductor)
     TERM_T_S_S_DIV = 6,  // (T[b] * s0) * s1 / s2           (specular transmission)
+    TERM_BLEND = 7,      // FresnelBlend::f: Rd = R, Rs = e0; diffuse and specular scalars s0..s3
 };
+
+// FresnelBlend::f for one bin, core/reflection.cpp:285-299 (+ SchlickFresnel, reflection.h):
+// s0, s1 = 1 - pow5(1 - |cos|/2) for wi and wo, s2 = pow5(1 - wi.wh), s3 = D / (4 |wi.wh| max|cos|).
+SPTX_DEV float blend_bin(float rd, float rs, float s0, float s1, float s2, float s3) {
+    const float kd = 28.f / (23.f * kPi);
+    const float diffuse = rd * kd * (1.f - rs) * s0 * s1;
+    const float schlick = rs + s2 * (1.f - rs);
+    return diffuse + schlick * s3;
+}
 
 struct FTerm {
     int kind;
@@ -106,6 +116,8 @@ SPTX_DEV float fterm_bin(const DScene &S, const FTerm &t, int b) {
         float F = fr_conductor_bin(t.s0, spec(S, t.e0, b), spec(S, t.e1, b), spec(S, t.e2, b));
         return F * spec(S, t.R, b) / t.s1;
     }
+    case TERM_BLEND:
+        return blend_bin(spec(S, t.R, b), spec(S, t.e0, b), t.s0, t.s1, t.s2, t.s3);
     default:  // TERM_T_S_S_DIV
         return (spec(S, t.R, b) * t.s0) * t.s1 / t.s2;
     }
@@ -152,6 +164,12 @@ SPTX_DEV float4 fterm4(const DScene &S, const FTerm &t, int c) {
                            fr_conductor_bin(t.s0, ei.y, et.y, k.y) * R.y / t.s1,
                            fr_conductor_bin(t.s0, ei.z, et.z, k.z) * R.z / t.s1,
                            c < 7 ? fr_conductor_bin(t.s0, ei.w, et.w, k.w) * R.w / t.s1 : 0.f);
+    }
+    case TERM_BLEND: {
+        const float4 rs = spec4(S, t.e0, c);
+        return make_float4(blend_bin(R.x, rs.x, t.s0, t.s1, t.s2, t.s3), blend_bin(R.y, rs.y, t.s0, t.s1, t.s2, t.s3),
+                           blend_bin(R.z, rs.z, t.s0, t.s1, t.s2, t.s3),
+                           c < 7 ? blend_bin(R.w, rs.w, t.s0, t.s1, t.s2, t.s3) : 0.f);
     }
     default:  // TERM_T_S_S_DIV
         return make_float4((R.x * t.s0) * t.s1 / t.s2, (R.y * t.s0) * t.s1 / t.s2,

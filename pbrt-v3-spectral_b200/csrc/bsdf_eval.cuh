@@ -38,6 +38,10 @@ SPTX_DEV int lobe_flags(int type) {
         return BSDF_TRANSMISSION | BSDF_SPECULAR;
     case SPTX_LOBE_FRESNEL_SPECULAR:
         return BSDF_REFLECTION | BSDF_TRANSMISSION | BSDF_SPECULAR;
+    case SPTX_LOBE_LAMBERT_TRANS:
+        return BSDF_TRANSMISSION | BSDF_DIFFUSE;
+    case SPTX_LOBE_MICROFACET_TRANS:
+        return BSDF_TRANSMISSION | BSDF_GLOSSY;
     default:
         return BSDF_REFLECTION | BSDF_GLOSSY;
     }
@@ -102,6 +106,42 @@ SPTX_NOINL void lobe_f(const sptx_lobe &L, V3 wo, V3 wi, FSum *out) {
             t.kind = TERM_MICRO_S;
             t.s2 = (L.fresnel == SPTX_FRESNEL_DIELECTRIC) ? fr_dielectric(c, L.eta_a, L.eta_b) : 1.f;
         }
+    } else if (L.type == SPTX_LOBE_LAMBERT_TRANS) {
+        // LambertianTransmission::f, core/reflection.cpp:187-190
+        t.kind = TERM_R_S;
+        t.R = L.T;
+        t.s0 = kInvPi;
+    } else if (L.type == SPTX_LOBE_MICROFACET_TRANS) {
+        // MicrofacetTransmission::f, core/reflection.cpp:244-266
+        if (same_hemisphere(wo, wi)) return;
+        float cosThetaO = cos_theta(wo), cosThetaI = cos_theta(wi);
+        if (cosThetaI == 0 || cosThetaO == 0) return;
+        float eta = cos_theta(wo) > 0 ? (L.eta_b / L.eta_a) : (L.eta_a / L.eta_b);
+        V3 wh = normalize(wo + wi * eta);
+        if (wh.z < 0) wh = -wh;
+        float F = fr_dielectric(dot(wo, wh), L.eta_a, L.eta_b);
+        float sqrtDenom = dot(wo, wh) + eta * dot(wi, wh);
+        float factor = 1.f / eta;  // TransportMode::Radiance
+        t.kind = TERM_R_S_S;  // ((1 - F) * T[b]) * |...|
+        t.R = L.T;
+        t.s0 = 1.f - F;
+        t.s1 = fabsf(tr_D(L.alpha_x, L.alpha_y, wh) * tr_G(L.alpha_x, L.alpha_y, wo, wi) * eta * eta *
+                     absdot(wi, wh) * absdot(wo, wh) * factor * factor /
+                     (cosThetaI * cosThetaO * sqrtDenom * sqrtDenom));
+    } else if (L.type == SPTX_LOBE_FRESNEL_BLEND) {
+        // FresnelBlend::f, core/reflection.cpp:285-299
+        V3 wh = wi + wo;
+        if (wh.x == 0 && wh.y == 0 && wh.z == 0) return;
+        wh = normalize(wh);
+        const float a = 1.f - .5f * abs_cos_theta(wi), b = 1.f - .5f * abs_cos_theta(wo);
+        const float c = 1.f - dot(wi, wh);
+        t.kind = TERM_BLEND;
+        t.e0 = L.T;  // Rs
+        t.s0 = 1.f - (a * a) * (a * a) * a;
+        t.s1 = 1.f - (b * b) * (b * b) * b;
+        t.s2 = (c * c) * (c * c) * c;
+        t.s3 = tr_D(L.alpha_x, L.alpha_y, wh) /
+               (4.f * absdot(wi, wh) * fmaxf(abs_cos_theta(wi), abs_cos_theta(wo)));
     } else
         return;  // specular lobes: f() == 0
     if (out->n < kMaxTerms) out->t[out->n++] = t;
@@ -115,6 +155,24 @@ SPTX_NOINL float lobe_pdf(const sptx_lobe &L, V3 wo, V3 wi) {
         if (!same_hemisphere(wo, wi)) return 0.f;
         V3 wh = normalize(wo + wi);
         return tr_pdf(L, wo, wh) / (4.f * dot(wo, wh));
+    }
+    if (L.type == SPTX_LOBE_LAMBERT_TRANS)  // core/reflection.cpp:400-403
+        return !same_hemisphere(wo, wi) ? abs_cos_theta(wi) * kInvPi : 0.f;
+    if (L.type == SPTX_LOBE_MICROFACET_TRANS) {
+        // MicrofacetTransmission::Pdf, core/reflection.cpp:436-448
+        if (same_hemisphere(wo, wi)) return 0.f;
+        float eta = cos_theta(wo) > 0 ? (L.eta_b / L.eta_a) : (L.eta_a / L.eta_b);
+        V3 wh = normalize(wo + wi * eta);
+        float sqrtDenom = dot(wo, wh) + eta * dot(wi, wh);
+        float dwh_dwi = fabsf((eta * eta * dot(wi, wh)) / (sqrtDenom * sqrtDenom));
+        return tr_pdf(L, wo, wh) * dwh_dwi;
+    }
+    if (L.type == SPTX_LOBE_FRESNEL_BLEND) {
+        // FresnelBlend::Pdf, core/reflection.cpp:470-475
+        if (!same_hemisphere(wo, wi)) return 0.f;
+        V3 wh = normalize(wo + wi);
+        float pdf_wh = tr_pdf(L, wo, wh);
+        return .5f * (abs_cos_theta(wi) * kInvPi + pdf_wh / (4.f * dot(wo, wh)));
     }
     return 0.f;  // specular lobes
 }
@@ -197,6 +255,29 @@ SPTX_NOINL void bsdf_sample_f(const DScene &S, const Bsdf &b, V3 woW, V2 u, int 
         V3 wh = tr_sample_wh(L, wo, ur);
         wi = -wo + 2.f * dot(wo, wh) * wh;  // Reflect(wo, wh)
         if (same_hemisphere(wo, wi)) *pdf = tr_pdf(L, wo, wh) / (4.f * dot(wo, wh));
+    } else if (L.type == SPTX_LOBE_LAMBERT_TRANS) {
+        // LambertianTransmission::Sample_f, core/reflection.cpp:391-398
+        wi = cosine_sample_hemisphere(ur);
+        if (wo.z > 0) wi.z *= -1.f;
+        *pdf = lobe_pdf(L, wo, wi);
+    } else if (L.type == SPTX_LOBE_MICROFACET_TRANS) {
+        // MicrofacetTransmission::Sample_f, core/reflection.cpp:425-434
+        V3 wh = tr_sample_wh(L, wo, ur);
+        float eta = cos_theta(wo) > 0 ? (L.eta_a / L.eta_b) : (L.eta_b / L.eta_a);
+        if (refract(wo, wh, eta, &wi)) *pdf = lobe_pdf(L, wo, wi);
+    } else if (L.type == SPTX_LOBE_FRESNEL_BLEND) {
+        // FresnelBlend::Sample_f, core/reflection.cpp:450-468
+        if (ur.x < .5f) {
+            V2 u2{fminf(2.f * ur.x, kOneMinusEpsilon), ur.y};
+            wi = cosine_sample_hemisphere(u2);
+            if (wo.z < 0) wi.z *= -1.f;
+            *pdf = lobe_pdf(L, wo, wi);
+        } else {
+            V2 u2{fminf(2.f * (ur.x - .5f), kOneMinusEpsilon), ur.y};
+            V3 wh = tr_sample_wh(L, wo, u2);
+            wi = -wo + 2.f * dot(wo, wh) * wh;  // Reflect(wo, wh)
+            if (same_hemisphere(wo, wi)) *pdf = lobe_pdf(L, wo, wi);
+        }
     } else if (L.type == SPTX_LOBE_SPECULAR_REFL) {
         // SpecularReflection::Sample_f, core/reflection.cpp:136-143
         wi = mk(-wo.x, -wo.y, wo.z);

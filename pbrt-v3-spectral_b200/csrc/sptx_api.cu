@@ -265,13 +265,22 @@ static int validate_scene(sptx_ctx *ctx, const sptx_scene_desc *sc) {
         REQ(m.n_lobes >= 0 && m.n_lobes <= 8 && m.first_lobe >= 0 &&
                 (int64_t)m.first_lobe + m.n_lobes <= sc->n_lobes,
             "material lobe range");
-        if (m.n_lobes > kMaxTerms)
-            return fail(ctx, SPTX_EUNSUPPORTED, "sptx_upload_scene: material with %d lobes (max %d)",
-                        m.n_lobes, kMaxTerms);
+        // BSDF::f sums the non-specular lobes only (specular lobes evaluate to zero)
+        int nonSpecular = 0;
+        for (int l = 0; l < m.n_lobes; ++l) {
+            const int ty = sc->lobes[m.first_lobe + l].type;
+            if (ty != SPTX_LOBE_SPECULAR_REFL && ty != SPTX_LOBE_SPECULAR_TRANS &&
+                ty != SPTX_LOBE_FRESNEL_SPECULAR)
+                ++nonSpecular;
+        }
+        if (nonSpecular > kMaxTerms)
+            return fail(ctx, SPTX_EUNSUPPORTED,
+                        "sptx_upload_scene: material with %d non-specular lobes (max %d)", nonSpecular,
+                        kMaxTerms);
     }
     for (int64_t i = 0; i < sc->n_lobes; ++i) {
         const sptx_lobe &l = sc->lobes[i];
-        REQ(l.type >= SPTX_LOBE_LAMBERT && l.type <= SPTX_LOBE_MICROFACET_REFL, "lobe type");
+        REQ(l.type >= SPTX_LOBE_LAMBERT && l.type <= SPTX_LOBE_FRESNEL_BLEND, "lobe type");
         REQ(l.R < sc->n_spectra && l.T < sc->n_spectra && l.fr_eta_i < sc->n_spectra &&
                 l.fr_eta_t < sc->n_spectra && l.fr_k < sc->n_spectra,
             "lobe spectrum row out of range");

@@ -121,10 +121,51 @@ def uber_world():
     s += ('AttributeBegin\n  Material "uber" "spectrum Kd" [400 0 700 0] "spectrum Ks" [400 0 700 0] '
           '"spectrum Kr" [400 .9 700 .7] "spectrum Kt" [400 .6 700 .9] "float index" [1.5]\n'
           '  Translate .45 -.65 .3\n  Shape "sphere" "float radius" [.35]\nAttributeEnd\n')
-    s += ('AttributeBegin\n  Material "uber"\n  Translate -.45 -.6 -.3\n'
+    # all five lobes at once: pass-through, diffuse, glossy, specular reflection and transmission
+    s += ('AttributeBegin\n  Material "uber" "spectrum Kr" [400 .2 700 .3] "spectrum Kt" [400 .3 700 .2] '
+          '"spectrum opacity" [400 .8 700 .9]\n  Translate -.45 -.6 -.3\n'
           '  Shape "sphere" "float radius" [.4]\nAttributeEnd\n')
     s += "WorldEnd\n"
     return s
+
+
+def lobes_world():
+    """Materials whose lobes go beyond the first five: "substrate" (FresnelBlend), "translucent"
+    (Lambertian and microfacet transmission) and rough "glass" (microfacet reflection +
+    transmission), in the Cornell box."""
+    s = "WorldBegin\n"
+    s += 'AttributeBegin\n  Material "matte" "spectrum Kd" [400 0 700 0]\n'
+    s += '  AreaLightSource "diffuse" "blackbody L" [6500 15]\n'
+    s += "  " + quad((-.25, .99, -.25), (.25, .99, -.25), (.25, .99, .25), (-.25, .99, .25))
+    s += "AttributeEnd\n"
+    s += (f'AttributeBegin\n  Material "substrate" "spectrum Kd" {WHITE} "spectrum Ks" [400 .1 700 .3] '
+          '"float uroughness" [.1] "float vroughness" [.25]\n')
+    s += "  " + quad((-1, -1, -1), (1, -1, -1), (1, 1, -1), (-1, 1, -1))      # back
+    s += "AttributeEnd\n"
+    s += f'AttributeBegin\n  Material "matte" "spectrum Kd" {WHITE}\n'
+    s += "  " + quad((-1, -1, 1), (1, -1, 1), (1, -1, -1), (-1, -1, -1))      # floor
+    s += "  " + quad((-1, 1, -1), (1, 1, -1), (1, 1, 1), (-1, 1, 1))          # ceiling
+    s += "AttributeEnd\n"
+    s += f'AttributeBegin\n  Material "matte" "spectrum Kd" {RED}\n'
+    s += "  " + quad((-1, -1, 1), (-1, -1, -1), (-1, 1, -1), (-1, 1, 1)) + "AttributeEnd\n"
+    s += f'AttributeBegin\n  Material "matte" "spectrum Kd" {GREEN}\n'
+    s += "  " + quad((1, -1, -1), (1, -1, 1), (1, 1, 1), (1, 1, -1)) + "AttributeEnd\n"
+    # a translucent panel standing in the box
+    s += ('AttributeBegin\n  Material "translucent" "spectrum Kd" [400 .5 700 .6] "spectrum Ks" [400 .3 700 .2] '
+          '"spectrum reflect" [400 .6 700 .5] "spectrum transmit" [400 .4 700 .7] "float roughness" [.2]\n')
+    s += "  " + quad((-.9, -1, .2), (-.1, -1, -.5), (-.1, .3, -.5), (-.9, .3, .2)) + "AttributeEnd\n"
+    s += ('AttributeBegin\n  Material "glass" "float index" [1.5] "float uroughness" [.1] "float vroughness" [.2]\n'
+          '  Translate .45 -.65 .3\n  Shape "sphere" "float radius" [.35]\nAttributeEnd\n')
+    s += ('AttributeBegin\n  Material "substrate" "spectrum Kd" [400 .6 700 .2] "spectrum Ks" [400 .5 700 .5] '
+          '"float uroughness" [.05] "float vroughness" [.05] "bool remaproughness" "false"\n'
+          '  Translate .2 -.7 -.45\n  Shape "sphere" "float radius" [.3]\nAttributeEnd\n')
+    s += "WorldEnd\n"
+    return s
+
+
+def lobes_box(opts, out):
+    cam = 'LookAt 0 0 3.8  0 0 0  0 1 0\nCamera "perspective" "float fov" [39]'
+    return header(opts, cam, os.path.splitext(os.path.basename(out))[0]) + lobes_world()
 
 
 def uber_box(opts, out):
@@ -277,6 +318,8 @@ def main(argv):
             opts[k] = v
     if name == "cornell":
         text = cornell(opts, out)
+    elif name == "lobes_box":
+        text = lobes_box(opts, out)
     elif name == "uber_box":
         text = uber_box(opts, out)
     elif name == "cornell_lens":

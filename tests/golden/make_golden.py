@@ -44,6 +44,8 @@ SCENES = {
     "furnace_area": dict(gen=["furnace_area", "res=10", "spp=256", "maxdepth=8"], res=(10, 10), spp=256),
     # Material "uber" (SURVEY 8f rank 4): every lobe combination src/materials/uber.cpp builds
     "uber_box": dict(gen=["uber_box", "res=64", "spp=16"], res=(64, 64), spp=16),
+    # "substrate", "translucent", rough "glass": FresnelBlend, Lambertian / microfacet transmission
+    "lobes_box": dict(gen=["lobes_box", "res=64", "spp=16"], res=(64, 64), spp=16),
     "killeroo128": dict(ref="killeroo-simple.pbrt", res=(128, 128), spp=8),
     # crop = croppedPixelBounds (ceil(res * cropwindow), core/film.cpp:57-63): the film / .dat size
     "zoo": dict(gen=["zoo", "res=96x64", "spp=8", "strategy=power"], res=(96, 64), spp=8, crop=(10, 4, 92, 58)),
