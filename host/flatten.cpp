@@ -541,7 +541,6 @@ bool Builder::AddAggregate(const Primitive *agg, bool topLevel) {
 
 void FlatScene::Finish() {
     desc.abi_version = SPTX_ABI_VERSION;
-    desc.reserved = 0;
 #define SPTX_SET(field, count, vec, div) \
     desc.count = (int64_t)(vec.size() / (div)); \
     desc.field = vec.empty() ? nullptr : vec.data();
@@ -723,6 +722,12 @@ bool FlattenScene(const Scene &scene, const Camera &camera, Sampler &sampler,
     fi.rr_threshold = params.rrThreshold;
     for (int i = 0; i < 4; ++i) fi.pixel_bounds[i] = params.pixelBounds[i];
     fi.num_ca_bands = params.numCABands;
+    out->desc.metadata_strategy = (uint32_t)params.metadataStrategy;
+    if (params.metadataStrategy &&
+        out->desc.sampler.type != SPTX_SAMPLER_HALTON)
+        return fail(
+            "Integrator \"metadata\" is on the GPU hot path for the halton "
+            "sampler only");
     if (params.numCABands > 1 && out->desc.sampler.type != SPTX_SAMPLER_HALTON)
         return fail(
             "spectralpath with numCABands > 1 is on the GPU hot path for the "

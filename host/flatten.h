@@ -31,6 +31,9 @@ struct PathParams {
     // 0: Integrator "path".  >= 1: Integrator "spectralpath", numCABands
     // (src/integrators/spectralpath.cpp:345-378)
     int numCABands = 0;
+    // 0: radiance.  SPTX_METADATA_*: Integrator "metadata"
+    // (src/integrators/metadata.cpp:91-130)
+    int metadataStrategy = 0;
 };
 
 // Owns the flattened arrays; desc points into them.

@@ -37,6 +37,7 @@
 #include "camera.h"
 #include "film.h"
 #include "integrator.h"
+#include "integrators/metadata.h"
 #include "integrators/path.h"
 #include "integrators/spectralpath.h"
 #include "paramset.h"
@@ -206,6 +207,34 @@ SpectralPathIntegrator *CreateSpectralPathIntegrator(
     }
     Integrator *gpu = new GpuPathIntegrator(pp, camera, sampler);
     return reinterpret_cast<SpectralPathIntegrator *>(gpu);
+}
+
+// Integrator "metadata" (src/integrators/metadata.cpp:91-130): the standard
+// sample loop with an Li that returns the first hit's depth, materialId,
+// instanceId or world position in place of radiance (ISET3d's depth maps and
+// label images).  Same binding as the two factories above.
+MetadataIntegrator *CreateMetadataIntegrator(
+    const ParamSet &params, std::shared_ptr<Sampler> sampler,
+    std::shared_ptr<const Camera> camera) {
+    sptx_host::PathParams pp = ReadPathParams(params, *camera);
+    std::string st = params.FindOneString("strategy", "depth");
+    if (st == "depth")
+        pp.metadataStrategy = SPTX_METADATA_DEPTH;
+    else if (st == "material")
+        pp.metadataStrategy = SPTX_METADATA_MATERIAL;
+    else if (st == "mesh")
+        pp.metadataStrategy = SPTX_METADATA_MESH;
+    else if (st == "coordinates")
+        pp.metadataStrategy = SPTX_METADATA_COORDINATES;
+    else {
+        Warning(
+            "Strategy \"%s\" for metadata unknown. "
+            "Using \"depth\".",
+            st.c_str());
+        pp.metadataStrategy = SPTX_METADATA_DEPTH;
+    }
+    Integrator *gpu = new GpuPathIntegrator(pp, camera, sampler);
+    return reinterpret_cast<MetadataIntegrator *>(gpu);
 }
 
 }  // namespace pbrt

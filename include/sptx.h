@@ -147,6 +147,8 @@ typedef struct sptx_material {
 } sptx_material;
 
 enum { SPTX_LIGHT_DIFFUSE_AREA = 0, SPTX_LIGHT_POINT = 1 };
+enum { SPTX_METADATA_NONE = 0, SPTX_METADATA_DEPTH = 1, SPTX_METADATA_MATERIAL = 2, SPTX_METADATA_MESH = 3,
+       SPTX_METADATA_COORDINATES = 4 };
 
 /* DiffuseAreaLight (src/lights/diffuse.cpp) or PointLight (src/lights/point.cpp). */
 typedef struct sptx_light {
@@ -226,7 +228,10 @@ typedef struct sptx_integrator {
  * and may free the arrays once sptx_upload_scene returns. */
 typedef struct sptx_scene_desc {
     uint32_t abi_version;
-    uint32_t reserved;
+    uint32_t metadata_strategy; /* 0: radiance (Integrator "path" / "spectralpath").      */
+                                /* SPTX_METADATA_*: Integrator "metadata", whose Li is the */
+                                /* first hit's depth / materialId / instanceId / position  */
+                                /* (src/integrators/metadata.cpp:53-89)                    */
     sptx_camera camera;
     sptx_sampler sampler;
     sptx_film film;

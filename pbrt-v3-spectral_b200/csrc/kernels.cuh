@@ -41,7 +41,7 @@ __global__ void k_generate(DScene S, DCamera C, DSampler H, PathArrays A, Render
         ray.tMax = kInf;
         float w = camera_ray(C, pFilm, pLens, R.wavelength, &ray);
         A.rayA[i] = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.d.x);
-        A.rayB[i] = make_float4(ray.d.y, ray.d.z, 1.f, w);
+        A.rayB[i] = make_float4(ray.d.y, ray.d.z, 1.f, R.ignoreRayWeight ? 1.f : w);
         A.sindex[i] = st.index;
         // SpectralPathIntegrator (integrators/spectralpath.cpp:262-283): the bands of a sample share
         // its CameraSample and draw from ONE sampler stream, band after band -- a band starts at

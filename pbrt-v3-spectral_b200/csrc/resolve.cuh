@@ -113,6 +113,39 @@ k_resolve(DScene S, PathArrays A, int betaIn, DeviceCounters *cnt) {
     if (lane == 0 && nShadow) atomicAdd(&cnt->shadowRays, nShadow);
 }
 
+// ---- MetadataIntegrator::Li (integrators/metadata.cpp:53-89) ---------------------
+// The first hit's depth |p - o|, materialId, instanceId (every bin), or world position
+// (bins 0..2); paths that hit nothing keep L = 0.  Runs over the active queue after K2.
+__global__ void k_metadata(DScene S, PathArrays A, int qi, int strategy) {
+    const int n = A.counters[qi];
+    for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
+        const int i = A.q[qi][k];
+        const float4 ra = A.rayA[i], rb = A.rayB[i], ha = A.hitA[i], hb = A.hitB[i];
+        const int prim = __float_as_int(ha.x), inst = __float_as_int(ha.y);
+        if (prim < 0) continue;
+        Ray ray{mk(ra.x, ra.y, ra.z), mk(ra.w, rb.x, rb.y), kInf};
+        Isect it;
+        if (!build_interaction(S, ray, prim, inst, ha.z, ha.w, hb.x, &it)) {
+            atomicOr(A.counters + 3, ERR_INTERACTION);
+            continue;
+        }
+        float v = 0.f;
+        if (strategy == SPTX_METADATA_DEPTH)
+            v = length(it.p - ray.o);
+        else if (strategy == SPTX_METADATA_MATERIAL)
+            v = (float)(uint32_t)S.materials[it.material].material_id;
+        else if (strategy == SPTX_METADATA_MESH)  // SurfaceInteraction::instanceId defaults to 0
+            v = inst >= 0 ? (float)(uint32_t)S.instances[inst].instance_id : 0.f;
+        float *Lp = A.L + (size_t)i * SPTX_SPECTRUM_STRIDE;
+        if (strategy == SPTX_METADATA_COORDINATES) {
+            Lp[0] = it.p.x;
+            Lp[1] = it.p.y;
+            Lp[2] = it.p.z;
+        } else
+            for (int b = 0; b < SPTX_NBINS; ++b) Lp[b] = v;
+    }
+}
+
 // ---- band merge of SpectralPathIntegrator --------------------------------------
 // integrators/spectralpath.cpp:284-318: the radiance of a band's path goes through the
 // NaN / negative / infinite-luminance guard, then only the band's bins [lo, hi) are copied into

@@ -36,6 +36,7 @@ struct sptx_ctx {
     // pinned staging for film downloads, and the device pixel list of the last render region
     float *dFilmSplit = nullptr;  // [P][31] contrib + [P] weight, the download layout
     size_t dFilmSplitFloats = 0;
+    int metadataStrategy = 0;     // SPTX_METADATA_*: Integrator "metadata" instead of radiance
     float *dLacc = nullptr;       // [P][32] merged spectrum of a sample's bands (num_ca_bands > 1)
     int64_t dLaccPaths = 0;
     int2 *dPixels = nullptr;
@@ -421,6 +422,9 @@ extern "C" int sptx_upload_scene(sptx_ctx *ctx, const sptx_scene_desc *sc) {
 
     // ---- light selection (core/lightdistrib.cpp:48-66) ----
     ctx->integ = sc->integrator;
+    if (sc->metadata_strategy > SPTX_METADATA_COORDINATES)
+        return fail(ctx, SPTX_EINVAL, "sptx_upload_scene: metadata strategy %u", sc->metadata_strategy);
+    ctx->metadataStrategy = (int)sc->metadata_strategy;
     const int nL = S.n_lights;
     int strategy = sc->integrator.light_strategy;
     if (nL == 1) strategy = SPTX_LIGHTS_UNIFORM;
@@ -633,6 +637,9 @@ static int render_serial(sptx_ctx *ctx, const int32_t *bounds, int part, int nPa
         return fail(ctx, SPTX_EUNSUPPORTED,
                     "render: RandomSampler streams run through all %d samples of a tile; sample range "
                     "[%d,%d) cannot be rendered on its own", ctx->H.s.spp, s0, s1);
+    if (ctx->metadataStrategy)
+        return fail(ctx, SPTX_EUNSUPPORTED,
+                    "render: Integrator \"metadata\" with the RandomSampler is not on the device path");
     if (ctx->integ.num_ca_bands > 1)
         return fail(ctx, SPTX_EUNSUPPORTED,
                     "render: SpectralPathIntegrator bands (numCABands = %d) with the RandomSampler are "
@@ -742,12 +749,31 @@ static int render_pixels(sptx_ctx *ctx, const std::vector<int2> &pixels, int s0,
             R.rrThreshold = ctx->integ.rr_threshold;
             R.pixels = dPixels + p0;
             R.sampleList = dSampleList;
+            R.ignoreRayWeight = ctx->metadataStrategy && !dSampleList;
             const int64_t nPaths = (int64_t)nPix * R.samplesInPass;
             const int g = grid_for(ctx, nPaths);
             // one resident block per SM; chunks = class queues in block-sized pieces
             const int gShade = (int)std::min<int64_t>((nPaths + kShadeBlock - 1) / kShadeBlock + kShadeClasses,
                                                      (int64_t)ctx->smCount * kShadeBlocksPerSM);
-            for (int band = 0; band < nBands; ++band) {
+            if (ctx->metadataStrategy && !dSampleList) {
+                // MetadataIntegrator: camera ray, closest hit, the hit's attribute as "radiance"
+                R.band = 0;
+                R.nBands = 1;
+                R.wavelength = 550.f;
+                k_set_counters<<<1, 1, 0, ctx->stream>>>(A.counters, 0, 0, 1, 0);
+                k_reset_bounce<<<1, 32, 0, ctx->stream>>>(A.counters, 1);
+                launches += 2;
+                tic(0);
+                k_generate<<<g, kBlock, 0, ctx->stream>>>(ctx->S, ctx->C, ctx->H, A, R, ctx->dCnt);
+                toc();
+                tic(1);
+                k_intersect<false><<<g, kBlock, 0, ctx->stream>>>(ctx->S, A, 0, ctx->dCnt);
+                toc();
+                tic(2);
+                k_metadata<<<g, kBlock, 0, ctx->stream>>>(ctx->S, A, 0, ctx->metadataStrategy);
+                toc();
+            }
+            for (int band = 0; band < (ctx->metadataStrategy && !dSampleList ? 0 : nBands); ++band) {
                 // ray.wavelength = middle of the band (integrators/spectralpath.cpp:240-268);
                 // one band = PathIntegrator at 550 nm
                 R.band = band;

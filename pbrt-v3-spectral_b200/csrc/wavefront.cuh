@@ -53,6 +53,9 @@ struct RenderParams {
     float rrThreshold;
     const int2 *pixels;  // [nPix] pixel coordinates
     float wavelength;    // ray.wavelength (550 for PathIntegrator)
+    int ignoreRayWeight; // MetadataIntegrator::IgnoreRayWeight (integrators/metadata.h:64): the film
+                         // weight of a sample is 1 (core/integrator.cpp:320-321); the camera's
+                         // weight still gates Li
     int band, nBands;    // SpectralPathIntegrator: this launch traces band `band` of `nBands`
     const int *sampleList;  // debug: explicit sample number per path (or NULL)
 };

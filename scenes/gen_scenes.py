@@ -58,7 +58,9 @@ def header(opts, camera, name):
              f'"string filename" "{name}.exr"')
     s.append(f'Sampler "{opts.get("sampler", "halton")}" "integer pixelsamples" [{opts["spp"]}]')
     integ = 'Integrator "path"'
-    if "bands" in opts:  # SpectralPathIntegrator: one path per wavelength band
+    if "metadata" in opts:  # MetadataIntegrator: depth / material / mesh / coordinates
+        integ = f'Integrator "metadata" "string strategy" "{opts["metadata"]}"'
+    elif "bands" in opts:  # SpectralPathIntegrator: one path per wavelength band
         integ = f'Integrator "spectralpath" "integer numCABands" [{int(opts["bands"])}]'
     s.append(f'{integ} "integer maxdepth" [{opts["maxdepth"]}] '
              f'"string lightsamplestrategy" "{opts["strategy"]}"')

@@ -223,6 +223,34 @@ BAND_SCENES = {
 }
 
 
+# MetadataIntegrator fixtures: the reference's render only
+META_SCENES = {
+    "meta_depth": dict(gen=["instanced", "res=64", "spp=4", "grid=48", "inst=3", "metadata=depth"], res=(64, 64), spp=4),
+    "meta_mesh": dict(gen=["instanced", "res=64", "spp=4", "grid=48", "inst=3", "metadata=mesh"], res=(64, 64), spp=4),
+    "meta_material": dict(gen=["cornell", "res=48", "spp=2", "metadata=material"], res=(48, 48), spp=2),
+    "meta_coordinates": dict(gen=["cornell_lens", "res=48", "spp=2", "metadata=coordinates"], res=(48, 48), spp=2),
+}
+
+
+def make_meta(name):
+    spec = META_SCENES[name]
+    gen = spec["gen"]
+    with tempfile.TemporaryDirectory() as work:
+        pbrt = os.path.join(work, name + ".pbrt")
+        run([sys.executable, os.path.join(ROOT, "scenes", "gen_scenes.py"), gen[0], pbrt] + gen[1:])
+        blob = os.path.join(GEN, name + ".sptx")
+        run([PBRT_B200, "--quiet", pbrt], env={"SPTX_DUMP_SCENE": blob, "SPTX_DUMP_ONLY": "1"}, cwd=work)
+        run([PBRT_REF, "--quiet", "--nthreads", "8", pbrt], cwd=work)
+        sys.path.insert(0, ROOT)
+        import importlib
+        capi = importlib.import_module("pbrt-v3-spectral_b200.capi")
+        dat = capi.read_dat(os.path.join(work, name + ".dat")).astype(np.float32)
+    np.savez_compressed(os.path.join(GOLD, name + ".npz"), res=np.array(spec["res"]), spp=np.array(spec["spp"]),
+                        dat=dat)
+    print(f"{name}: dat mean {dat.mean():.4f}, bins 0..3 {np.array2string(dat.mean(axis=(1, 2))[:4], precision=4)}, "
+          f"{len(np.unique(dat[0]))} distinct values in bin 0")
+
+
 def band_wavelengths(n_bands):
     """ray.wavelength of each band, integrators/spectralpath.cpp:240-268 (float arithmetic)."""
     delta_index = int(np.floor(np.float32(31) / np.float32(n_bands) + 0.5))  # round(), positive argument
@@ -294,11 +322,13 @@ def read_root_bounds(blob):
 
 
 if __name__ == "__main__":
-    names = sys.argv[1:] or list(SCENES) + ["cornell_random"] + list(BAND_SCENES)
+    names = sys.argv[1:] or list(SCENES) + ["cornell_random"] + list(BAND_SCENES) + list(META_SCENES)
     for n in names:
         if n == "cornell_random":
             make_random(n)
         elif n in BAND_SCENES:
             make_bands(n)
+        elif n in META_SCENES:
+            make_meta(n)
         else:
             make(n)

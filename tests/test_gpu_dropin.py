@@ -23,6 +23,8 @@ CASES = {
     "cornell64": ["cornell", "res=64", "spp=16"],
     "cornell_lens_ca": ["cornell_lens", "res=48", "spp=8", "bands=4", "ca=true"],
     "zoo_gauss": ["zoo", "res=64x48", "spp=4", "strategy=uniform", "filter=gaussian"],
+    "lobes_box": ["lobes_box", "res=64", "spp=16"],
+    "meta_depth": ["instanced", "res=64", "spp=4", "grid=48", "inst=3", "metadata=depth"],
 }
 
 
