@@ -57,6 +57,8 @@
 #include "sampler.h"
 #include "samplers/halton.h"
 #include "samplers/random.h"
+#include "samplers/sobol.h"
+#include "sobolmatrices.h"
 #include "scene.h"
 #include "shapes/sphere.h"
 #include "shapes/triangle.h"
@@ -709,12 +711,36 @@ bool FlattenScene(const Scene &scene, const Camera &camera, Sampler &sampler,
             HaltonSampler::radicalInversePermutations;
         if (perms.size() < nperm) return fail("Halton permutations missing");
         out->perms.assign(perms.begin(), perms.begin() + nperm);
+    } else if (auto *sb = dynamic_cast<SobolSampler *>(&sampler)) {
+        // SobolSampler (src/samplers/sobol.cpp): index from the pixel and the
+        // sample number through the two 64-bit van der Corput / Sobol' matrices
+        // of this resolution, values from SobolMatrices32.
+        fsm.type = SPTX_SAMPLER_SOBOL;
+        fsm.log2_resolution = sb->log2Resolution;
+        if (!sb->samples1DArraySizes.empty() || !sb->samples2DArraySizes.empty())
+            return fail("sampler array requests are not on the path");
+        int dims = 5 + 8 * (std::max(params.maxDepth, 0) + 2) *
+                           std::max(params.numCABands, 1);
+        dims = std::min(std::max(dims, 64), (int)NumSobolDimensions);
+        fsm.n_dims = dims;
+        out->primes.resize((size_t)dims * SobolMatrixSize);
+        std::memcpy(out->primes.data(), SobolMatrices32,
+                    out->primes.size() * sizeof(int32_t));
+        out->primeSums.assign((size_t)4 * SobolMatrixSize, 0);
+        if (sb->log2Resolution > 0) {
+            std::memcpy(out->primeSums.data(),
+                        VdCSobolMatrices[sb->log2Resolution - 1],
+                        SobolMatrixSize * sizeof(uint64_t));
+            std::memcpy(out->primeSums.data() + 2 * SobolMatrixSize,
+                        VdCSobolMatricesInv[sb->log2Resolution - 1],
+                        SobolMatrixSize * sizeof(uint64_t));
+        }
     } else if (dynamic_cast<RandomSampler *>(&sampler)) {
         fsm.type = SPTX_SAMPLER_RANDOM;
     } else
         return fail(
             "sampler type is outside the GPU hot path (supported: halton, "
-            "random)");
+            "sobol, random)");
 
     // ---- integrator
     sptx_integrator &fi = out->desc.integrator;
@@ -724,14 +750,14 @@ bool FlattenScene(const Scene &scene, const Camera &camera, Sampler &sampler,
     fi.num_ca_bands = params.numCABands;
     out->desc.metadata_strategy = (uint32_t)params.metadataStrategy;
     if (params.metadataStrategy &&
-        out->desc.sampler.type != SPTX_SAMPLER_HALTON)
+        out->desc.sampler.type == SPTX_SAMPLER_RANDOM)
         return fail(
             "Integrator \"metadata\" is on the GPU hot path for the halton "
-            "sampler only");
-    if (params.numCABands > 1 && out->desc.sampler.type != SPTX_SAMPLER_HALTON)
+            "and sobol samplers only");
+    if (params.numCABands > 1 && out->desc.sampler.type == SPTX_SAMPLER_RANDOM)
         return fail(
             "spectralpath with numCABands > 1 is on the GPU hot path for the "
-            "halton sampler only");
+            "halton and sobol samplers only");
     if (params.lightSampleStrategy == "uniform")
         fi.light_strategy = SPTX_LIGHTS_UNIFORM;
     else if (params.lightSampleStrategy == "power")

@@ -180,7 +180,7 @@ typedef struct sptx_camera {
     float pad[3];
 } sptx_camera;
 
-enum { SPTX_SAMPLER_HALTON = 0, SPTX_SAMPLER_RANDOM = 1 };
+enum { SPTX_SAMPLER_HALTON = 0, SPTX_SAMPLER_RANDOM = 1, SPTX_SAMPLER_SOBOL = 2 };
 
 /* HaltonSampler state, src/samplers/halton.cpp:65-92. */
 typedef struct sptx_sampler {
@@ -192,7 +192,7 @@ typedef struct sptx_sampler {
     int32_t sample_stride;
     int32_t mult_inverse[2];
     int32_t n_dims; /* dimensions covered by primes[]/prime_sums[]/perms[]    */
-    int32_t pad;
+    int32_t log2_resolution; /* SobolSampler::log2Resolution, src/samplers/sobol.h:69 */
 } sptx_sampler;
 
 /* Film, src/core/film.cpp:50-92. Bounds are {x0, y0, x1, y1}. */
@@ -257,6 +257,12 @@ typedef struct sptx_scene_desc {
     int64_t n_lights;     const sptx_light *lights;
     int64_t n_lens_floats;  const float *lens_elements;     /* 4 per element  */
     int64_t n_pupil_floats; const float *exit_pupil_bounds; /* 4 per bound    */
+    /* Sampler tables.  Halton: Primes / PrimeSums / radicalInversePermutations.
+     * Sobol (SPTX_SAMPLER_SOBOL) reuses the first two slots: `primes` holds
+     * SobolMatrices32[0 .. n_dims * 52) (bit patterns), `prime_sums` holds
+     * VdCSobolMatrices[m - 1][0..52) then VdCSobolMatricesInv[m - 1][0..52)
+     * (m = log2_resolution) as little-endian (lo, hi) int32 pairs; `perms` is empty
+     * (src/core/sobolmatrices.h:47-52, src/core/lowdiscrepancy.h:229-274). */
     int64_t n_primes;     const int32_t *primes;     /* Primes[0..n_dims)     */
     int64_t n_prime_sums; const int32_t *prime_sums; /* PrimeSums[0..n_dims)  */
     int64_t n_perms;      const uint16_t *perms; /* radicalInversePermutations */

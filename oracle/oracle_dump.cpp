@@ -259,8 +259,9 @@ void DumpIntegrator::Render(const Scene &scene) {
         if (!ReadAll(halIn, &q)) Error("oracle_dump: cannot read %s", halIn);
         const size_t n = q.size() / 4;
         std::vector<float> out(n);
-        auto *h = dynamic_cast<HaltonSampler *>(real->sampler.get());
-        if (!h) Error("oracle_dump: ORACLE_HALTON_IN needs Sampler \"halton\"");
+        // HaltonSampler and SobolSampler: GlobalSampler::GetIndexForSample / SampleDimension
+        auto *h = dynamic_cast<GlobalSampler *>(real->sampler.get());
+        if (!h) Error("oracle_dump: ORACLE_HALTON_IN needs a GlobalSampler (\"halton\", \"sobol\")");
         for (size_t i = 0; h && i < n; ++i) {
             h->StartPixel(Point2i(q[4 * i], q[4 * i + 1]));
             int64_t idx = h->GetIndexForSample(q[4 * i + 2]);

@@ -26,10 +26,8 @@ __global__ void k_generate(DScene S, DCamera C, DSampler H, PathArrays A, Render
         const int pix = (int)(i % R.nPix);
         const int sampleNum = R.sampleList ? R.sampleList[i] : R.sampleBegin + (int)(i / R.nPix);
         const int2 pxy = R.pixels[pix];
-        const int ox = pxy.x - H.sb[0], oy = pxy.y - H.sb[1];
-        const uint64_t off = H.pixel_offset[(size_t)oy * (H.sb[2] - H.sb[0]) + ox];
         SampleStream st;
-        st.index = off + (uint64_t)sampleNum * (uint64_t)H.s.sample_stride;
+        st.index = sample_index(H, pxy.x, pxy.y, sampleNum);
         st.dim = 0;
         V2 u = get2d(H, st);
         V2 pFilm{(float)pxy.x + u.x, (float)pxy.y + u.y};

@@ -117,8 +117,50 @@ SPTX_DEV float scrambled_radical_inverse(const uint16_t *perm, uint64_t a, uint3
     return (kOneMinusEpsilon < r) ? kOneMinusEpsilon : r;
 }
 
+// ---- SobolSampler (samplers/sobol.cpp, core/lowdiscrepancy.h:229-274) -------------------
+constexpr int kSobolMatrixSize = 52;
+// SobolIntervalToIndex: the index of sample number `frame` of pixel p (relative to the sample
+// bounds) in the global Sobol' sequence.
+SPTX_DEV uint64_t sobol_interval_to_index(const DSampler &H, uint64_t frame, int px, int py) {
+    const uint32_t m = (uint32_t)H.s.log2_resolution;
+    if (m == 0) return 0;
+    const uint64_t *vdc = reinterpret_cast<const uint64_t *>(H.prime_sums);
+    const uint64_t *vdcInv = vdc + kSobolMatrixSize;
+    const uint32_t m2 = m << 1;
+    uint64_t index = frame << m2;
+    uint64_t delta = 0;
+    for (int c = 0; frame; frame >>= 1, ++c)
+        if (frame & 1) delta ^= __ldg(vdc + c);
+    uint64_t b = (((uint64_t)((uint32_t)px) << m) | ((uint32_t)py)) ^ delta;
+    for (int c = 0; b; b >>= 1, ++c)
+        if (b & 1) index ^= __ldg(vdcInv + c);
+    return index;
+}
+// SobolSampler::SampleDimension = SobolSampleFloat + the pixel remap of dimensions 0 and 1.
+// The pixel the index belongs to is read off the sample's own top m bits (that is what
+// SobolIntervalToIndex arranges), so a path needs to carry nothing but its index.
+SPTX_NOINL float sobol_sample(const DSampler &H, uint64_t index, int dim) {
+    const int d = dim < H.s.n_dims ? dim : H.s.n_dims - 1;  // callers flag the overflow
+    const uint32_t *M = reinterpret_cast<const uint32_t *>(H.primes) + (size_t)d * kSobolMatrixSize;
+    uint32_t v = 0;
+    for (int i = 0; index != 0; index >>= 1, ++i)
+        if (index & 1) v ^= __ldg(M + i);
+    float s = (float)v * 0x1p-32f;
+    s = (kOneMinusEpsilon < s) ? kOneMinusEpsilon : s;
+    if (d == 0 || d == 1) {
+        const int m = H.s.log2_resolution;
+        const int resolution = 1 << m;
+        s = s * (float)resolution + (float)H.sb[d];
+        const int cur = H.sb[d] + (m > 0 ? (int)(v >> (32 - m)) : 0);
+        s = s - (float)cur;
+        s = (s < 0.f) ? 0.f : ((s > kOneMinusEpsilon) ? kOneMinusEpsilon : s);
+    }
+    return s;
+}
+
 // HaltonSampler::SampleDimension, samplers/halton.cpp:117-127.
 SPTX_NOINL float halton_sample(const DSampler &H, uint64_t index, int dim) {
+    if (H.s.type == SPTX_SAMPLER_SOBOL) return sobol_sample(H, index, dim);
     if (H.s.sample_at_center && (dim == 0 || dim == 1)) return 0.5f;
     if (dim == 0) {
         // RadicalInverse(0, a) = ReverseBits64(a) * 0x1p-64 in DOUBLE, rounded
@@ -140,7 +182,7 @@ SPTX_NOINL float halton_sample(const DSampler &H, uint64_t index, int dim) {
 // 32 bits, which holds while index * base < 2^32 (checked, else the scalar path).
 template <int N>
 SPTX_DEV void halton_n(const DSampler &H, uint64_t index, int dim, float *out) {
-    bool fast = dim >= 2 && dim + N <= H.s.n_dims && (index >> 32) == 0;
+    bool fast = H.s.type == SPTX_SAMPLER_HALTON && dim >= 2 && dim + N <= H.s.n_dims && (index >> 32) == 0;
     uint4 tab[N];
     if (fast) {
 #pragma unroll
@@ -191,6 +233,14 @@ SPTX_DEV void halton_n(const DSampler &H, uint64_t index, int dim, float *out) {
         float r = invN[j] * ((float)rev[j] + __ldg(H.dim_tail + dim + j));
         out[j] = (kOneMinusEpsilon < r) ? kOneMinusEpsilon : r;
     }
+}
+
+// Index of sample number `sampleNum` of pixel (px, py): GlobalSampler::GetIndexForSample.
+SPTX_DEV uint64_t sample_index(const DSampler &H, int px, int py, int sampleNum) {
+    if (H.s.type == SPTX_SAMPLER_SOBOL)
+        return sobol_interval_to_index(H, (uint64_t)sampleNum, px - H.sb[0], py - H.sb[1]);
+    const uint64_t off = H.pixel_offset[(size_t)(py - H.sb[1]) * (H.sb[2] - H.sb[0]) + (px - H.sb[0])];
+    return off + (uint64_t)sampleNum * (uint64_t)H.s.sample_stride;
 }
 
 // Per-path view of the sampler: GlobalSampler::Get1D/Get2D with no array

@@ -170,8 +170,11 @@ __global__ void k_sampler_eval(DSampler H, const int *px, const int *py, const i
                                const int *dim, int64_t n, float *out) {
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
          i += (int64_t)gridDim.x * blockDim.x) {
-        uint64_t off = halton_pixel_offset(H.s, px[i], py[i]);
-        uint64_t index = off + (uint64_t)sample[i] * (uint64_t)H.s.sample_stride;
+        uint64_t index;
+        if (H.s.type == SPTX_SAMPLER_SOBOL)
+            index = sobol_interval_to_index(H, (uint64_t)sample[i], px[i] - H.sb[0], py[i] - H.sb[1]);
+        else
+            index = halton_pixel_offset(H.s, px[i], py[i]) + (uint64_t)sample[i] * (uint64_t)H.s.sample_stride;
         out[i] = halton_sample(H, index, dim[i]);
     }
 }

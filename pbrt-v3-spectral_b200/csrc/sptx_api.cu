@@ -308,6 +308,11 @@ static int validate_scene(sptx_ctx *ctx, const sptx_scene_desc *sc) {
             "Halton tables missing");
         const int last = sc->sampler.n_dims - 1;
         REQ((int64_t)sc->prime_sums[last] + sc->primes[last] <= sc->n_perms, "Halton permutations short");
+    } else if (sc->sampler.type == SPTX_SAMPLER_SOBOL) {
+        REQ(sc->sampler.n_dims >= 5 && sc->sampler.n_dims <= 1024 &&
+                sc->n_primes >= (int64_t)sc->sampler.n_dims * 52 && sc->n_prime_sums >= 4 * 52 &&
+                sc->sampler.log2_resolution >= 0 && sc->sampler.log2_resolution < 26,
+            "Sobol tables missing");
     } else if (sc->sampler.type == SPTX_SAMPLER_RANDOM) {
         REQ(sc->sampler.spp > 0, "RandomSampler needs samplesPerPixel");
     } else
@@ -550,6 +555,10 @@ extern "C" int sptx_upload_scene(sptx_ctx *ctx, const sptx_scene_desc *sc) {
         H.pixel_offset = off;
     }
     }  // Halton
+    if (sc->sampler.type == SPTX_SAMPLER_SOBOL) {
+        if ((rc = upload(ctx, pool, sc->primes, (int64_t)sc->sampler.n_dims * 52, &H.primes))) return rc;
+        if ((rc = upload(ctx, pool, sc->prime_sums, (int64_t)4 * 52, &H.prime_sums))) return rc;
+    }
 
     // ---- film ----
     DFilm &F = ctx->F;
@@ -1161,8 +1170,8 @@ extern "C" int sptx_sampler_eval(sptx_ctx *ctx, const int32_t *px, const int32_t
     if (!ctx) return fail(nullptr, SPTX_EINVAL, "sptx_sampler_eval: ctx is NULL");
     if (!ctx->haveScene) return fail(ctx, SPTX_ESTATE, "sptx_sampler_eval: no scene uploaded");
     if (n <= 0) return SPTX_OK;
-    if (ctx->H.s.type != SPTX_SAMPLER_HALTON)
-        return fail(ctx, SPTX_EUNSUPPORTED, "sptx_sampler_eval: only for the Halton sampler (a RandomSampler value depends on the whole tile before it)");
+    if (ctx->H.s.type == SPTX_SAMPLER_RANDOM)
+        return fail(ctx, SPTX_EUNSUPPORTED, "sptx_sampler_eval: only for the Halton and Sobol samplers (a RandomSampler value depends on the whole tile before it)");
     CK(cudaSetDevice(ctx->device));
     std::vector<void *> pool;
     const int32_t *dpx, *dpy, *ds, *dd;
@@ -1215,8 +1224,8 @@ extern "C" int sptx_debug_radiance(sptx_ctx *ctx, const int32_t *px, const int32
     if (!ctx) return fail(nullptr, SPTX_EINVAL, "sptx_debug_radiance: ctx is NULL");
     if (!ctx->haveScene) return fail(ctx, SPTX_ESTATE, "sptx_debug_radiance: no scene uploaded");
     if (n <= 0) return SPTX_OK;
-    if (ctx->H.s.type != SPTX_SAMPLER_HALTON)
-        return fail(ctx, SPTX_EUNSUPPORTED, "sptx_debug_radiance: only for the Halton sampler (a RandomSampler value depends on the whole tile before it)");
+    if (ctx->H.s.type == SPTX_SAMPLER_RANDOM)
+        return fail(ctx, SPTX_EUNSUPPORTED, "sptx_debug_radiance: only for the Halton and Sobol samplers (a RandomSampler value depends on the whole tile before it)");
     CK(cudaSetDevice(ctx->device));
     std::vector<int2> pixels((size_t)n);
     for (int64_t i = 0; i < n; ++i) pixels[i] = make_int2(px[i], py[i]);

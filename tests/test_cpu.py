@@ -125,5 +125,5 @@ def test_flattener_rejects_bands_with_random_sampler(tmp_path):
                            "res=16", "spp=1", "sampler=random", "bands=2"])
     env = dict(os.environ, SPTX_DUMP_SCENE=str(tmp_path / "s.sptx"), SPTX_DUMP_ONLY="1")
     r = subprocess.run([exe, "--quiet", scene], cwd=str(tmp_path), env=env, capture_output=True, text=True)
-    assert r.returncode != 0 and "halton sampler only" in (r.stdout + r.stderr)
+    assert r.returncode != 0 and "halton and sobol samplers only" in (r.stdout + r.stderr)
     assert not os.path.exists(str(tmp_path / "s.sptx"))
