@@ -340,13 +340,13 @@ static float host_y(const sptx_scene_desc *sc, const float *row, float scale) {
 extern "C" int sptx_upload_scene(sptx_ctx *ctx, const sptx_scene_desc *sc) {
     if (!ctx) return fail(nullptr, SPTX_EINVAL, "sptx_upload_scene: ctx is NULL");
     if (!sc) return fail(ctx, SPTX_EINVAL, "sptx_upload_scene: scene is NULL");
+    // SPTX_TRACE_UPLOAD=1: wall time of each phase (stream drained at every mark), to stderr
+    const bool trace = getenv("SPTX_TRACE_UPLOAD") != nullptr;
+    auto tPrev = std::chrono::steady_clock::now();
     int rc = validate_scene(ctx, sc);
     if (rc) return rc;
     CK(cudaSetDevice(ctx->device));
     CK(cudaStreamSynchronize(ctx->stream));
-    // SPTX_TRACE_UPLOAD=1: wall time of each phase (stream drained at every mark), to stderr
-    const bool trace = getenv("SPTX_TRACE_UPLOAD") != nullptr;
-    auto tPrev = std::chrono::steady_clock::now();
     auto mark = [&](const char *what) {
         if (!trace) return;
         cudaStreamSynchronize(ctx->stream);
@@ -355,6 +355,7 @@ extern "C" int sptx_upload_scene(sptx_ctx *ctx, const sptx_scene_desc *sc) {
                 std::chrono::duration<double, std::milli>(now - tPrev).count());
         tPrev = now;
     };
+    mark("validate+drain");
     free_pool(ctx->sceneAllocs);
     ctx->haveScene = false;
     mark("free");
