@@ -157,6 +157,77 @@ struct PrimIndex {
     }
 };
 
+// ---- visit counts ------------------------------------------------------------------------
+// The reference's BVHAccel::Intersect is not instrumented, and the reference is not edited.  This
+// is that loop (src/accelerators/bvh.cpp:662-700) walked again over the reference's OWN node
+// array, with the reference's own Bounds3::IntersectP and Primitive::Intersect doing every test,
+// counting the nodes and primitives a ray visits (the per-ray counts the
+// traversal roofline is built on).  Nested aggregates of object instances are entered the way
+// TransformedPrimitive::Intersect does (src/core/primitive.cpp:78-99).  The walk's hit must
+// equal Scene::Intersect's, which the caller checks.
+struct NodeView {  // the bytes of the file-local LinearBVHNode, src/accelerators/bvh.cpp:95-104
+    Bounds3f bounds;
+    int offset;  // primitivesOffset (leaf) / secondChildOffset (interior)
+    uint16_t nPrimitives;
+    uint8_t axis;
+    uint8_t pad[1];
+};
+static_assert(sizeof(NodeView) == 32, "LinearBVHNode is 32 bytes");
+
+bool CountingWalk(const Primitive *agg, const Ray &ray, SurfaceInteraction *isect, int32_t *nNodes,
+                  int32_t *nTests) {
+    auto *bvh = dynamic_cast<const BVHAccel *>(agg);
+    if (!bvh) {  // a bare primitive as the aggregate
+        ++*nTests;
+        return agg->Intersect(ray, isect);
+    }
+    if (!bvh->nodes) return false;
+    const NodeView *nodes = reinterpret_cast<const NodeView *>(bvh->nodes);
+    bool hit = false;
+    Vector3f invDir(1 / ray.d.x, 1 / ray.d.y, 1 / ray.d.z);
+    int dirIsNeg[3] = {invDir.x < 0, invDir.y < 0, invDir.z < 0};
+    int toVisitOffset = 0, currentNodeIndex = 0;
+    int nodesToVisit[64];
+    while (true) {
+        const NodeView *node = &nodes[currentNodeIndex];
+        ++*nNodes;
+        if (node->bounds.IntersectP(ray, invDir, dirIsNeg)) {
+            if (node->nPrimitives > 0) {
+                for (int i = 0; i < node->nPrimitives; ++i) {
+                    const Primitive *p = bvh->primitives[node->offset + i].get();
+                    ++*nTests;
+                    if (auto *tp = dynamic_cast<const TransformedPrimitive *>(p)) {
+                        Transform p2w;
+                        tp->PrimitiveToWorld.Interpolate(ray.time, &p2w);
+                        Ray r2 = Inverse(p2w)(ray);
+                        if (CountingWalk(tp->primitive.get(), r2, isect, nNodes, nTests)) {
+                            ray.tMax = r2.tMax;
+                            if (!p2w.IsIdentity()) *isect = p2w(*isect);
+                            isect->instanceId = tp->instanceId;
+                            hit = true;
+                        }
+                    } else if (p->Intersect(ray, isect))
+                        hit = true;
+                }
+                if (toVisitOffset == 0) break;
+                currentNodeIndex = nodesToVisit[--toVisitOffset];
+            } else {
+                if (dirIsNeg[node->axis]) {
+                    nodesToVisit[toVisitOffset++] = currentNodeIndex + 1;
+                    currentNodeIndex = node->offset;
+                } else {
+                    nodesToVisit[toVisitOffset++] = node->offset;
+                    currentNodeIndex = currentNodeIndex + 1;
+                }
+            }
+        } else {
+            if (toVisitOffset == 0) break;
+            currentNodeIndex = nodesToVisit[--toVisitOffset];
+        }
+    }
+    return hit;
+}
+
 class DumpIntegrator : public Integrator {
   public:
     DumpIntegrator(PathIntegrator *real) : real(real) {}
@@ -193,6 +264,21 @@ void DumpIntegrator::Render(const Scene &scene) {
                 h.prim = h.instance = -1;
                 if (scene.Intersect(r, &isect)) index.Lookup(isect, &h.prim, &h.instance);
                 h.t = r.tMax;
+                if (getenv("ORACLE_COUNT_VISITS")) {
+                    Ray rc(Point3f(rays[i].o[0], rays[i].o[1], rays[i].o[2]),
+                           Vector3f(rays[i].d[0], rays[i].d[1], rays[i].d[2]), rays[i].tMax,
+                           rays[i].time);
+                    SurfaceInteraction ic;
+                    int32_t p2 = -1, i2 = -1;
+                    if (CountingWalk(scene.aggregate.get(), rc, &ic, &h.nNodes, &h.nTests))
+                        index.Lookup(ic, &p2, &i2);
+                    if (p2 != h.prim || i2 != h.instance || rc.tMax != r.tMax) {
+                        Error("oracle_dump: the counting walk disagrees with Scene::Intersect on ray %lld",
+                              (long long)i);
+                        fflush(nullptr);
+                        std::_Exit(3);
+                    }
+                }
                 hits[i] = h;
             }, n, 4096);
             WriteAll(out, hits);

@@ -305,6 +305,30 @@ def make_bands(name):
           f"{np.array2string(dat.mean(axis=(1, 2))[[0, 7, 8, 15, 16, 23, 24, 29, 30]], precision=4)}")
 
 
+VISIT_SCENES = ["cornell64", "killeroo128", "instanced", "zoo"]
+
+
+def make_visits():
+    """Per-ray node / primitive visit counts of the reference's traversal (oracle_dump's counting
+    walk over the reference's own BVH, checked there against Scene::Intersect) for the rays the
+    scene fixtures already hold -> tests/golden/visits.npz."""
+    out = {}
+    for name in VISIT_SCENES:
+        spec = SCENES[name]
+        g = np.load(os.path.join(GOLD, name + ".npz"))
+        with tempfile.TemporaryDirectory() as work:
+            pbrt = scene_file(name, spec, work)
+            np.ascontiguousarray(g["rays"]).tofile(os.path.join(work, "rays.bin"))
+            run([ORACLE, "--quiet", "--nthreads", "8", pbrt], cwd=work,
+                env={"ORACLE_RAYS_IN": "rays.bin", "ORACLE_HITS_OUT": "hits.bin", "ORACLE_COUNT_VISITS": "1"})
+            hits = np.fromfile(os.path.join(work, "hits.bin"), dtype=HIT)
+        assert np.array_equal(hits["prim"], g["hit_prim"]) and np.array_equal(hits["t"], g["hit_t"])
+        out[name + "_nodes"] = hits["n_nodes"].astype(np.int32)
+        out[name + "_tests"] = hits["n_tests"].astype(np.int32)
+        print(f"{name}: {hits['n_nodes'].mean():.2f} nodes, {hits['n_tests'].mean():.2f} primitive tests per ray")
+    np.savez_compressed(os.path.join(GOLD, "visits.npz"), **out)
+
+
 def read_root_bounds(blob):
     """Root node bounds of the scene aggregate, read straight from the scene file."""
     import ctypes as C
@@ -324,9 +348,11 @@ def read_root_bounds(blob):
 
 
 if __name__ == "__main__":
-    names = sys.argv[1:] or list(SCENES) + ["cornell_random"] + list(BAND_SCENES) + list(META_SCENES)
+    names = sys.argv[1:] or list(SCENES) + ["cornell_random"] + list(BAND_SCENES) + list(META_SCENES) + ["visits"]
     for n in names:
-        if n == "cornell_random":
+        if n == "visits":
+            make_visits()
+        elif n == "cornell_random":
             make_random(n)
         elif n in BAND_SCENES:
             make_bands(n)

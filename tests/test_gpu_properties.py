@@ -136,3 +136,21 @@ def test_errors_are_reported_not_swallowed(capi):
     with pytest.raises(capi.SptxError):
         ctx.set_option("no_such_option", 1)
     ctx.close()
+
+
+@pytest.mark.parametrize("name", ["cornell64", "killeroo128", "instanced", "zoo"])
+def test_visit_counts_are_the_reference_traversals(capi, gpu_ctx, name):
+    """the traversal roofline is built on per-ray node and primitive visit counts.
+    The device's counted traversal (sptx_intersect_batch(counters=1)) visits exactly what the
+    reference's BVHAccel::Intersect visits -- same order, same early exits -- so the counts are
+    equal ray by ray (fixture: oracle_dump's counting walk over the reference's own BVH)."""
+    from conftest import blob_path, golden
+    g, v = golden(name), golden("visits")
+    sf = capi.SceneFile(blob_path(name))
+    gpu_ctx.upload(sf)
+    rays = np.ascontiguousarray(g["rays"]).view(capi.RAY_DTYPE).reshape(-1)
+    hits = gpu_ctx.intersect(rays, any_hit=False, counters=True)
+    assert np.array_equal(hits["n_nodes"], v[name + "_nodes"]), \
+        f"{(hits['n_nodes'] != v[name + '_nodes']).sum()} rays visit a different number of nodes"
+    assert np.array_equal(hits["n_tests"], v[name + "_tests"])
+    sf.close()
