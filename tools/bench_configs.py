@@ -52,6 +52,30 @@ def render_rate(name, w, h, spp, warm_spp):
             "mrays_per_s_traversal": rays / max(c["traverse_ms"], 1e-9) * 1e-3}
 
 
+def reference_rate(gen, w, h, spp_lo, spp_hi):
+    """The reference's own CPU renderer (oracle/_ref/pbrt, all host threads) on a procedural scene:
+    samples / (t(spp_hi) - t(spp_lo)), which removes parsing, BVH build and the .dat write."""
+    import subprocess
+    import tempfile
+    import time
+    exe = os.path.join(ROOT, "oracle", "_ref", "pbrt")
+    if not os.path.exists(exe):
+        return {"unavailable": "oracle/_ref/pbrt was not built"}
+    t = []
+    with tempfile.TemporaryDirectory() as work:
+        for spp in (spp_lo, spp_hi):
+            pbrt = os.path.join(work, f"s{spp}.pbrt")
+            subprocess.check_call([sys.executable, os.path.join(ROOT, "scenes", "gen_scenes.py"), gen[0], pbrt] +
+                                  gen[1:] + [f"res={w}x{h}", f"spp={spp}"])
+            t0 = time.perf_counter()
+            subprocess.run([exe, "--quiet", "--nthreads", str(os.cpu_count()), pbrt], cwd=work, check=True,
+                           stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+            t.append(time.perf_counter() - t0)
+    dt = max(t[1] - t[0], 1e-6)
+    return {"msamples_per_s": w * h * (spp_hi - spp_lo) / dt * 1e-6, "cores": os.cpu_count(),
+            "sample": f"{spp_hi - spp_lo} spp (difference of a {spp_hi}-spp and a {spp_lo}-spp run, {dt:.1f} s)"}
+
+
 def c1():
     return render_rate("killeroo400", 400, 400, 64, 8)
 
@@ -61,6 +85,7 @@ def c3():
     # camera-ray generation alone (K1 with lens tracing): share of the render
     out["generate_ms"] = out["kernel_ms"]["generate"]
     out["camera_mrays_per_s"] = 2048 * 2048 * 256 / out["generate_ms"] * 1e-3
+    out["cpu_reference"] = reference_rate(["cornell_lens"], 2048, 2048, 1, 3)
     return out
 
 
@@ -103,7 +128,32 @@ def c4():
                 "nodes_per_ray": nodes, "tests_per_ray": tests, "algorithmic_bytes_per_ray": bytes_per_ray,
                 "achieved_gbs": gbs, "frac_of_hbm_peak": gbs / PEAK}
     ctx.close()
+    # the reference's BVHAccel::Intersect / IntersectP on the box's host cores, timed by the oracle
+    # (BASELINE.md 3.3): 2^20 rays of each batch, every host thread
+    res["cpu_reference"] = c4_cpu({k: v[:1 << 20] for k, v in batches.items()})
     return res
+
+
+def c4_cpu(batches):
+    import re
+    import subprocess
+    import tempfile
+    exe = os.path.join(ROOT, "oracle", "_ref", "oracle_dump")
+    if not os.path.exists(exe):
+        return {"unavailable": "oracle/_ref/oracle_dump was not built"}
+    out = {"cores": os.cpu_count(), "rays_per_batch": 1 << 20}
+    with tempfile.TemporaryDirectory() as work:
+        pbrt = os.path.join(work, "instanced_c4.pbrt")
+        subprocess.check_call([sys.executable, os.path.join(ROOT, "scenes", "gen_scenes.py"), "instanced", pbrt,
+                               "res=1024", "spp=4", "grid=317", "inst=10"])
+        for name, rays in batches.items():
+            np.ascontiguousarray(rays).tofile(os.path.join(work, "rays.bin"))
+            env = dict(os.environ, ORACLE_RAYS_IN="rays.bin", ORACLE_TIME_RAYS="4")
+            r = subprocess.run([exe, "--quiet", "--nthreads", str(os.cpu_count()), pbrt], cwd=work, env=env,
+                               capture_output=True, text=True)
+            for kind, rate in re.findall(r"ORACLE_TIMING (\w+) .*?mrays_per_s=([0-9.]+)", r.stdout + r.stderr):
+                out[f"{name}/{kind}"] = {"mrays_per_s": float(rate)}
+    return out
 
 
 if __name__ == "__main__":
