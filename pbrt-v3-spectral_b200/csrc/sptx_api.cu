@@ -26,6 +26,16 @@ struct sptx_ctx {
     bool haveScene = false;
     std::vector<void *> sceneAllocs;
     std::vector<void *> pathAllocs;
+    // Device buffers of the previous scene, kept across the free -> allocate cycle of a re-upload
+    // (sptx_upload_scene): a scene of the same shape takes them back instead of going through
+    // cudaFree / cudaMalloc, which are device-wide synchronisation points (measured: sporadic
+    // 60-110 ms stalls per upload).  Whatever is not taken back is freed when the upload ends.
+    struct Spare {
+        void *ptr;
+        size_t bytes;
+    };
+    std::vector<Spare> spares;
+    std::vector<Spare> sizes;  // byte size of every live allocation made through dmalloc()
     DScene S;
     DCamera C;
     DSampler H;
@@ -84,20 +94,44 @@ static int grid_for(const sptx_ctx *ctx, int64_t n, int block = kBlock) {
     return (int)blocks;
 }
 
+// cudaMalloc, or a spare buffer of exactly this size.
+static cudaError_t dmalloc(sptx_ctx *ctx, void **p, size_t bytes) {
+    for (size_t i = 0; i < ctx->spares.size(); ++i)
+        if (ctx->spares[i].bytes == bytes) {
+            *p = ctx->spares[i].ptr;
+            ctx->spares.erase(ctx->spares.begin() + (long)i);
+            ctx->sizes.push_back({*p, bytes});
+            return cudaSuccess;
+        }
+    cudaError_t e = cudaMalloc(p, bytes);
+    if (e == cudaSuccess) ctx->sizes.push_back({*p, bytes});
+    return e;
+}
+static size_t forget_size(sptx_ctx *ctx, void *p) {
+    for (size_t i = 0; i < ctx->sizes.size(); ++i)
+        if (ctx->sizes[i].ptr == p) {
+            const size_t b = ctx->sizes[i].bytes;
+            ctx->sizes[i] = ctx->sizes.back();
+            ctx->sizes.pop_back();
+            return b;
+        }
+    return 0;
+}
+
 template <typename T>
 static int upload(sptx_ctx *ctx, std::vector<void *> &pool, const T *src, int64_t n, const T **out) {
     *out = nullptr;
     if (n <= 0) {
         // keep kernels safe: a 1-element dummy so pointers are never null
         void *p = nullptr;
-        CK(cudaMalloc(&p, sizeof(T) > 16 ? sizeof(T) : 16));
+        CK(dmalloc(ctx, &p, sizeof(T) > 16 ? sizeof(T) : 16));
         CK(cudaMemsetAsync(p, 0, sizeof(T) > 16 ? sizeof(T) : 16, ctx->stream));
         pool.push_back(p);
         *out = (const T *)p;
         return SPTX_OK;
     }
     void *p = nullptr;
-    CK(cudaMalloc(&p, (size_t)n * sizeof(T)));
+    CK(dmalloc(ctx, &p, (size_t)n * sizeof(T)));
     pool.push_back(p);
     CK(cudaMemcpyAsync(p, src, (size_t)n * sizeof(T), cudaMemcpyHostToDevice, ctx->stream));
     *out = (const T *)p;
@@ -108,15 +142,33 @@ template <typename T>
 static int dalloc(sptx_ctx *ctx, std::vector<void *> &pool, int64_t n, T **out) {
     void *p = nullptr;
     if (n < 1) n = 1;
-    CK(cudaMalloc(&p, (size_t)n * sizeof(T)));
+    CK(dmalloc(ctx, &p, (size_t)n * sizeof(T)));
     pool.push_back(p);
     *out = (T *)p;
     return SPTX_OK;
 }
 
-static void free_pool(std::vector<void *> &pool) {
-    for (void *p : pool) cudaFree(p);
+static void free_pool(sptx_ctx *ctx, std::vector<void *> &pool) {
+    for (void *p : pool) {
+        forget_size(ctx, p);
+        cudaFree(p);
+    }
     pool.clear();
+}
+// The pool's buffers become spares for the allocations that follow; drop_spares() ends the cycle.
+static void recycle_pool(sptx_ctx *ctx, std::vector<void *> &pool) {
+    for (void *p : pool) {
+        const size_t b = forget_size(ctx, p);
+        if (b)
+            ctx->spares.push_back({p, b});
+        else
+            cudaFree(p);
+    }
+    pool.clear();
+}
+static void drop_spares(sptx_ctx *ctx) {
+    for (auto &s : ctx->spares) cudaFree(s.ptr);
+    ctx->spares.clear();
 }
 
 extern "C" int sptx_abi_version(void) { return SPTX_ABI_VERSION; }
@@ -174,8 +226,9 @@ extern "C" void sptx_destroy(sptx_ctx *ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
-    free_pool(ctx->sceneAllocs);
-    free_pool(ctx->pathAllocs);
+    free_pool(ctx, ctx->sceneAllocs);
+    free_pool(ctx, ctx->pathAllocs);
+    drop_spares(ctx);
     if (ctx->dCnt) cudaFree(ctx->dCnt);
     if (ctx->dS) cudaFree(ctx->dS);
     if (ctx->dFilmSplit) cudaFree(ctx->dFilmSplit);
@@ -341,7 +394,9 @@ extern "C" int sptx_upload_scene(sptx_ctx *ctx, const sptx_scene_desc *sc) {
     if (!ctx) return fail(nullptr, SPTX_EINVAL, "sptx_upload_scene: ctx is NULL");
     if (!sc) return fail(ctx, SPTX_EINVAL, "sptx_upload_scene: scene is NULL");
     // SPTX_TRACE_UPLOAD=1: wall time of each phase (stream drained at every mark), to stderr
-    const bool trace = getenv("SPTX_TRACE_UPLOAD") != nullptr;
+    const char *traceEnv = getenv("SPTX_TRACE_UPLOAD");  // "2": host time only, no extra syncs
+    const bool trace = traceEnv != nullptr;
+    const bool traceSync = trace && traceEnv[0] != '2';
     auto tPrev = std::chrono::steady_clock::now();
     int rc = validate_scene(ctx, sc);
     if (rc) return rc;
@@ -349,14 +404,14 @@ extern "C" int sptx_upload_scene(sptx_ctx *ctx, const sptx_scene_desc *sc) {
     CK(cudaStreamSynchronize(ctx->stream));
     auto mark = [&](const char *what) {
         if (!trace) return;
-        cudaStreamSynchronize(ctx->stream);
+        if (traceSync) cudaStreamSynchronize(ctx->stream);
         auto now = std::chrono::steady_clock::now();
         fprintf(stderr, "sptx_upload_scene: %-18s %8.3f ms\n", what,
                 std::chrono::duration<double, std::milli>(now - tPrev).count());
         tPrev = now;
     };
     mark("validate+drain");
-    free_pool(ctx->sceneAllocs);
+    recycle_pool(ctx, ctx->sceneAllocs);
     ctx->haveScene = false;
     mark("free");
     std::vector<void *> &pool = ctx->sceneAllocs;
@@ -578,6 +633,7 @@ extern "C" int sptx_upload_scene(sptx_ctx *ctx, const sptx_scene_desc *sc) {
     CK(cudaMemcpyAsync(ctx->dH, &ctx->H, sizeof(DSampler), cudaMemcpyHostToDevice, ctx->stream));
     CK(cudaGetLastError());
     CK(cudaStreamSynchronize(ctx->stream));
+    drop_spares(ctx);  // buffers of the previous scene this one did not take back
     mark("sampler+film");
     ctx->haveScene = true;
     return SPTX_OK;
@@ -602,7 +658,7 @@ __global__ void k_reset_bounce(int *counters, int qNext) {
 static int ensure_paths(sptx_ctx *ctx, int64_t P) {
     if (ctx->allocatedPaths >= P) return SPTX_OK;
     CK(cudaStreamSynchronize(ctx->stream));
-    free_pool(ctx->pathAllocs);
+    free_pool(ctx, ctx->pathAllocs);
     ctx->allocatedPaths = 0;
     std::vector<void *> &pool = ctx->pathAllocs;
     PathArrays &A = ctx->A;
@@ -1181,13 +1237,13 @@ extern "C" int sptx_sampler_eval(sptx_ctx *ctx, const int32_t *px, const int32_t
     if ((rc = upload(ctx, pool, px, n, &dpx)) || (rc = upload(ctx, pool, py, n, &dpy)) ||
         (rc = upload(ctx, pool, sample, n, &ds)) || (rc = upload(ctx, pool, dim, n, &dd)) ||
         (rc = dalloc(ctx, pool, n, &dv))) {
-        free_pool(pool);
+        free_pool(ctx, pool);
         return rc;
     }
     k_sampler_eval<<<grid_for(ctx, n), kBlock, 0, ctx->stream>>>(ctx->H, dpx, dpy, ds, dd, n, dv);
     cudaError_t e = cudaMemcpyAsync(values, dv, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
-    free_pool(pool);
+    free_pool(ctx, pool);
     if (e != cudaSuccess) return fail(ctx, SPTX_ECUDA, "sptx_sampler_eval: %s", cudaGetErrorString(e));
     return SPTX_OK;
 }
@@ -1205,7 +1261,7 @@ extern "C" int sptx_camera_rays(sptx_ctx *ctx, const float *cs, int64_t n, float
     int rc;
     if ((rc = upload(ctx, pool, cs, 5 * n, &dcs)) || (rc = dalloc(ctx, pool, n, &dr)) ||
         (rc = dalloc(ctx, pool, n, &dw))) {
-        free_pool(pool);
+        free_pool(ctx, pool);
         return rc;
     }
     k_camera_rays<<<grid_for(ctx, n), kBlock, 0, ctx->stream>>>(ctx->C, dcs, n, wavelength, dr, dw);
@@ -1213,7 +1269,7 @@ extern "C" int sptx_camera_rays(sptx_ctx *ctx, const float *cs, int64_t n, float
     if (e == cudaSuccess)
         e = cudaMemcpyAsync(weights, dw, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
-    free_pool(pool);
+    free_pool(ctx, pool);
     if (e != cudaSuccess) return fail(ctx, SPTX_ECUDA, "sptx_camera_rays: %s", cudaGetErrorString(e));
     return SPTX_OK;
 }
@@ -1234,7 +1290,7 @@ extern "C" int sptx_debug_radiance(sptx_ctx *ctx, const int32_t *px, const int32
     const int32_t *dS;
     int rc = upload(ctx, pool, sample, n, &dS);
     if (rc == SPTX_OK) rc = render_pixels(ctx, pixels, 0, 1, dS);
-    free_pool(pool);
+    free_pool(ctx, pool);
     if (rc) return rc;
     const PathArrays &A = ctx->A;
     std::vector<float> tmp((size_t)n * SPTX_SPECTRUM_STRIDE);
