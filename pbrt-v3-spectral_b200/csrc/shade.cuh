@@ -83,8 +83,12 @@ __device__ unsigned long long g_stageClocks[32];
 #else
 #define SPTX_TICK(slot)
 #endif
+// Which stage ends carry the barrier (bit s = after slot s).  Measured on one 4-spp pass of the
+// bench scene (shade ms): none 11.97, 0x01 9.39, 0x04 9.24, 0x10 9.13, 0x40 8.85, 0x100 9.31,
+// 0x11 9.56 (the previous setting), 0x44 9.21, 0x50 8.99, 0x140 9.40, 0x41 9.46 -- one barrier,
+// after the f / pdf / fa-row stage, is best; C1 -2.5 %, C3 -7.7 % with it as well.
 #ifndef SPTX_STAGE_MASK
-#define SPTX_STAGE_MASK 0x11
+#define SPTX_STAGE_MASK 0x40
 #endif
 #define SPTX_STAGE(slot)                                       \
     do {                                                       \
