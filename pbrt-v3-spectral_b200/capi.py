@@ -104,6 +104,25 @@ def _ptr(a):
     return a.ctypes.data_as(C.c_void_p)
 
 
+def unpack_blob(path):
+    """`path` (a .sptx scene blob); when only its committed .xz form exists (the large configuration
+    blobs are kept compressed in git), it is unpacked next to it first.  Returns `path`, or None."""
+    if os.path.exists(path):
+        return path
+    if os.path.exists(path + ".xz"):
+        import lzma
+        tmp = path + f".tmp{os.getpid()}"
+        with lzma.open(path + ".xz", "rb") as src, open(tmp, "wb") as dst:
+            while True:
+                chunk = src.read(1 << 24)
+                if not chunk:
+                    break
+                dst.write(chunk)
+        os.replace(tmp, path)
+        return path
+    return None
+
+
 class SceneFile:
     """A flattened scene (host arrays) loaded from a file host/flatten.cpp wrote."""
 

@@ -1,6 +1,6 @@
 // resolve.cuh -- K4 (shadow / MIS rays of EstimateDirect) and K5/K6 (film).
 #pragma once
-#include "shade.cuh"
+#include "kernels.cuh"
 
 namespace sptx {
 
@@ -235,16 +235,6 @@ SPTX_DEV float guard_scale(const DScene &S, const DFilm &F, const PathArrays &A,
 
 __global__ void __launch_bounds__(kBlock)
 k_film(DScene S, DFilm F, PathArrays A, RenderParams R) {
-#ifdef SPTX_STAGE_CLOCKS
-    if (blockIdx.x == 0 && threadIdx.x == 0) {
-        unsigned long long tot = 0;
-        for (int c = 0; c < 24; ++c) tot += g_stageClocks[c];
-        for (int c = 0; c < 17; ++c) {
-            printf("S%02d %5.1f%%  ", c, 100.0 * (double)g_stageClocks[c] / (double)tot);
-            g_stageClocks[c] = 0;
-        }
-    }
-#endif
     for (int pix = blockIdx.x * blockDim.x + threadIdx.x; pix < R.nPix;
          pix += gridDim.x * blockDim.x) {
         const int2 pxy = R.pixels[pix];

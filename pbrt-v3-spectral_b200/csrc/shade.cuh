@@ -11,35 +11,9 @@
 // The two rays EstimateDirect traces (shadow ray, BSDF-sampled MIS ray) are
 // written out with their per-bin contributions (fa, fb) and traced by K4.
 #pragma once
-#include "kernels.cuh"
+#include "wavefront.cuh"
 
 namespace sptx {
-
-// LightDistribution::Lookup + Distribution1D::SampleDiscrete.
-SPTX_DEV int select_light(const DScene &S, V3 p, float u, float *pdf) {
-    const int n = S.n_lights;
-    if (S.light_strategy != SPTX_LIGHTS_SPATIAL)
-        return sample_discrete(S.light_func, S.light_func + n, n, S.light_func_int, u, pdf);
-    // SpatialLightDistribution::Lookup, core/lightdistrib.cpp:135-147
-    V3 pmin = mk(S.wb_min[0], S.wb_min[1], S.wb_min[2]);
-    V3 pmax = mk(S.wb_max[0], S.wb_max[1], S.wb_max[2]);
-    V3 o = p - pmin;  // Bounds3::Offset
-    if (pmax.x > pmin.x) o.x /= pmax.x - pmin.x;
-    if (pmax.y > pmin.y) o.y /= pmax.y - pmin.y;
-    if (pmax.z > pmin.z) o.z /= pmax.z - pmin.z;
-    int pi0 = min(max((int)(o.x * (float)S.n_voxels[0]), 0), S.n_voxels[0] - 1);
-    int pi1 = min(max((int)(o.y * (float)S.n_voxels[1]), 0), S.n_voxels[1] - 1);
-    int pi2 = min(max((int)(o.z * (float)S.n_voxels[2]), 0), S.n_voxels[2] - 1);
-    size_t voxel = ((size_t)pi0 * S.n_voxels[1] + pi1) * S.n_voxels[2] + pi2;
-    const float *row = S.voxel_tables + voxel * (size_t)(2 * n + 2);
-    return sample_discrete(row, row + n, n, __ldg(row + 2 * n + 1), u, pdf);
-}
-
-SPTX_DEV float power_heuristic(float fPdf, float gPdf) {
-    float f = 1.f * fPdf, g = 1.f * gPdf;
-    return (f * f) / (f * f + g * g);
-}
-
 
 struct Row4 {
     float4 *p;

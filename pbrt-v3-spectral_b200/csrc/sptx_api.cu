@@ -16,6 +16,12 @@
 
 using namespace sptx;
 
+namespace sptx {  // shade.cu
+void launch_shade(cudaStream_t stream, int smCount, int64_t nPaths, const DScene *dS, const DSampler *dH,
+                  const PathArrays &A, const RenderParams &R, int qi, int betaIn, DeviceCounters *cnt);
+const char *shade_arithmetic();
+}  // namespace sptx
+
 static std::string g_last_error;
 
 struct sptx_ctx {
@@ -818,9 +824,6 @@ static int render_pixels(sptx_ctx *ctx, const std::vector<int2> &pixels, int s0,
             R.ignoreRayWeight = ctx->metadataStrategy && !dSampleList;
             const int64_t nPaths = (int64_t)nPix * R.samplesInPass;
             const int g = grid_for(ctx, nPaths);
-            // one resident block per SM; chunks = class queues in block-sized pieces
-            const int gShade = (int)std::min<int64_t>((nPaths + kShadeBlock - 1) / kShadeBlock + kShadeClasses,
-                                                     (int64_t)ctx->smCount * kShadeBlocksPerSM);
             if (ctx->metadataStrategy && !dSampleList) {
                 // MetadataIntegrator: camera ray, closest hit, the hit's attribute as "radiance"
                 R.band = 0;
@@ -861,8 +864,8 @@ static int render_pixels(sptx_ctx *ctx, const std::vector<int2> &pixels, int s0,
                         k_intersect<false><<<g, kBlock, 0, ctx->stream>>>(ctx->S, A, qi, ctx->dCnt);
                     toc();
                     tic(2);
-                    k_shade<<<gShade, kShadeBlock, 0, ctx->stream>>>(ctx->dS, ctx->dH, A, R, qi, betaIn,
-                                                                     ctx->dCnt);
+                    launch_shade(ctx->stream, ctx->smCount, nPaths, ctx->dS, ctx->dH, A, R, qi, betaIn,
+                                 ctx->dCnt);
                     toc();
                     if (bounce < maxDepth) {
                         tic(3);

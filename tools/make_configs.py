@@ -8,8 +8,8 @@
     C4  instanced_c4      100 instances of a 199,712-triangle mesh (2.0e7 instanced triangles)
 
 Runs only in the build container (needs /root/reference, host/_build/pbrt_b200, oracle/_ref).
-Blobs go to scenes/_gen/ (git-ignored for the large ones; they travel to the GPU box with the
-tree).  Fixtures are reference outputs reduced to a committable size:
+Blobs go to scenes/_gen/ (the two large ones, C1 and C4, are committed xz-compressed and unpacked
+on first use by capi.unpack_blob).  Fixtures are reference outputs reduced to a committable size:
     c1: the reference's 64-spp .dat as 8x8 block means          -> tests/golden/c1_killeroo400.npz
     c3: the reference's 2-spp .dat as 16x16 block means         -> tests/golden/c3_cornell_lens2048.npz
     c2: the reference's 4-spp .dat as 8x8 block means           -> tests/golden/c2_cornell1024.npz
@@ -40,8 +40,12 @@ def block_means(planes, k):
     return planes.reshape(b, h // k, k, w // k, k).mean(axis=(2, 4)).astype(np.float32)
 
 
-def flatten(pbrt, blob, work):
+def flatten(pbrt, blob, work, pack=False):
     mg.run([mg.PBRT_B200, "--quiet", pbrt], env={"SPTX_DUMP_SCENE": blob, "SPTX_DUMP_ONLY": "1"}, cwd=work)
+    if pack:  # the committed form of the large blobs (capi.unpack_blob restores them)
+        import lzma
+        with open(blob, "rb") as src, lzma.open(blob + ".xz", "wb", preset=9) as dst:
+            dst.write(src.read())
 
 
 def c1():
@@ -49,7 +53,7 @@ def c1():
     spec = dict(ref="killeroo-simple.pbrt", res=(400, 400), spp=64)
     with tempfile.TemporaryDirectory() as work:
         pbrt = mg.scene_file(name, spec, work)
-        flatten(pbrt, os.path.join(mg.GEN, name + ".sptx"), work)
+        flatten(pbrt, os.path.join(mg.GEN, name + ".sptx"), work, pack=True)
         mg.run([mg.PBRT_REF, "--quiet", "--nthreads", NT, pbrt], cwd=work)
         dat = capi.read_dat(os.path.join(work, name + ".dat"))
     np.savez_compressed(os.path.join(mg.GOLD, "c1_killeroo400.npz"), res=np.array([400, 400]), spp=np.array(64),
@@ -84,7 +88,7 @@ def c4():
         mg.run([sys.executable, os.path.join(ROOT, "scenes", "gen_scenes.py"), "instanced", pbrt,
                 "res=1024", "spp=4", "grid=317", "inst=10"])
         blob = os.path.join(mg.GEN, name + ".sptx")
-        flatten(pbrt, blob, work)
+        flatten(pbrt, blob, work, pack=True)
         lo, hi = mg.read_root_bounds(blob)
         n_sub = 1 << 17
         rays = config_rays.incoherent_rays(n_sub, lo, hi, first=0)
