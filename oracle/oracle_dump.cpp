@@ -9,6 +9,8 @@
 //   ORACLE_RAYS_IN / ORACLE_HITS_OUT     Scene::Intersect  (BVHAccel::Intersect,
 //                                        src/accelerators/bvh.cpp:662-700)
 //   ORACLE_RAYS_IN / ORACLE_ANYHIT_OUT   Scene::IntersectP (bvh.cpp:702-738)
+//   ORACLE_RAYS_IN / ORACLE_SPAWN_OUT    SurfaceInteraction::SpawnRay / SpawnRayTo from the hits
+//                                        (src/tests/shapes.cpp:154-205), ORACLE_SPAWN_K per kind
 //   ORACLE_CAMSAMPLES_IN / ORACLE_CAMRAYS_OUT   Camera::GenerateRayDifferential
 //   ORACLE_HALTON_IN / ORACLE_HALTON_OUT HaltonSampler::SampleDimension
 //                                        (src/samplers/halton.cpp:96-127)
@@ -282,6 +284,59 @@ void DumpIntegrator::Render(const Scene &scene) {
                 hits[i] = h;
             }, n, 4096);
             WriteAll(out, hits);
+        }
+        if (const char *out = getenv("ORACLE_SPAWN_OUT")) {
+            // src/tests/shapes.cpp:154-205 (Triangle.Reintersect) on a whole scene: for every input ray
+            // that hits, ORACLE_SPAWN_K rays leave the hit through the reference's own
+            // SurfaceInteraction::SpawnRay(w) (w uniform on the sphere, RNG(i) as in the test) and as
+            // many through SpawnRayTo(a seeded point of the scene bound).  Output records: the
+            // spawned ray (RayIn layout) followed by the parent's primitive / instance index.
+            const int K = std::max(1, atoi(getenv("ORACLE_SPAWN_K") ? getenv("ORACLE_SPAWN_K") : "4"));
+            struct SpawnOut {
+                RayIn ray;
+                int32_t parentPrim, parentInst;
+            };
+            std::vector<SpawnOut> spawned((size_t)n * 2 * K);
+            std::vector<uint8_t> valid((size_t)n, 0);
+            const Bounds3f wb = scene.WorldBound();
+            ParallelFor([&](int64_t i) {
+                Ray r(Point3f(rays[i].o[0], rays[i].o[1], rays[i].o[2]),
+                      Vector3f(rays[i].d[0], rays[i].d[1], rays[i].d[2]), rays[i].tMax, rays[i].time);
+                SurfaceInteraction isect;
+                if (!scene.Intersect(r, &isect)) return;
+                int32_t pp = -1, pi = -1;
+                index.Lookup(isect, &pp, &pi);
+                valid[i] = 1;
+                RNG rng((uint64_t)i);
+                for (int j = 0; j < 2 * K; ++j) {
+                    Point2f u;
+                    u[0] = rng.UniformFloat();
+                    u[1] = rng.UniformFloat();
+                    Ray out;
+                    if (j < K)
+                        out = isect.SpawnRay(UniformSampleSphere(u));
+                    else {
+                        Float w = rng.UniformFloat();
+                        Point3f p2 = wb.Lerp(Point3f(u[0], u[1], w));
+                        out = isect.SpawnRayTo(p2);
+                    }
+                    SpawnOut &o = spawned[(size_t)i * 2 * K + j];
+                    for (int c = 0; c < 3; ++c) {
+                        o.ray.o[c] = out.o[c];
+                        o.ray.d[c] = out.d[c];
+                    }
+                    o.ray.tMax = out.tMax;
+                    o.ray.time = 0;
+                    o.parentPrim = pp;
+                    o.parentInst = pi;
+                }
+            }, n, 1024);
+            std::vector<SpawnOut> kept;
+            for (int64_t i = 0; i < n; ++i)
+                if (valid[i])
+                    kept.insert(kept.end(), spawned.begin() + (size_t)i * 2 * K,
+                                spawned.begin() + (size_t)(i + 1) * 2 * K);
+            WriteAll(out, kept);
         }
         if (const char *out = getenv("ORACLE_ANYHIT_OUT")) {
             std::vector<int32_t> any(n);

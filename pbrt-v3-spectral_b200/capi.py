@@ -59,11 +59,14 @@ def lib():
     global _lib
     if _lib is not None:
         return _lib
-    if not os.path.exists(LIB_PATH):
+    path = LIB_PATH
+    if os.environ.get("SPTX_LIB"):   # experiments: another build of the same library (Makefile LIB=)
+        path = os.path.join(os.path.dirname(LIB_PATH), os.environ["SPTX_LIB"])
+    if not os.path.exists(path):
         raise SptxError(
-            f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+            f"{path} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
             "(there is no fallback implementation)")
-    L = C.CDLL(LIB_PATH)
+    L = C.CDLL(path)
     vp, i32, i64, f32p = C.c_void_p, C.c_int, C.c_int64, C.POINTER(C.c_float)
     i32p = C.POINTER(C.c_int32)
     L.sptx_abi_version.restype = i32
