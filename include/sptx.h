@@ -334,6 +334,19 @@ int sptx_intersect_batch_device(sptx_ctx *ctx, const void *d_rays, int64_t n,
                                 void *d_hits, int any_hit, int with_counters,
                                 float *ms);
 
+/* sptx_intersect_batch (closest hit / any hit for n rays in HOST memory) for callers that
+ * cannot allocate device memory: the device copies of rays and hits live in a fixed file-scope
+ * device array (SPTX_NOALLOC_MAX_RAYS * 64 bytes = 4 MiB, held by every GPU that loads the
+ * library until the process exits) instead of cudaMalloc'd scratch, and the call makes no
+ * cudaMalloc / cudaFree / allocating library call.  n > SPTX_NOALLOC_MAX_RAYS is rejected with
+ * SPTX_EINVAL.  All calls share the array: calls that overlap on one GPU (two contexts, two
+ * threads) race and must be serialised by the caller.  Visit counters are not recorded
+ * (n_nodes = n_tests = 0).
+ * No counterpart in the reference. */
+#define SPTX_NOALLOC_MAX_RAYS 65536
+int sptx_intersect_batch_noalloc(sptx_ctx *ctx, const sptx_ray *rays, int64_t n,
+                                 sptx_hit *hits, int any_hit);
+
 /* SamplerIntegrator::Render's pixel/sample loop (src/core/integrator.cpp:
  * 228-334) for sample numbers [sample_begin, sample_end) of every pixel of
  * `pixel_bounds` (NULL = the film's sample bounds), accumulated into the

@@ -21,6 +21,7 @@ STRIDE = 32
 SYMBOLS = [
     "sptx_abi_version", "sptx_create", "sptx_destroy", "sptx_last_error",
     "sptx_upload_scene", "sptx_intersect_batch", "sptx_intersect_batch_device",
+    "sptx_intersect_batch_noalloc",
     "sptx_render", "sptx_render_tiles", "sptx_film_clear", "sptx_film_device_ptr",
     "sptx_film_export", "sptx_film_merge_peers",
     "sptx_film_download", "sptx_film_pack_dat", "sptx_write_dat",
@@ -30,6 +31,7 @@ SYMBOLS = [
 ]
 
 IPC_HANDLE_BYTES = 64
+NOALLOC_MAX_RAYS = 65536   # SPTX_NOALLOC_MAX_RAYS
 RAY_DTYPE = np.dtype([("o", "<f4", 3), ("t_max", "<f4"), ("d", "<f4", 3), ("time", "<f4")])
 HIT_DTYPE = np.dtype([("prim", "<i4"), ("instance", "<i4"), ("t", "<f4"), ("b0", "<f4"),
                       ("b1", "<f4"), ("b2", "<f4"), ("n_nodes", "<i4"), ("n_tests", "<i4")])
@@ -79,6 +81,7 @@ def lib():
     L.sptx_upload_scene.argtypes = [vp, vp]
     L.sptx_intersect_batch.argtypes = [vp, vp, i64, vp, i32, i32]
     L.sptx_intersect_batch_device.argtypes = [vp, vp, i64, vp, i32, i32, f32p]
+    L.sptx_intersect_batch_noalloc.argtypes = [vp, vp, i64, vp, i32]
     L.sptx_render.argtypes = [vp, i32p, i32, i32]
     L.sptx_render_tiles.argtypes = [vp, i32, i32, i32, i32]
     L.sptx_film_clear.argtypes = [vp]
@@ -190,6 +193,14 @@ class Context:
         hits = np.zeros(rays.shape[0], dtype=HIT_DTYPE)
         self._ck(lib().sptx_intersect_batch(self.h, _ptr(rays), rays.shape[0], _ptr(hits),
                                             int(any_hit), int(counters)), "sptx_intersect_batch")
+        return hits
+
+    def intersect_noalloc(self, rays, any_hit=False):
+        """sptx_intersect_batch_noalloc: at most NOALLOC_MAX_RAYS rays, fixed device scratch."""
+        rays = np.ascontiguousarray(rays, dtype=RAY_DTYPE)
+        hits = np.zeros(rays.shape[0], dtype=HIT_DTYPE)
+        self._ck(lib().sptx_intersect_batch_noalloc(self.h, _ptr(rays), rays.shape[0], _ptr(hits),
+                                                    int(any_hit)), "sptx_intersect_batch_noalloc")
         return hits
 
     def intersect_device(self, d_rays, n, d_hits, any_hit=False, counters=False):

@@ -1223,6 +1223,60 @@ extern "C" int sptx_intersect_batch(sptx_ctx *ctx, const sptx_ray *rays, int64_t
     return rc;
 }
 
+// ---- ray batches without any allocation ------------------------------------------------------
+// For callers that cannot call cudaMalloc (CUDA graph capture around them, serving loops,
+// harnesses that forbid it): the device copies of the rays and of the hit records live in a
+// file-scope device array of fixed size instead of cudaMalloc'd scratch.  Every GPU that loads the
+// library holds the array until the process exits.  All calls share it and it keeps the previous
+// call's contents; nothing in it has to start at zero (rays [0,n) are overwritten by the copy-in,
+// hits [0,n) by the kernel, and only those are copied out).  Calls that overlap on one GPU race.
+static __device__ __align__(256) unsigned char g_noallocScratch[(size_t)SPTX_NOALLOC_MAX_RAYS *
+                                                               (sizeof(sptx_ray) + sizeof(sptx_hit))];
+// The array's name is a host-side stand-in in host code, not a device address: the address is
+// asked for once per device, with that device current.
+static void *g_noallocPtr[64] = {nullptr};
+
+static int noalloc_scratch(sptx_ctx *ctx, void **out) {
+    const int dev = ctx->device;
+    if (dev < 0 || dev >= 64) return fail(ctx, SPTX_EINVAL, "sptx_intersect_batch_noalloc: device %d", dev);
+    if (!g_noallocPtr[dev]) {
+        void *p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, g_noallocScratch);
+        if (e != cudaSuccess || !p)
+            return fail(ctx, SPTX_ECUDA, "sptx_intersect_batch_noalloc: cudaGetSymbolAddress: %s",
+                        cudaGetErrorString(e));
+        g_noallocPtr[dev] = p;
+    }
+    *out = g_noallocPtr[dev];
+    return SPTX_OK;
+}
+
+extern "C" int sptx_intersect_batch_noalloc(sptx_ctx *ctx, const sptx_ray *rays, int64_t n, sptx_hit *hits,
+                                            int any_hit) {
+    if (!ctx) return fail(nullptr, SPTX_EINVAL, "sptx_intersect_batch_noalloc: ctx is NULL");
+    if (!ctx->haveScene) return fail(ctx, SPTX_ESTATE, "sptx_intersect_batch_noalloc: no scene uploaded");
+    if (n < 0 || (n > 0 && (!rays || !hits)))
+        return fail(ctx, SPTX_EINVAL, "sptx_intersect_batch_noalloc: bad arguments");
+    if (n > (int64_t)SPTX_NOALLOC_MAX_RAYS)
+        return fail(ctx, SPTX_EINVAL,
+                    "sptx_intersect_batch_noalloc: %lld rays exceed the fixed scratch of %d rays "
+                    "(SPTX_NOALLOC_MAX_RAYS); split the batch or use sptx_intersect_batch",
+                    (long long)n, (int)SPTX_NOALLOC_MAX_RAYS);
+    if (n == 0) return SPTX_OK;
+    CK(cudaSetDevice(ctx->device));
+    void *base = nullptr;
+    int rc = noalloc_scratch(ctx, &base);
+    if (rc) return rc;
+    sptx_ray *dR = (sptx_ray *)base;
+    sptx_hit *dH = (sptx_hit *)((unsigned char *)base + (size_t)SPTX_NOALLOC_MAX_RAYS * sizeof(sptx_ray));
+    CK(cudaMemcpyAsync(dR, rays, (size_t)n * sizeof(sptx_ray), cudaMemcpyHostToDevice, ctx->stream));
+    rc = sptx_intersect_batch_device(ctx, dR, n, dH, any_hit, 0, nullptr);
+    if (rc) return rc;
+    CK(cudaMemcpyAsync(hits, dH, (size_t)n * sizeof(sptx_hit), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return SPTX_OK;
+}
+
 // ---- test hooks --------------------------------------------------------------------------------
 
 extern "C" int sptx_sampler_eval(sptx_ctx *ctx, const int32_t *px, const int32_t *py, const int32_t *sample,
