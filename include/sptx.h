@@ -281,7 +281,7 @@ typedef struct sptx_hit {
     int32_t prim;     /* global index into prims[] of the hit primitive, -1 = miss */
     int32_t instance; /* index into instances[] of the enclosing instance, -1 = none */
     float t;          /* ray.tMax after the traversal                         */
-    float b0, b1, b2; /* triangle barycentrics at the hit (0 for spheres)     */
+    float b0, b1, b2; /* triangle: barycentrics at the hit; sphere: its object-space hit point */
     int32_t n_nodes;  /* BVH nodes visited (only when counters are enabled)   */
     int32_t n_tests;  /* primitive tests made (only when counters are enabled) */
 } sptx_hit; /* 32 B */

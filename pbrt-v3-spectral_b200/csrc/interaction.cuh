@@ -92,14 +92,14 @@ SPTX_NOINL void triangle_interaction(const DScene &S, int shape, V3 rayD, float 
     it->sdpdu = sdpdu;
 }
 
-// Object-space sphere interaction moved to the sphere's parent space.
-SPTX_NOINL bool sphere_interaction(const DScene &S, int shape, const Ray &ray, Isect *it) {
+// Object-space sphere interaction moved to the sphere's parent space.  `pHit` is the refined
+// object-space hit point Sphere::Intersect computed (shapes/sphere.cpp:84-90), carried by the hit
+// record; `rayD` is the direction of the ray in the sphere's parent space.
+SPTX_NOINL bool sphere_interaction_at(const DScene &S, int shape, V3 rayD, V3 pHit, Isect *it) {
     const sptx_sphere &sp = S.spheres[shape];
-    Ray r = ray;
-    r.tMax = kInf;  // the accepted root does not depend on tMax
     SphereHit sh;
-    if (!sphere_test(sp, r, &sh)) return false;
-    const V3 pHit = sh.pHit;
+    sh.pHit = pHit;
+    sh.oray.d = xf_vec(sp.w2o, rayD);
     const float radius = sp.radius;
     float theta = acosf(clampf(pHit.z / radius, -1.f, 1.f));
     float zRadius = sqrtf(pHit.x * pHit.x + pHit.y * pHit.y);
@@ -125,6 +125,15 @@ SPTX_NOINL bool sphere_interaction(const DScene &S, int shape, const Ray &ray, I
     return true;
 }
 
+// The same from a ray (Shape::Pdf intersects the emitter itself, core/shape.cpp:72-87).
+SPTX_NOINL bool sphere_interaction(const DScene &S, int shape, const Ray &ray, Isect *it) {
+    Ray r = ray;
+    r.tMax = kInf;
+    SphereHit sh;
+    if (!sphere_test(S.spheres[shape], r, &sh)) return false;
+    return sphere_interaction_at(S, shape, ray.d, sh.pHit, it);
+}
+
 // Scene-level interaction for a closest-hit record of world ray `ray`.
 SPTX_NOINL bool build_interaction(const DScene &S, const Ray &ray, int prim, int inst, float b0,
                                 float b1, float b2, Isect *it) {
@@ -136,8 +145,8 @@ SPTX_NOINL bool build_interaction(const DScene &S, const Ray &ray, int prim, int
     if (inst >= 0) lr = xf_ray(S.instances[inst].w2p, ray);
     if (P.kind == SPTX_PRIM_TRIANGLE)
         triangle_interaction(S, P.shape, lr.d, b0, b1, b2, it);
-    else if (!sphere_interaction(S, P.shape, lr, it))
-        return false;
+    else  // (b0, b1, b2) of a sphere hit = its object-space hit point
+        sphere_interaction_at(S, P.shape, lr.d, mk(b0, b1, b2), it);
     if (inst >= 0 && !S.instances[inst].is_identity) {
         // InterpolatedPrimToWorld(*isect), core/primitive.cpp:88-89
         const sptx_instance &I = S.instances[inst];

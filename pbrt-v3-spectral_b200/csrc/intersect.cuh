@@ -313,7 +313,11 @@ SPTX_DEV bool prim_test(const DScene &S, int gp, Ray &ray, HitRec *hit, int kind
         if (ANY) return true;
         ray.tMax = sh.tHit;
         hit->prim = gp;
-        hit->b0 = hit->b1 = hit->b2 = 0.f;
+        // a sphere hit carries its refined object-space hit point where a triangle hit carries
+        // its barycentrics: the interaction is built from it without intersecting again
+        hit->b0 = sh.pHit.x;
+        hit->b1 = sh.pHit.y;
+        hit->b2 = sh.pHit.z;
         return true;
     }
 }

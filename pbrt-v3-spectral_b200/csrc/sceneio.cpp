@@ -121,9 +121,22 @@ extern "C" int sptx_scene_load(const char *path, sptx_scene_desc **out) {
     memcpy(&tmp, blob + 16, sizeof(tmp));
     size_t pos = 16 + sizeof(tmp);
     if (pos % 16) pos += 16 - pos % 16;
+    // the counts come from the file: none may be negative (a negative count would wrap the size
+    // arithmetic below past the truncation check)
+    const int64_t counts[] = {tmp.n_nodes, tmp.n_bvhs, tmp.n_prims, tmp.n_meshes, tmp.n_triangles,
+                              tmp.n_positions, tmp.n_normals, tmp.n_tangents, tmp.n_uvs, tmp.n_spheres,
+                              tmp.n_instances, tmp.n_materials, tmp.n_lobes, tmp.n_spectra, tmp.n_lights,
+                              tmp.n_lens_floats, tmp.n_pupil_floats, tmp.n_primes, tmp.n_prime_sums,
+                              tmp.n_perms};
+    for (int64_t c : counts)
+        if (c < 0 || c > (int64_t)size) {  // every element is at least one byte
+            free(blob);
+            g_io_error = std::string("corrupt scene file (array count out of range): ") + path;
+            return SPTX_EINVAL;
+        }
     std::vector<Section> secs = sections(&tmp);
     for (Section &s : secs) {
-        if (pos + s.bytes > (size_t)size) {
+        if (s.bytes > (size_t)size || pos > (size_t)size - s.bytes) {
             free(blob);
             g_io_error = std::string("truncated scene file: ") + path;
             return SPTX_EINVAL;

@@ -57,7 +57,12 @@ struct sptx_ctx {
     int64_t dLaccPaths = 0;
     int2 *dPixels = nullptr;
     int64_t dPixelsCap = 0;
-    std::vector<int2> pixelsKey;  // host copy of what dPixels holds
+    int64_t nPixels = 0;          // entries of dPixels in use
+    int pixelsKey[8] = {-1, 0, 0, 0, 0, 0, 0, 0};  // what dPixels holds: {kind, bounds / partition ...}
+    // grow-only device scratch of the entry points that stage host data (ray batches, .dat planes):
+    // no cudaMalloc / cudaFree per call (both are device-wide synchronisation points)
+    void *scratch[3] = {nullptr, nullptr, nullptr};
+    size_t scratchBytes[3] = {0, 0, 0};
     DFilm F;
     PathArrays A;
     sptx_integrator integ;
@@ -177,6 +182,19 @@ static void drop_spares(sptx_ctx *ctx) {
     ctx->spares.clear();
 }
 
+static int ctx_scratch(sptx_ctx *ctx, int slot, size_t bytes, void **out) {
+    if (bytes > ctx->scratchBytes[slot]) {
+        CK(cudaStreamSynchronize(ctx->stream));
+        if (ctx->scratch[slot]) cudaFree(ctx->scratch[slot]);
+        ctx->scratch[slot] = nullptr;
+        ctx->scratchBytes[slot] = 0;
+        CK(cudaMalloc(&ctx->scratch[slot], bytes));
+        ctx->scratchBytes[slot] = bytes;
+    }
+    *out = ctx->scratch[slot];
+    return SPTX_OK;
+}
+
 extern "C" int sptx_abi_version(void) { return SPTX_ABI_VERSION; }
 
 extern "C" const char *sptx_last_error(const sptx_ctx *ctx) {
@@ -220,7 +238,8 @@ extern "C" int sptx_create(int device, sptx_ctx **out) {
     cudaEventCreate(&ctx->ev3);
     if ((e = cudaMalloc((void **)&ctx->dCnt, sizeof(DeviceCounters))) != cudaSuccess)
         return bail(e, "cudaMalloc");
-    cudaMemset(ctx->dCnt, 0, sizeof(DeviceCounters));
+    cudaMemsetAsync(ctx->dCnt, 0, sizeof(DeviceCounters), ctx->stream);
+    cudaStreamSynchronize(ctx->stream);
     // Traversal keeps a 64-entry stack per thread in local memory.
     cudaDeviceSetLimit(cudaLimitStackSize, 2048);
     ctx->profileKernels = getenv("SPTX_PROFILE_KERNELS") != nullptr;
@@ -240,6 +259,8 @@ extern "C" void sptx_destroy(sptx_ctx *ctx) {
     if (ctx->dFilmSplit) cudaFree(ctx->dFilmSplit);
     if (ctx->dLacc) cudaFree(ctx->dLacc);
     if (ctx->dPixels) cudaFree(ctx->dPixels);
+    for (void *s : ctx->scratch)
+        if (s) cudaFree(s);
     if (ctx->dH) cudaFree(ctx->dH);
     cudaEventDestroy(ctx->ev0);
     cudaEventDestroy(ctx->ev1);
@@ -283,15 +304,30 @@ static int validate_scene(sptx_ctx *ctx, const sptx_scene_desc *sc) {
             "bvh node range out of bounds");
         REQ(b.prim_base >= 0 && b.n_prims >= 0 && (int64_t)b.prim_base + b.n_prims <= sc->n_prims,
             "bvh primitive range out of bounds");
+        // children come after their parent (checked below), so one forward pass gives every
+        // node's depth; the device's traversal stack holds 64 entries like the reference's
+        // (accelerators/bvh.cpp:671)
+        std::vector<uint8_t> depth((size_t)std::max(b.n_nodes, 1), 0);
         for (int k = 0; k < b.n_nodes; ++k) {
             const sptx_bvh_node &n = sc->nodes[b.node_base + k];
             if (n.n_prims > 0)
                 REQ(n.offset >= 0 && n.offset + (int)n.n_prims <= b.n_prims, "leaf range out of bounds");
-            else
+            else {
                 REQ(n.offset > k && n.offset < b.n_nodes && k + 1 < b.n_nodes && n.axis < 3,
                     "interior node malformed");
+                REQ(depth[k] < 63, "BVH deeper than the 64-entry traversal stack");
+                depth[k + 1] = std::max<uint8_t>(depth[k + 1], (uint8_t)(depth[k] + 1));
+                depth[n.offset] = std::max<uint8_t>(depth[n.offset], (uint8_t)(depth[k] + 1));
+            }
         }
+        if (i > 0)  // an instance's aggregate holds shapes only (no nested instances on the device)
+            for (int k = 0; k < b.n_prims; ++k)
+                if (sc->prims[b.prim_base + k].kind == SPTX_PRIM_INSTANCE)
+                    return fail(ctx, SPTX_EUNSUPPORTED, "sptx_upload_scene: nested object instances");
     }
+    REQ(sc->n_prims < ((int64_t)1 << 31) && sc->n_nodes < ((int64_t)1 << 31), "scene too large for 32-bit ids");
+    REQ(sc->integrator.max_depth <= 255,
+        "maxdepth above 255 (the path state keeps the bounce count in 8 bits)");
     for (int64_t i = 0; i < sc->n_prims; ++i) {
         const sptx_prim &p = sc->prims[i];
         REQ(p.material >= -1 && p.material < sc->n_materials, "material index out of range");
@@ -341,9 +377,21 @@ static int validate_scene(sptx_ctx *ctx, const sptx_scene_desc *sc) {
     for (int64_t i = 0; i < sc->n_lobes; ++i) {
         const sptx_lobe &l = sc->lobes[i];
         REQ(l.type >= SPTX_LOBE_LAMBERT && l.type <= SPTX_LOBE_FRESNEL_BLEND, "lobe type");
-        REQ(l.R < sc->n_spectra && l.T < sc->n_spectra && l.fr_eta_i < sc->n_spectra &&
+        REQ(l.R >= -1 && l.T >= -1 && l.fr_eta_i >= -1 && l.fr_eta_t >= -1 && l.fr_k >= -1 &&
+                l.R < sc->n_spectra && l.T < sc->n_spectra && l.fr_eta_i < sc->n_spectra &&
                 l.fr_eta_t < sc->n_spectra && l.fr_k < sc->n_spectra,
             "lobe spectrum row out of range");
+        // the rows a lobe of this type reads must exist
+        const bool needsT = l.type == SPTX_LOBE_SPECULAR_TRANS || l.type == SPTX_LOBE_FRESNEL_SPECULAR ||
+                            l.type == SPTX_LOBE_LAMBERT_TRANS || l.type == SPTX_LOBE_MICROFACET_TRANS ||
+                            l.type == SPTX_LOBE_FRESNEL_BLEND;
+        const bool needsR = l.type != SPTX_LOBE_SPECULAR_TRANS && l.type != SPTX_LOBE_LAMBERT_TRANS &&
+                            l.type != SPTX_LOBE_MICROFACET_TRANS;
+        REQ(!needsR || l.R >= 0, "lobe without its reflectance row");
+        REQ(!needsT || l.T >= 0, "lobe without its transmittance row");
+        if (l.fresnel == SPTX_FRESNEL_CONDUCTOR &&
+            (l.type == SPTX_LOBE_SPECULAR_REFL || l.type == SPTX_LOBE_MICROFACET_REFL))
+            REQ(l.fr_eta_i >= 0 && l.fr_eta_t >= 0 && l.fr_k >= 0, "conductor lobe without its Fresnel rows");
     }
     for (int64_t i = 0; i < sc->n_lights; ++i) {
         const sptx_light &l = sc->lights[i];
@@ -419,6 +467,7 @@ extern "C" int sptx_upload_scene(sptx_ctx *ctx, const sptx_scene_desc *sc) {
     mark("validate+drain");
     recycle_pool(ctx, ctx->sceneAllocs);
     ctx->haveScene = false;
+    ctx->pixelsKey[0] = -1;
     mark("free");
     std::vector<void *> &pool = ctx->sceneAllocs;
     DScene &S = ctx->S;
@@ -489,6 +538,7 @@ extern "C" int sptx_upload_scene(sptx_ctx *ctx, const sptx_scene_desc *sc) {
 
     // ---- light selection (core/lightdistrib.cpp:48-66) ----
     ctx->integ = sc->integrator;
+    if (ctx->integ.max_depth < 0) ctx->integ.max_depth = 0;  // (path.cpp:88-112: the first vertex is always visited)
     if (sc->metadata_strategy > SPTX_METADATA_COORDINATES)
         return fail(ctx, SPTX_EINVAL, "sptx_upload_scene: metadata strategy %u", sc->metadata_strategy);
     ctx->metadataStrategy = (int)sc->metadata_strategy;
@@ -747,32 +797,42 @@ static int render_serial(sptx_ctx *ctx, const int32_t *bounds, int part, int nPa
     return SPTX_OK;
 }
 
-// Renders `pixels` (host list) for sample numbers [s0, s1).
-static int render_pixels(sptx_ctx *ctx, const std::vector<int2> &pixels, int s0, int s1,
-                         const int *dSampleList = nullptr) {
-    if (pixels.empty() || s1 <= s0) return SPTX_OK;
+// Device pixel list of a render region.  `key` says what the list describes (rectangle, tile
+// partition): the list of the previous call is kept when the key is the same, so a caller that
+// renders the same region sample range after sample range pays for it once.
+static int set_pixels(sptx_ctx *ctx, const int key[8], const std::vector<int2> &pixels) {
+    const int64_t n = (int64_t)pixels.size();
+    if (n > ctx->dPixelsCap) {
+        CK(cudaStreamSynchronize(ctx->stream));
+        if (ctx->dPixels) cudaFree(ctx->dPixels);
+        ctx->dPixels = nullptr;
+        ctx->dPixelsCap = 0;
+        ctx->pixelsKey[0] = -1;
+        CK(cudaMalloc((void **)&ctx->dPixels, (size_t)n * sizeof(int2)));
+        ctx->dPixelsCap = n;
+    }
+    if (n > 0) {
+        CK(cudaMemcpyAsync(ctx->dPixels, pixels.data(), (size_t)n * sizeof(int2), cudaMemcpyHostToDevice,
+                           ctx->stream));
+        CK(cudaStreamSynchronize(ctx->stream));
+    }
+    ctx->nPixels = n;
+    memcpy(ctx->pixelsKey, key, sizeof(ctx->pixelsKey));
+    return SPTX_OK;
+}
+static bool have_pixels(const sptx_ctx *ctx, const int key[8]) {
+    return key[0] >= 0 && memcmp(ctx->pixelsKey, key, sizeof(ctx->pixelsKey)) == 0;
+}
+
+// Renders the pixels of ctx->dPixels for sample numbers [s0, s1).
+static int render_pixels(sptx_ctx *ctx, int s0, int s1, const int *dSampleList = nullptr) {
+    const int64_t nPixAll = ctx->nPixels;
+    if (nPixAll <= 0 || s1 <= s0) return SPTX_OK;
     int rc;
     const int64_t want = ctx->maxPaths > 0 ? ctx->maxPaths : ((int64_t)1 << 22);
-    const int64_t nPixAll = (int64_t)pixels.size();
     const int64_t chunkPix = dSampleList ? nPixAll : std::min<int64_t>(nPixAll, want);
     int S_pass = (int)std::max<int64_t>(1, std::min<int64_t>(s1 - s0, want / chunkPix));
     if ((rc = ensure_paths(ctx, chunkPix * S_pass))) return rc;
-    // the device copy of the pixel list is kept between calls (same region, next samples)
-    if (ctx->pixelsKey.size() != pixels.size() ||
-        memcmp(ctx->pixelsKey.data(), pixels.data(), pixels.size() * sizeof(int2)) != 0) {
-        if (nPixAll > ctx->dPixelsCap) {
-            if (ctx->dPixels) cudaFree(ctx->dPixels);
-            ctx->dPixels = nullptr;
-            ctx->dPixelsCap = 0;
-            ctx->pixelsKey.clear();
-            CK(cudaMalloc((void **)&ctx->dPixels, (size_t)nPixAll * sizeof(int2)));
-            ctx->dPixelsCap = nPixAll;
-        }
-        CK(cudaMemcpyAsync(ctx->dPixels, pixels.data(), (size_t)nPixAll * sizeof(int2),
-                           cudaMemcpyHostToDevice, ctx->stream));
-        CK(cudaStreamSynchronize(ctx->stream));
-        ctx->pixelsKey = pixels;
-    }
     int2 *dPixels = ctx->dPixels;
     PathArrays &A = ctx->A;
     const int maxDepth = ctx->integ.max_depth;
@@ -920,10 +980,12 @@ static int render_pixels(sptx_ctx *ctx, const std::vector<int2> &pixels, int s0,
     }
     ctx->counters.kernel_launches += launches;
     int flags[8];
-    CK(cudaMemcpy(flags, A.counters, sizeof(flags), cudaMemcpyDeviceToHost));
+    CK(cudaMemcpyAsync(flags, A.counters, sizeof(flags), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
     if (flags[3]) {
         int f = flags[3];
-        cudaMemset(A.counters + 3, 0, sizeof(int));
+        cudaMemsetAsync(A.counters + 3, 0, sizeof(int), ctx->stream);
+        cudaStreamSynchronize(ctx->stream);
         if (f & ERR_DIM_OVERFLOW)
             return fail(ctx, SPTX_EINVAL,
                         "render: a path ran past the %d Halton dimensions uploaded "
@@ -931,21 +993,6 @@ static int render_pixels(sptx_ctx *ctx, const std::vector<int2> &pixels, int s0,
         return fail(ctx, SPTX_EINVAL, "render: device error flags 0x%x", f);
     }
     return SPTX_OK;
-}
-
-static void region_pixels(const sptx_ctx *ctx, const int32_t *bounds, std::vector<int2> *out) {
-    int b[4];
-    for (int i = 0; i < 4; ++i) b[i] = ctx->F.f.sample_bounds[i];
-    auto clip = [&](const int32_t *o) {
-        b[0] = std::max(b[0], o[0]);
-        b[1] = std::max(b[1], o[1]);
-        b[2] = std::min(b[2], o[2]);
-        b[3] = std::min(b[3], o[3]);
-    };
-    clip(ctx->integ.pixel_bounds);  // the InsideExclusive(pixel, pixelBounds) test
-    if (bounds) clip(bounds);
-    for (int y = b[1]; y < b[3]; ++y)
-        for (int x = b[0]; x < b[2]; ++x) out->push_back(make_int2(x, y));
 }
 
 extern "C" int sptx_render(sptx_ctx *ctx, const int32_t *pixel_bounds, int sample_begin,
@@ -956,9 +1003,25 @@ extern "C" int sptx_render(sptx_ctx *ctx, const int32_t *pixel_bounds, int sampl
         return fail(ctx, SPTX_EINVAL, "sptx_render: bad sample range [%d,%d)", sample_begin, sample_end);
     CK(cudaSetDevice(ctx->device));
     if (ctx->H.s.type == SPTX_SAMPLER_RANDOM) return render_serial(ctx, pixel_bounds, 0, 1, sample_begin, sample_end);
-    std::vector<int2> pixels;
-    region_pixels(ctx, pixel_bounds, &pixels);
-    return render_pixels(ctx, pixels, sample_begin, sample_end);
+    int b[4];
+    for (int i = 0; i < 4; ++i) b[i] = ctx->F.f.sample_bounds[i];
+    auto clip = [&](const int32_t *o) {
+        b[0] = std::max(b[0], o[0]);
+        b[1] = std::max(b[1], o[1]);
+        b[2] = std::min(b[2], o[2]);
+        b[3] = std::min(b[3], o[3]);
+    };
+    clip(ctx->integ.pixel_bounds);  // the InsideExclusive(pixel, pixelBounds) test
+    if (pixel_bounds) clip(pixel_bounds);
+    const int key[8] = {1, b[0], b[1], b[2], b[3], 0, 0, 0};
+    if (!have_pixels(ctx, key)) {
+        std::vector<int2> pixels;
+        for (int y = b[1]; y < b[3]; ++y)
+            for (int x = b[0]; x < b[2]; ++x) pixels.push_back(make_int2(x, y));
+        int rc = set_pixels(ctx, key, pixels);
+        if (rc) return rc;
+    }
+    return render_pixels(ctx, sample_begin, sample_end);
 }
 
 extern "C" int sptx_render_tiles(sptx_ctx *ctx, int part, int n_parts, int sample_begin,
@@ -975,18 +1038,24 @@ extern "C" int sptx_render_tiles(sptx_ctx *ctx, int part, int n_parts, int sampl
     const int tileSize = 16;
     const int ntx = (sb[2] - sb[0] + tileSize - 1) / tileSize;
     const int nty = (sb[3] - sb[1] + tileSize - 1) / tileSize;
-    std::vector<int2> pixels;
-    for (int ty = 0; ty < nty; ++ty)
-        for (int tx = 0; tx < ntx; ++tx) {
-            if ((ty * ntx + tx) % n_parts != part) continue;
-            int x0 = sb[0] + tx * tileSize, x1 = std::min(x0 + tileSize, sb[2]);
-            int y0 = sb[1] + ty * tileSize, y1 = std::min(y0 + tileSize, sb[3]);
-            for (int y = y0; y < y1; ++y)
-                for (int x = x0; x < x1; ++x)
-                    if (x >= pb[0] && x < pb[2] && y >= pb[1] && y < pb[3])
-                        pixels.push_back(make_int2(x, y));
-        }
-    return render_pixels(ctx, pixels, sample_begin, sample_end);
+    const int key[8] = {2, part, n_parts, sb[0] ^ (sb[2] << 16), sb[1] ^ (sb[3] << 16), pb[0] ^ (pb[2] << 16),
+                        pb[1] ^ (pb[3] << 16), 0};
+    if (!have_pixels(ctx, key)) {
+        std::vector<int2> pixels;
+        for (int ty = 0; ty < nty; ++ty)
+            for (int tx = 0; tx < ntx; ++tx) {
+                if ((ty * ntx + tx) % n_parts != part) continue;
+                int x0 = sb[0] + tx * tileSize, x1 = std::min(x0 + tileSize, sb[2]);
+                int y0 = sb[1] + ty * tileSize, y1 = std::min(y0 + tileSize, sb[3]);
+                for (int y = y0; y < y1; ++y)
+                    for (int x = x0; x < x1; ++x)
+                        if (x >= pb[0] && x < pb[2] && y >= pb[1] && y < pb[3])
+                            pixels.push_back(make_int2(x, y));
+            }
+        int rc = set_pixels(ctx, key, pixels);
+        if (rc) return rc;
+    }
+    return render_pixels(ctx, sample_begin, sample_end);
 }
 
 // ---- film -----------------------------------------------------------------------------
@@ -1074,10 +1143,7 @@ extern "C" int sptx_film_merge_peers(sptx_ctx *ctx, const void *handles, int n_r
         P.film[r] = (const float *)mapped[r];
     }
     double *dPlanes = nullptr;
-    if (rc == SPTX_OK && planes) {
-        cudaError_t e = cudaMalloc((void **)&dPlanes, (size_t)nPix * SPTX_NBINS * sizeof(double));
-        if (e != cudaSuccess) rc = fail(ctx, SPTX_ECUDA, "sptx_film_merge_peers: %s", cudaGetErrorString(e));
-    }
+    if (rc == SPTX_OK && planes) rc = ctx_scratch(ctx, 0, (size_t)nPix * SPTX_NBINS * sizeof(double), (void **)&dPlanes);
     if (rc == SPTX_OK) {
         cudaEventRecord(ctx->ev2, ctx->stream);
         k_film_merge_pack<<<ctx->smCount * 4, 256, 0, ctx->stream>>>(P, ctx->F.pixels, nPix, ctx->F.f.scale, dPlanes);
@@ -1093,7 +1159,6 @@ extern "C" int sptx_film_merge_peers(sptx_ctx *ctx, const void *handles, int n_r
         if (rc == SPTX_OK && cudaEventElapsedTime(&ms, ctx->ev2, ctx->ev3) == cudaSuccess) ctx->counters.film_ms += ms;
         ctx->counters.kernel_launches += 1;
     }
-    if (dPlanes) cudaFree(dPlanes);
     for (int r = 0; r < n_ranks; ++r)
         if (mapped[r]) cudaIpcCloseMemHandle(mapped[r]);
     return rc;
@@ -1107,11 +1172,11 @@ extern "C" int sptx_film_pack_dat(sptx_ctx *ctx, double *planes) {
     const int64_t n = (int64_t)ctx->F.width * ctx->F.height * SPTX_NBINS;
     if (n == 0) return SPTX_OK;
     double *d = nullptr;
-    CK(cudaMalloc((void **)&d, (size_t)n * sizeof(double)));
+    int rc = ctx_scratch(ctx, 0, (size_t)n * sizeof(double), (void **)&d);
+    if (rc) return rc;
     k_pack_dat<<<grid_for(ctx, n), kBlock, 0, ctx->stream>>>(ctx->F, d);
     cudaError_t e = cudaMemcpyAsync(planes, d, (size_t)n * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
-    cudaFree(d);
     if (e != cudaSuccess) return fail(ctx, SPTX_ECUDA, "sptx_film_pack_dat: %s", cudaGetErrorString(e));
     return SPTX_OK;
 }
@@ -1136,7 +1201,8 @@ extern "C" int sptx_get_counters(sptx_ctx *ctx, sptx_counters *out) {
     CK(cudaSetDevice(ctx->device));
     DeviceCounters dc;
     CK(cudaStreamSynchronize(ctx->stream));
-    CK(cudaMemcpy(&dc, ctx->dCnt, sizeof(dc), cudaMemcpyDeviceToHost));
+    CK(cudaMemcpyAsync(&dc, ctx->dCnt, sizeof(dc), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
     ctx->counters.camera_rays = dc.cameraRays;
     ctx->counters.closest_hit_rays = dc.closestRays;
     ctx->counters.shadow_rays = dc.shadowRays;
@@ -1153,7 +1219,8 @@ extern "C" int sptx_reset_counters(sptx_ctx *ctx) {
     if (!ctx) return fail(nullptr, SPTX_EINVAL, "sptx_reset_counters: ctx is NULL");
     CK(cudaSetDevice(ctx->device));
     CK(cudaStreamSynchronize(ctx->stream));
-    CK(cudaMemset(ctx->dCnt, 0, sizeof(DeviceCounters)));
+    CK(cudaMemsetAsync(ctx->dCnt, 0, sizeof(DeviceCounters), ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
     memset(&ctx->counters, 0, sizeof(ctx->counters));
     return SPTX_OK;
 }
@@ -1206,21 +1273,15 @@ extern "C" int sptx_intersect_batch(sptx_ctx *ctx, const sptx_ray *rays, int64_t
     if (n == 0) return SPTX_OK;
     CK(cudaSetDevice(ctx->device));
     void *dR = nullptr, *dH = nullptr;
-    CK(cudaMalloc(&dR, (size_t)n * sizeof(sptx_ray)));
-    cudaError_t e = cudaMalloc(&dH, (size_t)n * sizeof(sptx_hit));
-    if (e != cudaSuccess) {
-        cudaFree(dR);
-        return fail(ctx, SPTX_ECUDA, "sptx_intersect_batch: %s", cudaGetErrorString(e));
-    }
-    int rc = SPTX_OK;
-    e = cudaMemcpyAsync(dR, rays, (size_t)n * sizeof(sptx_ray), cudaMemcpyHostToDevice, ctx->stream);
-    if (e == cudaSuccess) rc = sptx_intersect_batch_device(ctx, dR, n, dH, any_hit, with_counters, nullptr);
-    if (e == cudaSuccess && rc == SPTX_OK)
-        e = cudaMemcpy(hits, dH, (size_t)n * sizeof(sptx_hit), cudaMemcpyDeviceToHost);
-    cudaFree(dR);
-    cudaFree(dH);
-    if (e != cudaSuccess) return fail(ctx, SPTX_ECUDA, "sptx_intersect_batch: %s", cudaGetErrorString(e));
-    return rc;
+    int rc = ctx_scratch(ctx, 1, (size_t)n * sizeof(sptx_ray), &dR);
+    if (rc == SPTX_OK) rc = ctx_scratch(ctx, 2, (size_t)n * sizeof(sptx_hit), &dH);
+    if (rc) return rc;
+    CK(cudaMemcpyAsync(dR, rays, (size_t)n * sizeof(sptx_ray), cudaMemcpyHostToDevice, ctx->stream));
+    rc = sptx_intersect_batch_device(ctx, dR, n, dH, any_hit, with_counters, nullptr);
+    if (rc) return rc;
+    CK(cudaMemcpyAsync(hits, dH, (size_t)n * sizeof(sptx_hit), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return SPTX_OK;
 }
 
 // ---- ray batches without any allocation ------------------------------------------------------
@@ -1346,7 +1407,9 @@ extern "C" int sptx_debug_radiance(sptx_ctx *ctx, const int32_t *px, const int32
     std::vector<void *> pool;
     const int32_t *dS;
     int rc = upload(ctx, pool, sample, n, &dS);
-    if (rc == SPTX_OK) rc = render_pixels(ctx, pixels, 0, 1, dS);
+    const int noKey[8] = {-1, 0, 0, 0, 0, 0, 0, 0};
+    if (rc == SPTX_OK) rc = set_pixels(ctx, noKey, pixels);
+    if (rc == SPTX_OK) rc = render_pixels(ctx, 0, 1, dS);
     free_pool(ctx, pool);
     if (rc) return rc;
     const PathArrays &A = ctx->A;

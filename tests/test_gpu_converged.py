@@ -1,0 +1,39 @@
+"""north_star's render criterion as a test: converged spectral radiance at 4096 spp agrees per bin
+within 0.5 % relative RMSE with the reference's own CPU render of the same scene file
+(tests/golden/make_converged.py made the fixtures with oracle/_ref/pbrt).  The run renders Halton
+sample numbers 0..4095 of every pixel, i.e. sample indices far beyond what the equal-spp fixtures
+(<= 256 spp) reach."""
+import numpy as np
+import pytest
+
+from conftest import blob_path, golden
+
+pytestmark = pytest.mark.gpu
+TOLERANCE = 0.005   # north_star: "< 0.5 % at 4096 spp"
+
+
+@pytest.mark.parametrize("name", ["converged_cornell", "converged_lens"])
+def test_converged_radiance_matches_the_reference_render(capi, name):
+    g = golden(name)
+    w, h = [int(v) for v in g["res"]]
+    spp = int(g["spp"])
+    assert spp == 4096
+    ctx = capi.Context(0)
+    sf = capi.SceneFile(blob_path(name))
+    ctx.upload(sf)
+    sf.close()
+    ctx.render(0, spp)
+    mine = ctx.film_pack_dat(w, h)
+    ref = g["dat"].astype(np.float64)
+    rel_rmse = np.sqrt(((mine - ref) ** 2).mean(axis=(1, 2))) / np.maximum(ref.mean(axis=(1, 2)), 1e-30)
+    assert rel_rmse.max() < TOLERANCE, f"{name}: per-bin relRMSE {rel_rmse.max():.3e} at {spp} spp"
+    # and no bias: whole-image energy of every bin within 0.1 %
+    ratio = mine.sum(axis=(1, 2)) / ref.sum(axis=(1, 2))
+    assert np.abs(ratio - 1).max() < 1e-3, ratio
+    # the same samples rendered as two calls (sample numbers [0, 1000) then [1000, 4096)) give the same film
+    ctx.film_clear()
+    ctx.render(0, 1000)
+    ctx.render(1000, spp)
+    again = ctx.film_pack_dat(w, h)
+    np.testing.assert_allclose(again, mine, rtol=2e-5, atol=1e-6 * ref.mean())
+    ctx.close()

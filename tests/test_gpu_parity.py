@@ -73,10 +73,18 @@ def test_camera_rays(scene):
     np.testing.assert_allclose(rays["d"][ok], ref[ok, 4:7], rtol=1e-6, atol=1e-7)
 
 
+# Fraction of the fixture's samples allowed to differ from the reference by more than 1e-4
+# (relative to the sample's largest bin).  Measured with the exact build (profiles/r02b_diag.jsonl):
+# no sample above 1e-4 in any scene except killeroo128, where 0.15 % of the samples take a visibly
+# different value (all of them > 1e-3: discrete events, not drift -- a 1-ulp difference between the
+# device's and glibc's sinf / cosf in the sampled point of the sphere light or in the microfacet
+# half vector decides a grazing shadow ray on the finely tessellated mesh the other way).
+LI_ALLOWED_ABOVE_1E4 = {"killeroo128": 3e-3}
+
+
 def test_per_sample_radiance(scene):
-    """PathIntegrator::Li per (pixel, sample): same Halton stream, same path -> same L
-    up to libm rounding; a few paths may branch differently (a hit flipping on a 1-ulp
-    direction difference), so the bar is on the bulk, not on every sample."""
+    """PathIntegrator::Li per (pixel, sample): same Halton stream, same path -> same L up to libm
+    rounding (measured ~1e-7).  The documented bar is 1e-4 relative per sample."""
     name, g, ctx = scene
     q = g["li_q"]
     L, pw = ctx.debug_radiance(q[:, 0], q[:, 1], q[:, 2])
@@ -84,8 +92,10 @@ def test_per_sample_radiance(scene):
     np.testing.assert_allclose(pw[:, 0:2], ref[:, 31:33], rtol=0, atol=0)
     scale = np.maximum(np.abs(ref[:, :31]).max(axis=1), 1e-3)
     err = np.abs(L - ref[:, :31]).max(axis=1) / scale
-    frac_bad = (err > 1e-3).mean()
-    assert frac_bad < 0.01, f"{name}: {frac_bad:.3%} of samples differ by more than 1e-3"
+    frac_bad = (err > 1e-4).mean()
+    allowed = LI_ALLOWED_ABOVE_1E4.get(name, 5e-4)
+    assert frac_bad <= allowed, f"{name}: {frac_bad:.3%} of samples differ by more than 1e-4 (allowed {allowed:.3%})"
+    assert np.median(err) <= 1e-6
     assert abs(L.mean() - ref[:, :31].mean()) <= 0.01 * abs(ref[:, :31].mean()) + 1e-6
 
 
