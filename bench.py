@@ -317,7 +317,8 @@ def bench_ours(args):
             "config": {"workload": WORKLOAD, "samples_per_step": RES_W * RES_H * SPP_STEP,
                        "spp_per_step": SPP_STEP, "partition": "sample numbers across ranks + film merge on rank 0"
                        if world > 1 else "single GPU",
-                       "l2": "path state of a pass (4.2 M paths, ~3.7 GB) exceeds L2 between launches"},
+                       "l2": "path state of a pass (4.2 M paths, ~3.7 GB) exceeds L2 between launches",
+                       "shade_arithmetic": ctx.shade_arithmetic},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "steps": e2e_steps,
                     "ms_per_step": {n: 1e3 * v / e2e_steps

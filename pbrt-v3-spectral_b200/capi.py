@@ -154,12 +154,23 @@ class SceneFile:
 class Context:
     """One GPU context (sptx_ctx).  Mirrors the call sequence of GpuPathIntegrator::Render."""
 
-    def __init__(self, device=0):
+    def __init__(self, device=0, exact=None):
+        """exact: K3's arithmetic -- True = the reference's roundings, False = the fast build of
+        K3 (FMA contraction, approximate division / square root), None = the library's default
+        (fast unless SPTX_EXACT=1 is in the environment)."""
         self.h = C.c_void_p()
         rc = lib().sptx_create(int(device), C.byref(self.h))
         if rc != 0:
             raise SptxError(f"sptx_create -> {rc}: {lib().sptx_last_error(None).decode()}")
         self.film_shape = None
+        env = os.environ.get("SPTX_EXACT", "")
+        self.exact = bool(env and env[0] != "0") if exact is None else bool(exact)
+        if exact is not None:
+            self.set_option("shade_exact", int(self.exact))
+
+    @property
+    def shade_arithmetic(self):
+        return "exact" if self.exact else "fast"
 
     def _ck(self, rc, what):
         if rc != 0:

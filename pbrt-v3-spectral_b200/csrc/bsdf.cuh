@@ -49,10 +49,22 @@ struct FTerm {
     int e0, e1, e2;  // conductor rows: etaI, etaT, k
     float s0, s1, s2, s3;
 };
-struct FSum {
+template <int MAXT>
+struct FSumN {
     int n;
-    FTerm t[kMaxTerms];
+    FTerm t[MAXT];
 };
+using FSum = FSumN<kMaxTerms>;
+
+// A shading variant (K3 is compiled once per variant, see shade.cuh) is the set of lobe types its
+// code can evaluate: branches for other types are removed at compile time.
+constexpr int kAllLobes = (1 << (SPTX_LOBE_FRESNEL_BLEND + 1)) - 1;
+template <int LOBES>
+SPTX_DEV constexpr bool has_lobe(int type) { return ((LOBES >> type) & 1) != 0; }
+constexpr int kSpecularLobes = (1 << SPTX_LOBE_SPECULAR_REFL) | (1 << SPTX_LOBE_SPECULAR_TRANS) |
+                               (1 << SPTX_LOBE_FRESNEL_SPECULAR);
+constexpr int kMicrofacetLobes = (1 << SPTX_LOBE_MICROFACET_REFL) | (1 << SPTX_LOBE_MICROFACET_TRANS) |
+                                 (1 << SPTX_LOBE_FRESNEL_BLEND);
 
 SPTX_DEV float spec(const DScene &S, int row, int b) {
     return __ldg(S.spectra + (size_t)row * SPTX_SPECTRUM_STRIDE + b);
@@ -123,7 +135,8 @@ SPTX_DEV float fterm_bin(const DScene &S, const FTerm &t, int b) {
     }
 }
 // Sum of terms in lobe order, starting from Spectrum(0) as BSDF::f does.
-SPTX_DEV float fsum_bin(const DScene &S, const FSum &f, int b) {
+template <int MAXT>
+SPTX_DEV float fsum_bin(const DScene &S, const FSumN<MAXT> &f, int b) {
     float v = 0.f;
     for (int i = 0; i < f.n; ++i) v += fterm_bin(S, f.t[i], b);
     return v;
@@ -138,52 +151,65 @@ SPTX_DEV float4 spec4(const DScene &S, int row, int c) {
 // 0 / d (or a conductor Fresnel term of an all-zero bin) would run the IEEE division and
 // square-root slow paths for nothing
 SPTX_DEV float padless(int c, float x, float d) { return c < 7 ? x / d : 0.f; }
+// (term kinds a variant can meet: R_S Lambert / Lambert transmission; R_S_S Oren-Nayar /
+//  microfacet transmission; MICRO_* microfacet reflection; *_DIV the specular lobes; BLEND)
+template <int LOBES>
 SPTX_DEV float4 fterm4(const DScene &S, const FTerm &t, int c) {
     const float4 R = spec4(S, t.R, c);
-    switch (t.kind) {
-    case TERM_R_S:
+    constexpr bool kRS = has_lobe<LOBES>(SPTX_LOBE_LAMBERT) || has_lobe<LOBES>(SPTX_LOBE_LAMBERT_TRANS);
+    constexpr bool kRSS = has_lobe<LOBES>(SPTX_LOBE_OREN_NAYAR) || has_lobe<LOBES>(SPTX_LOBE_MICROFACET_TRANS);
+    constexpr bool kMicro = has_lobe<LOBES>(SPTX_LOBE_MICROFACET_REFL);
+    constexpr bool kSpecR = has_lobe<LOBES>(SPTX_LOBE_SPECULAR_REFL) || has_lobe<LOBES>(SPTX_LOBE_FRESNEL_SPECULAR);
+    constexpr bool kSpecRC = has_lobe<LOBES>(SPTX_LOBE_SPECULAR_REFL);
+    constexpr bool kSpecT = has_lobe<LOBES>(SPTX_LOBE_SPECULAR_TRANS) || has_lobe<LOBES>(SPTX_LOBE_FRESNEL_SPECULAR);
+    constexpr bool kBlend = has_lobe<LOBES>(SPTX_LOBE_FRESNEL_BLEND);
+    if (kRS && (t.kind == TERM_R_S || !(kRSS || kMicro || kSpecR || kSpecT || kBlend)))
         return make_float4(R.x * t.s0, R.y * t.s0, R.z * t.s0, R.w * t.s0);
-    case TERM_R_S_S:
+    if (kRSS && t.kind == TERM_R_S_S)
         return make_float4(R.x * t.s0 * t.s1, R.y * t.s0 * t.s1, R.z * t.s0 * t.s1, R.w * t.s0 * t.s1);
-    case TERM_MICRO_S:
+    if (kMicro && t.kind == TERM_MICRO_S)
         return make_float4(R.x * t.s0 * t.s1 * t.s2 / t.s3, R.y * t.s0 * t.s1 * t.s2 / t.s3,
                            R.z * t.s0 * t.s1 * t.s2 / t.s3, padless(c, R.w * t.s0 * t.s1 * t.s2, t.s3));
-    case TERM_MICRO_COND: {
+    if (kMicro && t.kind == TERM_MICRO_COND) {
         const float4 ei = spec4(S, t.e0, c), et = spec4(S, t.e1, c), k = spec4(S, t.e2, c);
         return make_float4(R.x * t.s0 * t.s1 * fr_conductor_bin(t.s2, ei.x, et.x, k.x) / t.s3,
                            R.y * t.s0 * t.s1 * fr_conductor_bin(t.s2, ei.y, et.y, k.y) / t.s3,
                            R.z * t.s0 * t.s1 * fr_conductor_bin(t.s2, ei.z, et.z, k.z) / t.s3,
                            c < 7 ? R.w * t.s0 * t.s1 * fr_conductor_bin(t.s2, ei.w, et.w, k.w) / t.s3 : 0.f);
     }
-    case TERM_S_R_DIV:
+    if (kSpecR && t.kind == TERM_S_R_DIV)
         return make_float4(t.s0 * R.x / t.s1, t.s0 * R.y / t.s1, t.s0 * R.z / t.s1,
                            padless(c, t.s0 * R.w, t.s1));
-    case TERM_COND_R_DIV: {
+    if (kSpecRC && t.kind == TERM_COND_R_DIV) {
         const float4 ei = spec4(S, t.e0, c), et = spec4(S, t.e1, c), k = spec4(S, t.e2, c);
         return make_float4(fr_conductor_bin(t.s0, ei.x, et.x, k.x) * R.x / t.s1,
                            fr_conductor_bin(t.s0, ei.y, et.y, k.y) * R.y / t.s1,
                            fr_conductor_bin(t.s0, ei.z, et.z, k.z) * R.z / t.s1,
                            c < 7 ? fr_conductor_bin(t.s0, ei.w, et.w, k.w) * R.w / t.s1 : 0.f);
     }
-    case TERM_BLEND: {
+    if (kBlend && t.kind == TERM_BLEND) {
         const float4 rs = spec4(S, t.e0, c);
         return make_float4(blend_bin(R.x, rs.x, t.s0, t.s1, t.s2, t.s3), blend_bin(R.y, rs.y, t.s0, t.s1, t.s2, t.s3),
                            blend_bin(R.z, rs.z, t.s0, t.s1, t.s2, t.s3),
                            c < 7 ? blend_bin(R.w, rs.w, t.s0, t.s1, t.s2, t.s3) : 0.f);
     }
-    default:  // TERM_T_S_S_DIV
+    if (kSpecT)  // TERM_T_S_S_DIV
         return make_float4((R.x * t.s0) * t.s1 / t.s2, (R.y * t.s0) * t.s1 / t.s2,
                            (R.z * t.s0) * t.s1 / t.s2, padless(c, (R.w * t.s0) * t.s1, t.s2));
-    }
+    return make_float4(0.f, 0.f, 0.f, 0.f);
 }
-SPTX_DEV float4 fsum4(const DScene &S, const FSum &f, int c) {
+template <int LOBES = kAllLobes, int MAXT = kMaxTerms>
+SPTX_DEV float4 fsum4(const DScene &S, const FSumN<MAXT> &f, int c) {
     float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (int i = 0; i < f.n; ++i) {
-        const float4 t = fterm4(S, f.t[i], c);
-        v.x += t.x;
-        v.y += t.y;
-        v.z += t.z;
-        v.w += t.w;
+#pragma unroll
+    for (int i = 0; i < MAXT; ++i) {
+        if (i < f.n) {
+            const float4 t = fterm4<LOBES>(S, f.t[i], c);
+            v.x += t.x;
+            v.y += t.y;
+            v.z += t.z;
+            v.w += t.w;
+        }
     }
     return v;
 }

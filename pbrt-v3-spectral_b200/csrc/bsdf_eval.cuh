@@ -48,7 +48,11 @@ SPTX_DEV int lobe_flags(int type) {
 }
 SPTX_DEV bool matches(int lobeFlags, int flags) { return (lobeFlags & flags) == lobeFlags; }
 
+template <int LOBES = kAllLobes>
 SPTX_DEV int bsdf_num_components(const DScene &S, const Bsdf &b, int flags) {
+    // a variant made of specular lobes only has no component outside BSDF_SPECULAR
+    if ((LOBES & ~kSpecularLobes) == 0 && !(flags & BSDF_SPECULAR)) return 0;
+    if (LOBES == (1 << SPTX_LOBE_LAMBERT)) return b.n;  // 0 or 1 diffuse reflection lobe
     int num = 0;
     for (int i = 0; i < b.n; ++i)
         if (matches(lobe_flags(S.lobes[b.first + i].type), flags)) ++num;
@@ -57,17 +61,18 @@ SPTX_DEV int bsdf_num_components(const DScene &S, const Bsdf &b, int flags) {
 
 // BxDF::f for the non-specular lobes; appends one term (or nothing when the
 // lobe evaluates to zero).
-SPTX_NOINL void lobe_f(const sptx_lobe &L, V3 wo, V3 wi, FSum *out) {
+template <int LOBES = kAllLobes, int MAXT = kMaxTerms>
+SPTX_NOINL void lobe_f(const sptx_lobe &L, V3 wo, V3 wi, FSumN<MAXT> *out) {
     FTerm t;
     t.R = L.R;
     t.e0 = L.fr_eta_i;
     t.e1 = L.fr_eta_t;
     t.e2 = L.fr_k;
     t.s0 = t.s1 = t.s2 = t.s3 = 0.f;
-    if (L.type == SPTX_LOBE_LAMBERT) {
+    if (has_lobe<LOBES>(SPTX_LOBE_LAMBERT) && L.type == SPTX_LOBE_LAMBERT) {
         t.kind = TERM_R_S;
         t.s0 = kInvPi;
-    } else if (L.type == SPTX_LOBE_OREN_NAYAR) {
+    } else if (has_lobe<LOBES>(SPTX_LOBE_OREN_NAYAR) && L.type == SPTX_LOBE_OREN_NAYAR) {
         // OrenNayar::f, core/reflection.cpp:197-219
         float sinThetaI = sin_theta(wi), sinThetaO = sin_theta(wo);
         float maxCos = 0;
@@ -88,7 +93,7 @@ SPTX_NOINL void lobe_f(const sptx_lobe &L, V3 wo, V3 wi, FSum *out) {
         t.kind = TERM_R_S_S;
         t.s0 = kInvPi;
         t.s1 = (L.A + L.B * maxCos * sinAlpha * tanBeta);
-    } else if (L.type == SPTX_LOBE_MICROFACET_REFL) {
+    } else if (has_lobe<LOBES>(SPTX_LOBE_MICROFACET_REFL) && L.type == SPTX_LOBE_MICROFACET_REFL) {
         // MicrofacetReflection::f, core/reflection.cpp:226-236
         float cosThetaO = abs_cos_theta(wo), cosThetaI = abs_cos_theta(wi);
         V3 wh = wi + wo;
@@ -106,12 +111,12 @@ SPTX_NOINL void lobe_f(const sptx_lobe &L, V3 wo, V3 wi, FSum *out) {
             t.kind = TERM_MICRO_S;
             t.s2 = (L.fresnel == SPTX_FRESNEL_DIELECTRIC) ? fr_dielectric(c, L.eta_a, L.eta_b) : 1.f;
         }
-    } else if (L.type == SPTX_LOBE_LAMBERT_TRANS) {
+    } else if (has_lobe<LOBES>(SPTX_LOBE_LAMBERT_TRANS) && L.type == SPTX_LOBE_LAMBERT_TRANS) {
         // LambertianTransmission::f, core/reflection.cpp:187-190
         t.kind = TERM_R_S;
         t.R = L.T;
         t.s0 = kInvPi;
-    } else if (L.type == SPTX_LOBE_MICROFACET_TRANS) {
+    } else if (has_lobe<LOBES>(SPTX_LOBE_MICROFACET_TRANS) && L.type == SPTX_LOBE_MICROFACET_TRANS) {
         // MicrofacetTransmission::f, core/reflection.cpp:244-266
         if (same_hemisphere(wo, wi)) return;
         float cosThetaO = cos_theta(wo), cosThetaI = cos_theta(wi);
@@ -128,7 +133,7 @@ SPTX_NOINL void lobe_f(const sptx_lobe &L, V3 wo, V3 wi, FSum *out) {
         t.s1 = fabsf(tr_D(L.alpha_x, L.alpha_y, wh) * tr_G(L.alpha_x, L.alpha_y, wo, wi) * eta * eta *
                      absdot(wi, wh) * absdot(wo, wh) * factor * factor /
                      (cosThetaI * cosThetaO * sqrtDenom * sqrtDenom));
-    } else if (L.type == SPTX_LOBE_FRESNEL_BLEND) {
+    } else if (has_lobe<LOBES>(SPTX_LOBE_FRESNEL_BLEND) && L.type == SPTX_LOBE_FRESNEL_BLEND) {
         // FresnelBlend::f, core/reflection.cpp:285-299
         V3 wh = wi + wo;
         if (wh.x == 0 && wh.y == 0 && wh.z == 0) return;
@@ -144,21 +149,23 @@ SPTX_NOINL void lobe_f(const sptx_lobe &L, V3 wo, V3 wi, FSum *out) {
                (4.f * absdot(wi, wh) * fmaxf(abs_cos_theta(wi), abs_cos_theta(wo)));
     } else
         return;  // specular lobes: f() == 0
-    if (out->n < kMaxTerms) out->t[out->n++] = t;
+    if (out->n < MAXT) out->t[out->n++] = t;
 }
 
 // BxDF::Pdf, core/reflection.cpp:386-388 and MicrofacetReflection::Pdf :418-422.
+template <int LOBES = kAllLobes>
 SPTX_NOINL float lobe_pdf(const sptx_lobe &L, V3 wo, V3 wi) {
-    if (L.type == SPTX_LOBE_LAMBERT || L.type == SPTX_LOBE_OREN_NAYAR)
+    if ((has_lobe<LOBES>(SPTX_LOBE_LAMBERT) && L.type == SPTX_LOBE_LAMBERT) ||
+        (has_lobe<LOBES>(SPTX_LOBE_OREN_NAYAR) && L.type == SPTX_LOBE_OREN_NAYAR))
         return same_hemisphere(wo, wi) ? abs_cos_theta(wi) * kInvPi : 0.f;
-    if (L.type == SPTX_LOBE_MICROFACET_REFL) {
+    if (has_lobe<LOBES>(SPTX_LOBE_MICROFACET_REFL) && L.type == SPTX_LOBE_MICROFACET_REFL) {
         if (!same_hemisphere(wo, wi)) return 0.f;
         V3 wh = normalize(wo + wi);
         return tr_pdf(L, wo, wh) / (4.f * dot(wo, wh));
     }
-    if (L.type == SPTX_LOBE_LAMBERT_TRANS)  // core/reflection.cpp:400-403
+    if (has_lobe<LOBES>(SPTX_LOBE_LAMBERT_TRANS) && L.type == SPTX_LOBE_LAMBERT_TRANS)  // core/reflection.cpp:400-403
         return !same_hemisphere(wo, wi) ? abs_cos_theta(wi) * kInvPi : 0.f;
-    if (L.type == SPTX_LOBE_MICROFACET_TRANS) {
+    if (has_lobe<LOBES>(SPTX_LOBE_MICROFACET_TRANS) && L.type == SPTX_LOBE_MICROFACET_TRANS) {
         // MicrofacetTransmission::Pdf, core/reflection.cpp:436-448
         if (same_hemisphere(wo, wi)) return 0.f;
         float eta = cos_theta(wo) > 0 ? (L.eta_b / L.eta_a) : (L.eta_a / L.eta_b);
@@ -167,7 +174,7 @@ SPTX_NOINL float lobe_pdf(const sptx_lobe &L, V3 wo, V3 wi) {
         float dwh_dwi = fabsf((eta * eta * dot(wi, wh)) / (sqrtDenom * sqrtDenom));
         return tr_pdf(L, wo, wh) * dwh_dwi;
     }
-    if (L.type == SPTX_LOBE_FRESNEL_BLEND) {
+    if (has_lobe<LOBES>(SPTX_LOBE_FRESNEL_BLEND) && L.type == SPTX_LOBE_FRESNEL_BLEND) {
         // FresnelBlend::Pdf, core/reflection.cpp:470-475
         if (!same_hemisphere(wo, wi)) return 0.f;
         V3 wh = normalize(wo + wi);
@@ -178,32 +185,54 @@ SPTX_NOINL float lobe_pdf(const sptx_lobe &L, V3 wo, V3 wi) {
 }
 
 // BSDF::f, core/reflection.cpp:670-683.
-SPTX_NOINL void bsdf_f(const DScene &S, const Bsdf &b, V3 woW, V3 wiW, int flags, FSum *f) {
+// The matte variant: a material is one LambertianReflection lobe (or none, Kd black), which
+// matches every `flags` the path asks with; the generic lobe loops below reduce to this.
+constexpr int kLambertOnly = 1 << SPTX_LOBE_LAMBERT;
+template <int MAXT>
+SPTX_DEV void lambert_term(const DScene &S, const Bsdf &b, FSumN<MAXT> *f) {
+    FTerm t;
+    t.kind = TERM_R_S;
+    t.R = S.lobes[b.first].R;
+    t.e0 = t.e1 = t.e2 = -1;
+    t.s0 = kInvPi;
+    t.s1 = t.s2 = t.s3 = 0.f;
+    f->t[0] = t;
+    f->n = 1;
+}
+
+template <int LOBES = kAllLobes, int MAXT = kMaxTerms>
+SPTX_NOINL void bsdf_f(const DScene &S, const Bsdf &b, V3 woW, V3 wiW, int flags, FSumN<MAXT> *f) {
     f->n = 0;
     V3 wi = to_local(b, wiW), wo = to_local(b, woW);
     if (wo.z == 0) return;
     bool reflect = dot(wiW, b.ng) * dot(woW, b.ng) > 0;
+    if (LOBES == kLambertOnly) {
+        if (b.n > 0 && reflect) lambert_term(S, b, f);
+        return;
+    }
     for (int i = 0; i < b.n; ++i) {
         const sptx_lobe &L = S.lobes[b.first + i];
         int lf = lobe_flags(L.type);
         if (matches(lf, flags) &&
             ((reflect && (lf & BSDF_REFLECTION)) || (!reflect && (lf & BSDF_TRANSMISSION))))
-            lobe_f(L, wo, wi, f);
+            lobe_f<LOBES>(L, wo, wi, f);
     }
 }
 
 // BSDF::Pdf, core/reflection.cpp:770-785.
+template <int LOBES = kAllLobes>
 SPTX_NOINL float bsdf_pdf(const DScene &S, const Bsdf &b, V3 woW, V3 wiW, int flags) {
     if (b.n == 0) return 0.f;
     V3 wo = to_local(b, woW), wi = to_local(b, wiW);
     if (wo.z == 0) return 0.f;
+    if (LOBES == kLambertOnly) return same_hemisphere(wo, wi) ? abs_cos_theta(wi) * kInvPi : 0.f;
     float pdf = 0.f;
     int matching = 0;
     for (int i = 0; i < b.n; ++i) {
         const sptx_lobe &L = S.lobes[b.first + i];
         if (matches(lobe_flags(L.type), flags)) {
             ++matching;
-            pdf += lobe_pdf(L, wo, wi);
+            pdf += lobe_pdf<LOBES>(L, wo, wi);
         }
     }
     return matching > 0 ? pdf / (float)matching : 0.f;
@@ -218,12 +247,31 @@ SPTX_DEV V3 cosine_sample_hemisphere(V2 u) {
 
 // BSDF::Sample_f, core/reflection.cpp:703-768.  Returns false when the
 // reference returns a black spectrum with pdf == 0 (f->n == 0, *pdf == 0).
+template <int LOBES = kAllLobes, int MAXT = kMaxTerms>
 SPTX_NOINL void bsdf_sample_f(const DScene &S, const Bsdf &b, V3 woW, V2 u, int type, V3 *wiW,
-                            float *pdf, int *sampledType, FSum *f) {
+                            float *pdf, int *sampledType, FSumN<MAXT> *f) {
     f->n = 0;
     *pdf = 0.f;
     *sampledType = 0;
-    int matching = bsdf_num_components(S, b, type);
+    if (LOBES == kLambertOnly) {
+        // matchingComps = 1, comp = 0, uRemapped = u (core/reflection.cpp:707-722), then
+        // BxDF::Sample_f (:378-385) and the f of the one lobe
+        if (b.n == 0) return;
+        const V3 wo = to_local(b, woW);
+        if (wo.z == 0) return;
+        *sampledType = BSDF_REFLECTION | BSDF_DIFFUSE;
+        V3 wi = cosine_sample_hemisphere(V2{fminf(u.x * 1.f - 0.f, kOneMinusEpsilon), u.y});
+        if (wo.z < 0) wi.z *= -1.f;
+        *pdf = same_hemisphere(wo, wi) ? abs_cos_theta(wi) * kInvPi : 0.f;
+        if (*pdf == 0) {
+            *sampledType = 0;
+            return;
+        }
+        *wiW = to_world(b, wi);
+        if (dot(*wiW, b.ng) * dot(woW, b.ng) > 0) lambert_term(S, b, f);
+        return;
+    }
+    int matching = bsdf_num_components<LOBES>(S, b, type);
     if (matching == 0) return;
     int comp = min((int)floorf(u.x * (float)matching), matching - 1);
     int chosen = -1, count = comp;
@@ -245,40 +293,41 @@ SPTX_NOINL void bsdf_sample_f(const DScene &S, const Bsdf &b, V3 woW, V2 u, int 
     t.e2 = L.fr_k;
     t.s0 = t.s1 = t.s2 = t.s3 = 0.f;
     bool haveTerm = false;
-    if (L.type == SPTX_LOBE_LAMBERT || L.type == SPTX_LOBE_OREN_NAYAR) {
+    if ((has_lobe<LOBES>(SPTX_LOBE_LAMBERT) && L.type == SPTX_LOBE_LAMBERT) ||
+        (has_lobe<LOBES>(SPTX_LOBE_OREN_NAYAR) && L.type == SPTX_LOBE_OREN_NAYAR)) {
         // BxDF::Sample_f, core/reflection.cpp:378-385
         wi = cosine_sample_hemisphere(ur);
         if (wo.z < 0) wi.z *= -1.f;
-        *pdf = lobe_pdf(L, wo, wi);
-    } else if (L.type == SPTX_LOBE_MICROFACET_REFL) {
+        *pdf = lobe_pdf<LOBES>(L, wo, wi);
+    } else if (has_lobe<LOBES>(SPTX_LOBE_MICROFACET_REFL) && L.type == SPTX_LOBE_MICROFACET_REFL) {
         // MicrofacetReflection::Sample_f, core/reflection.cpp:405-416
         V3 wh = tr_sample_wh(L, wo, ur);
         wi = -wo + 2.f * dot(wo, wh) * wh;  // Reflect(wo, wh)
         if (same_hemisphere(wo, wi)) *pdf = tr_pdf(L, wo, wh) / (4.f * dot(wo, wh));
-    } else if (L.type == SPTX_LOBE_LAMBERT_TRANS) {
+    } else if (has_lobe<LOBES>(SPTX_LOBE_LAMBERT_TRANS) && L.type == SPTX_LOBE_LAMBERT_TRANS) {
         // LambertianTransmission::Sample_f, core/reflection.cpp:391-398
         wi = cosine_sample_hemisphere(ur);
         if (wo.z > 0) wi.z *= -1.f;
-        *pdf = lobe_pdf(L, wo, wi);
-    } else if (L.type == SPTX_LOBE_MICROFACET_TRANS) {
+        *pdf = lobe_pdf<LOBES>(L, wo, wi);
+    } else if (has_lobe<LOBES>(SPTX_LOBE_MICROFACET_TRANS) && L.type == SPTX_LOBE_MICROFACET_TRANS) {
         // MicrofacetTransmission::Sample_f, core/reflection.cpp:425-434
         V3 wh = tr_sample_wh(L, wo, ur);
         float eta = cos_theta(wo) > 0 ? (L.eta_a / L.eta_b) : (L.eta_b / L.eta_a);
-        if (refract(wo, wh, eta, &wi)) *pdf = lobe_pdf(L, wo, wi);
-    } else if (L.type == SPTX_LOBE_FRESNEL_BLEND) {
+        if (refract(wo, wh, eta, &wi)) *pdf = lobe_pdf<LOBES>(L, wo, wi);
+    } else if (has_lobe<LOBES>(SPTX_LOBE_FRESNEL_BLEND) && L.type == SPTX_LOBE_FRESNEL_BLEND) {
         // FresnelBlend::Sample_f, core/reflection.cpp:450-468
         if (ur.x < .5f) {
             V2 u2{fminf(2.f * ur.x, kOneMinusEpsilon), ur.y};
             wi = cosine_sample_hemisphere(u2);
             if (wo.z < 0) wi.z *= -1.f;
-            *pdf = lobe_pdf(L, wo, wi);
+            *pdf = lobe_pdf<LOBES>(L, wo, wi);
         } else {
             V2 u2{fminf(2.f * (ur.x - .5f), kOneMinusEpsilon), ur.y};
             V3 wh = tr_sample_wh(L, wo, u2);
             wi = -wo + 2.f * dot(wo, wh) * wh;  // Reflect(wo, wh)
-            if (same_hemisphere(wo, wi)) *pdf = lobe_pdf(L, wo, wi);
+            if (same_hemisphere(wo, wi)) *pdf = lobe_pdf<LOBES>(L, wo, wi);
         }
-    } else if (L.type == SPTX_LOBE_SPECULAR_REFL) {
+    } else if (has_lobe<LOBES>(SPTX_LOBE_SPECULAR_REFL) && L.type == SPTX_LOBE_SPECULAR_REFL) {
         // SpecularReflection::Sample_f, core/reflection.cpp:136-143
         wi = mk(-wo.x, -wo.y, wo.z);
         *pdf = 1.f;
@@ -292,7 +341,7 @@ SPTX_NOINL void bsdf_sample_f(const DScene &S, const Bsdf &b, V3 woW, V2 u, int 
                                                           : 1.f;
         }
         haveTerm = true;
-    } else if (L.type == SPTX_LOBE_SPECULAR_TRANS) {
+    } else if (has_lobe<LOBES>(SPTX_LOBE_SPECULAR_TRANS) && L.type == SPTX_LOBE_SPECULAR_TRANS) {
         // SpecularTransmission::Sample_f, core/reflection.cpp:150-166
         bool entering = cos_theta(wo) > 0;
         float etaI = entering ? L.eta_a : L.eta_b;
@@ -307,7 +356,7 @@ SPTX_NOINL void bsdf_sample_f(const DScene &S, const Bsdf &b, V3 woW, V2 u, int 
             t.s2 = abs_cos_theta(wi);
             haveTerm = true;
         }
-    } else {  // SPTX_LOBE_FRESNEL_SPECULAR, core/reflection.cpp:477-511
+    } else if (has_lobe<LOBES>(SPTX_LOBE_FRESNEL_SPECULAR)) {  // core/reflection.cpp:477-511
         float F = fr_dielectric(cos_theta(wo), L.eta_a, L.eta_b);
         if (ur.x < F) {
             wi = mk(-wo.x, -wo.y, wo.z);
@@ -342,7 +391,7 @@ SPTX_NOINL void bsdf_sample_f(const DScene &S, const Bsdf &b, V3 woW, V2 u, int 
     if (!(lf & BSDF_SPECULAR) && matching > 1)
         for (int i = 0; i < b.n; ++i) {
             const sptx_lobe &Lo = S.lobes[b.first + i];
-            if (i != chosen && matches(lobe_flags(Lo.type), type)) *pdf += lobe_pdf(Lo, wo, wi);
+            if (i != chosen && matches(lobe_flags(Lo.type), type)) *pdf += lobe_pdf<LOBES>(Lo, wo, wi);
         }
     if (matching > 1) *pdf /= (float)matching;
     if (!(lf & BSDF_SPECULAR)) {
@@ -352,7 +401,7 @@ SPTX_NOINL void bsdf_sample_f(const DScene &S, const Bsdf &b, V3 woW, V2 u, int 
             int f2 = lobe_flags(Lo.type);
             if (matches(f2, type) &&
                 ((reflect && (f2 & BSDF_REFLECTION)) || (!reflect && (f2 & BSDF_TRANSMISSION))))
-                lobe_f(Lo, wo, wi, f);
+                lobe_f<LOBES>(Lo, wo, wi, f);
         }
     } else if (haveTerm) {
         f->t[0] = t;

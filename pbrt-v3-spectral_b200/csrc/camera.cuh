@@ -24,7 +24,13 @@ SPTX_DEV V2 concentric_sample_disk(V2 u) {
         r = o.y;
         theta = kPiOver2 - kPiOver4 * (o.x / o.y);
     }
+#ifdef SPTX_SHADE_FAST   // K3's fast build: hardware sine / cosine (|theta| <= 3 pi / 4, abs. error < 5e-7)
+    float sn, cs;
+    __sincosf(theta, &sn, &cs);
+    return V2{r * cs, r * sn};
+#else
     return V2{r * cosf(theta), r * sinf(theta)};
+#endif
 }
 
 SPTX_DEV float perspective_ray(const DCamera &C, V2 pFilm, V2 pLensU, Ray *out) {

@@ -138,10 +138,10 @@ SPTX_NOINL float shape_pdf_generic(const DScene &S, int kind, int shape, const R
         tri_uvs(S, T, M, uv);
         V3 du, dv;
         if (!tri_partials(uv, p0, p1, p2, &du, &dv)) return 0.f;
-        Isect it;
-        triangle_interaction(S, shape, ray.d, b0, b1, b2, &it);
-        pHit = it.p;
-        nHit = it.n;
+        // of the interaction Triangle::Intersect builds only p and |n . wi| are used: the shading
+        // normal and the orientation flips change the sign of n at most (shapes/triangle.cpp:320-415)
+        pHit = b0 * p0 + b1 * p1 + b2 * p2;
+        nHit = normalize(cross(p0 - p2, p1 - p2));
     } else {
         Isect it;
         if (!sphere_interaction(S, shape, ray, &it)) return 0.f;

@@ -196,20 +196,24 @@ SPTX_DEV void halton_n(const DSampler &H, uint64_t index, int dim, float *out) {
         for (int j = 0; j < N; ++j) out[j] = halton_sample(H, index, dim + j);
         return;
     }
+    // (fast path: index * base < 2^32, so a < 2^31 and the round-down magic undershoots the
+    //  quotient by at most one: a * (1/base - magic/2^32) <= a / 2^32 < 1/2 -- one fix-up.  The
+    //  bases of consecutive dimensions ascend, so dimension `dim` has the most digits: the loop
+    //  runs while ITS digits last, the others drop out through their predicate.)
     uint32_t a[N], rev[N];
     float invN[N];
+    const uint16_t *perm[N];
 #pragma unroll
     for (int j = 0; j < N; ++j) {
         a[j] = (uint32_t)index;
         rev[j] = 0;
         invN[j] = 1.f;
+        perm[j] = H.perms + tab[j].z;
     }
-    bool more = (uint32_t)index != 0;
-    while (more) {
-        more = false;
+    while (a[0]) {
 #pragma unroll
         for (int j = 0; j < N; ++j) {
-            if (a[j]) {
+            if (j == 0 || a[j]) {
                 const uint32_t base = tab[j].x;
                 uint32_t next = __umulhi(a[j], tab[j].y);
                 uint32_t digit = a[j] - next * base;
@@ -217,14 +221,9 @@ SPTX_DEV void halton_n(const DSampler &H, uint64_t index, int dim, float *out) {
                     ++next;
                     digit -= base;
                 }
-                if (digit >= base) {
-                    ++next;
-                    digit -= base;
-                }
-                rev[j] = rev[j] * base + __ldg(H.perms + tab[j].z + digit);
+                rev[j] = rev[j] * base + __ldg(perm[j] + digit);
                 invN[j] *= __uint_as_float(tab[j].w);
                 a[j] = next;
-                more |= next != 0;
             }
         }
     }

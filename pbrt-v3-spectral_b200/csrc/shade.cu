@@ -1,14 +1,25 @@
-// shade.cu -- the translation unit of K3 (k_shade).
+// shade.cu -- the translation unit of K3 (k_shade), compiled TWICE into libsptx.so:
 //
-// K3 is compiled on its own so that its arithmetic mode can differ from the rest of the
-// library: traversal, the sampler and the camera (sptx_api.cu) must round like the
-// reference's x86-64 build (hit ids, t, Halton values and camera rays are bit-exact), while
-// per-sample radiance only has to meet north_star's tolerance (see the Makefile: SHADE_FLAGS).
+//   SPTX_SHADE_NS=shade_exact   the reference's roundings (no FMA contraction, IEEE division and
+//                               square root), like the rest of the library: per-sample radiance
+//                               agrees with the reference to ~1e-7;
+//   SPTX_SHADE_NS=shade_fast    -fmad=true -prec-div=false -prec-sqrt=false (-DSPTX_SHADE_FAST):
+//                               FMA contraction and approximate division / square root in K3 only.
+//
+// Traversal, the sampler and the camera live in sptx_api.cu and are exact in both: hit ids, t,
+// Halton values and camera rays stay bit-identical to the reference; only per-sample radiance
+// moves (by ~1e-7 relative per sample, unbiased; north_star's bar for it is 0.5 % relative RMSE).
+// The context picks the mode at run time (sptx_set_option "shade_exact").
 #include <algorithm>
 
 #include "shade.cuh"
 
+#ifndef SPTX_SHADE_NS
+#error "compile with -DSPTX_SHADE_NS=shade_exact or shade_fast"
+#endif
+
 namespace sptx {
+namespace SPTX_SHADE_NS {
 
 #ifdef SPTX_STAGE_CLOCKS
 __global__ void k_stage_clocks_print() {
@@ -22,26 +33,37 @@ __global__ void k_stage_clocks_print() {
 }
 #endif
 
-// One launch of K3 over the class queues K2 filled.  One resident block per SM; chunks =
-// class queues in block-sized pieces.
-void launch_shade(cudaStream_t stream, int smCount, int64_t nPaths, const DScene *dS, const DSampler *dH,
-                  const PathArrays &A, const RenderParams &R, int qi, int betaIn, DeviceCounters *cnt) {
-    const int grid = (int)std::min<int64_t>((nPaths + kShadeBlock - 1) / kShadeBlock + kShadeClasses,
+template <int V>
+static void launch_variant(cudaStream_t stream, int grid, const DScene *dS, const DSampler *dH, const PathArrays &A,
+                           const RenderParams &R, int qi, int betaIn, int cls, DeviceCounters *cnt) {
+    k_shade<kVariantLobes[V], kVariantTerms[V]><<<grid, kShadeBlock, 0, stream>>>(dS, dH, A, R, qi, betaIn, cls, cnt);
+}
+
+// K3 for one bounce: one launch per shading class in use, each with the variant compiled for
+// the class's lobe types; one resident block per SM, a class queue is walked in block-sized
+// chunks.  Returns the number of kernels launched.
+int launch_shade(cudaStream_t stream, int smCount, int64_t nPaths, const DScene *dS, const DSampler *dH,
+                 const PathArrays &A, const RenderParams &R, int qi, int betaIn, const ShadePlan &plan,
+                 DeviceCounters *cnt) {
+    const int grid = (int)std::min<int64_t>((nPaths + kShadeBlock - 1) / kShadeBlock,
                                             (int64_t)smCount * kShadeBlocksPerSM);
-    k_shade<<<grid, kShadeBlock, 0, stream>>>(dS, dH, A, R, qi, betaIn, cnt);
+    int launches = 1;
+    k_shade_miss<<<R.nBands > 1 ? std::max(1, std::min(grid, smCount * 4)) : 1, 256, 0, stream>>>(A, R, cnt);
+    for (int cls = 1; cls < kShadeClasses; ++cls) {
+        switch (plan.variant[cls]) {
+        case 0: launch_variant<0>(stream, grid, dS, dH, A, R, qi, betaIn, cls, cnt); break;
+        case 1: launch_variant<1>(stream, grid, dS, dH, A, R, qi, betaIn, cls, cnt); break;
+        case 2: launch_variant<2>(stream, grid, dS, dH, A, R, qi, betaIn, cls, cnt); break;
+        case 3: launch_variant<3>(stream, grid, dS, dH, A, R, qi, betaIn, cls, cnt); break;
+        default: continue;  // no primitive of the scene is in this class
+        }
+        ++launches;
+    }
 #ifdef SPTX_STAGE_CLOCKS
     k_stage_clocks_print<<<1, 1, 0, stream>>>();
 #endif
+    return launches;
 }
 
-// "exact" (the reference's roundings: no FMA contraction, IEEE division and square root) or
-// "fast" (FMA contraction, approximate division / square root / reciprocal in K3 only)
-const char *shade_arithmetic() {
-#ifdef SPTX_SHADE_FAST
-    return "fast";
-#else
-    return "exact";
-#endif
-}
-
+}  // namespace SPTX_SHADE_NS
 }  // namespace sptx

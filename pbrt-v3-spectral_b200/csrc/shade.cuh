@@ -3,11 +3,12 @@
 // integrators/path.cpp:88-184 for the vertex, core/integrator.cpp:85-215
 // (UniformSampleOneLight, EstimateDirect) for next-event estimation.
 //
-// One thread per path.  K2 hands the paths over sorted by shading class, so a
-// warp holds one kind of material and the 31-bin loops of its paths run without
-// diverging; no shared memory is used (the L1 keeps the whole carve-out for
-// the per-thread interaction / BSDF state).  Spectra are path-major ([P][32]
-// floats): a thread moves its 128-byte rows as float4.
+// One thread per path.  K2 hands the paths over sorted by shading class (one class per
+// material lobe signature), and K3 is launched once per class with the kernel VARIANT compiled
+// for that class's lobe types: a matte vertex runs code that contains no specular, microfacet or
+// Fresnel branch at all, a glass / mirror vertex code without next-event estimation.  No shared
+// memory is used (the L1 keeps the whole carve-out for the per-thread interaction / BSDF state).
+// Spectra are path-major ([P][32] floats): a thread moves its 128-byte rows as float4.
 // The two rays EstimateDirect traces (shadow ray, BSDF-sampled MIS ray) are
 // written out with their per-bin contributions (fa, fb) and traced by K4.
 #pragma once
@@ -18,6 +19,9 @@ namespace sptx {
 struct Row4 {
     float4 *p;
     SPTX_DEV float4 ld(int c) const { return p[c]; }
+    // rows this kernel only reads (the incoming beta): the read-only path tells the compiler that
+    // the stores to the other rows cannot alias them, so the eight loads issue together
+    SPTX_DEV float4 ldro(int c) const { return __ldg(p + c); }
     SPTX_DEV void st(int c, float4 v) const { p[c] = v; }
 };
 SPTX_DEV Row4 row4(float *base, int i) {
@@ -71,31 +75,27 @@ __device__ unsigned long long g_stageClocks[32];
         SPTX_TICK(slot + 1);                                   \
     } while (0)
 
+#ifdef SPTX_SHADE_NS
+namespace SPTX_SHADE_NS {  // (one copy of the kernels per arithmetic mode, see shade.cu)
+#endif
+
+template <int LOBES, int MAXT>
 __global__ void __launch_bounds__(kShadeBlock, kShadeBlocksPerSM)
 k_shade(const DScene *__restrict__ Sp, const DSampler *__restrict__ Hp, PathArrays A, RenderParams R,
-        int qi, int betaIn, DeviceCounters *cnt) {
+        int qi, int betaIn, int cls, DeviceCounters *cnt) {
     const DScene &S = *Sp;
     const DSampler &H = *Hp;
-    int classN[kShadeClasses], nChunks = 0, n = 0;
-    for (int c = 0; c < kShadeClasses; ++c) {
-        classN[c] = A.counters[kClassCounter0 + c];
-        nChunks += (classN[c] + (int)blockDim.x - 1) / (int)blockDim.x;
-        n += classN[c];
-    }
+    const int n = A.counters[kClassCounter0 + cls];
+    const int nChunks = (n + (int)blockDim.x - 1) / (int)blockDim.x;
+    const int *queue = A.qc + (size_t)cls * A.capacity;
     const int noSpec = BSDF_ALL & ~BSDF_SPECULAR;
 #ifdef SPTX_STAGE_CLOCKS
     long long stageClk[24] = {0};
     long long tPrev = clock64();
 #endif
     for (int chunk = blockIdx.x; chunk < nChunks; chunk += gridDim.x) {
-        int cls = 0, first = chunk;
-        while (first >= (classN[cls] + (int)blockDim.x - 1) / (int)blockDim.x) {
-            first -= (classN[cls] + (int)blockDim.x - 1) / (int)blockDim.x;
-            ++cls;
-        }
-        const int *queue = A.qc + (size_t)cls * A.capacity;
-        const int k = first * (int)blockDim.x + (int)threadIdx.x;
-        bool alive = k < classN[cls];
+        const int k = chunk * (int)blockDim.x + (int)threadIdx.x;
+        bool alive = k < n;
         const bool valid = alive;
         int i = 0, iNext = -1;
         SampleStream st{0, 0};
@@ -103,7 +103,7 @@ k_shade(const DScene *__restrict__ Sp, const DSampler *__restrict__ Hp, PathArra
         float lightPdfSel = 0.f, etaScale = 1.f, rayWeight = 0.f;
         Isect it;
         Bsdf bs;
-        FSum f;
+        FSumN<MAXT> f;
         Ray ray{mk(0, 0, 0), mk(0, 0, 1), kInf};
         // ---- stage 0: interaction, emission (path.cpp:91-112) ----
         if (alive) {
@@ -112,7 +112,7 @@ k_shade(const DScene *__restrict__ Sp, const DSampler *__restrict__ Hp, PathArra
             prefetch_l2(A.beta[betaIn] + (size_t)i * SPTX_SPECTRUM_STRIDE);
             {   // the next chunk of this block: its path state is a scattered gather, start it now
                 const int kn = k + (int)(gridDim.x * blockDim.x);
-                if (kn < classN[cls]) iNext = queue[kn];  // (same class only)
+                if (kn < n) iNext = queue[kn];
             }
 #endif
             const float4 ra = A.rayA[i], rb = A.rayB[i];
@@ -144,7 +144,7 @@ k_shade(const DScene *__restrict__ Sp, const DSampler *__restrict__ Hp, PathArra
                     const Row4 Lr = row4(A.L, i), br = row4(A.beta[betaIn], i);
                     for (int c = 0; c < 8; ++c) {
                         float4 l = Lr.ld(c);
-                        const float4 b = br.ld(c), e = spec4(S, Lt.spectrum, c);
+                        const float4 b = br.ldro(c), e = spec4(S, Lt.spectrum, c);
                         l.x += b.x * e.x;
                         l.y += b.y * e.y;
                         l.z += b.z * e.z;
@@ -161,7 +161,7 @@ k_shade(const DScene *__restrict__ Sp, const DSampler *__restrict__ Hp, PathArra
         V2 uLight{0, 0}, uScattering{0, 0};
         if (alive) {
             bsdf_init(S, it, &bs);
-            if (bsdf_num_components(S, bs, noSpec) > 0 && S.n_lights > 0) {
+            if (bsdf_num_components<LOBES>(S, bs, noSpec) > 0 && S.n_lights > 0) {
                 // the five values next-event estimation consumes (Get1D, Get2D, Get2D) are pure
                 // functions of (index, dimension): evaluated together, consumed as the reference does
                 float u5[5];
@@ -201,14 +201,14 @@ k_shade(const DScene *__restrict__ Sp, const DSampler *__restrict__ Hp, PathArra
         }
         SPTX_STAGE(4);
         if (nee && ls.pdf > 0 && !ls.black) {
-            bsdf_f(S, bs, it.wo, ls.wi, noSpec, &f);
+            bsdf_f<LOBES>(S, bs, it.wo, ls.wi, noSpec, &f);
             const float ad = absdot(ls.wi, it.ns);
-            const float scatteringPdf = bsdf_pdf(S, bs, it.wo, ls.wi, noSpec);
+            const float scatteringPdf = bsdf_pdf<LOBES>(S, bs, it.wo, ls.wi, noSpec);
             const float weight = delta ? 1.f : power_heuristic(ls.pdf, scatteringPdf);
             const Row4 fa = row4(A.fa, i);
             bool fNon = false, liNon = false;
             for (int c = 0; c < 8; ++c) {
-                float4 fv = fsum4(S, f, c), li = spec4(S, ls.spectrum, c);
+                float4 fv = fsum4<LOBES>(S, f, c), li = spec4(S, ls.spectrum, c);
                 if (ls.divisor != 0.f) {
                     li.x = li.x / ls.divisor;
                     li.y = li.y / ls.divisor;
@@ -243,7 +243,7 @@ k_shade(const DScene *__restrict__ Sp, const DSampler *__restrict__ Hp, PathArra
         if (nee && !delta) {
             float sPdf;
             int sType;
-            bsdf_sample_f(S, bs, it.wo, uScattering, noSpec, &misD, &sPdf, &sType, &f);
+            bsdf_sample_f<LOBES>(S, bs, it.wo, uScattering, noSpec, &misD, &sPdf, &sType, &f);
             if (f.n > 0 && sPdf > 0) {
                 float weight = 1.f;
                 bool skip = false;
@@ -261,7 +261,7 @@ k_shade(const DScene *__restrict__ Sp, const DSampler *__restrict__ Hp, PathArra
                     const Row4 fb = row4(A.fb, i);
                     bool fNon = false;
                     for (int c = 0; c < 8; ++c) {
-                        float4 fv = fsum4(S, f, c);
+                        float4 fv = fsum4<LOBES>(S, f, c);
                         const float4 le = spec4(S, leRow, c);
                         fv.x *= ad;
                         fv.y *= ad;
@@ -291,7 +291,7 @@ k_shade(const DScene *__restrict__ Sp, const DSampler *__restrict__ Hp, PathArra
             V3 wi;
             float pdf;
             int flags;
-            bsdf_sample_f(S, bs, it.wo, get2d(H, st), BSDF_ALL, &wi, &pdf, &flags, &f);
+            bsdf_sample_f<LOBES>(S, bs, it.wo, get2d(H, st), BSDF_ALL, &wi, &pdf, &flags, &f);
             bool fNon = false;
             float maxBeta = 0.f;
             const Row4 bIn = row4(A.beta[betaIn], i), bOut = row4(A.beta[betaIn ^ 1], i);
@@ -301,8 +301,12 @@ k_shade(const DScene *__restrict__ Sp, const DSampler *__restrict__ Hp, PathArra
                     etaScale *= (dot(it.wo, it.n) > 0) ? (eta * eta) : 1.f / (eta * eta);
                 }
                 const float ad = absdot(wi, it.ns);
+                float4 bRow[8];
+#pragma unroll
+                for (int c = 0; c < 8; ++c) bRow[c] = bIn.ldro(c);
+#pragma unroll
                 for (int c = 0; c < 8; ++c) {
-                    const float4 fv = fsum4(S, f, c), b = bIn.ld(c);
+                    const float4 fv = fsum4<LOBES>(S, f, c), b = bRow[c];
                     const float4 nb = make_float4(b.x * (fv.x * ad / pdf), b.y * (fv.y * ad / pdf),
                                                   b.z * (fv.z * ad / pdf), b.w * padless(c, fv.w * ad, pdf));
                     bOut.st(c, nb);
@@ -361,5 +365,23 @@ k_shade(const DScene *__restrict__ Sp, const DSampler *__restrict__ Hp, PathArra
 #endif
     if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&cnt->vertices, (unsigned long long)n);
 }
+
+// Class 0: paths whose ray left the scene.  PathIntegrator::Li ends them (there is no infinite
+// light on this path); with SpectralPathIntegrator bands the next band still needs the sampler
+// dimension the path stopped at.
+__global__ void k_shade_miss(PathArrays A, RenderParams R, DeviceCounters *cnt) {
+    const int n = A.counters[kClassCounter0];
+    if (R.nBands > 1)
+        for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
+            const int i = A.qc[k];
+            const uint32_t info = A.info[i];
+            A.info[i] = pack_info((int)(info & 0xffu), 0, (int)(info >> 16));
+        }
+    if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&cnt->vertices, (unsigned long long)n);
+}
+
+#ifdef SPTX_SHADE_NS
+}  // namespace SPTX_SHADE_NS
+#endif
 
 }  // namespace sptx

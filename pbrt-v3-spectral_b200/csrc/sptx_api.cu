@@ -16,10 +16,17 @@
 
 using namespace sptx;
 
-namespace sptx {  // shade.cu
-void launch_shade(cudaStream_t stream, int smCount, int64_t nPaths, const DScene *dS, const DSampler *dH,
-                  const PathArrays &A, const RenderParams &R, int qi, int betaIn, DeviceCounters *cnt);
-const char *shade_arithmetic();
+namespace sptx {  // shade.cu, compiled once per arithmetic mode
+namespace shade_exact {
+int launch_shade(cudaStream_t stream, int smCount, int64_t nPaths, const DScene *dS, const DSampler *dH,
+                 const PathArrays &A, const RenderParams &R, int qi, int betaIn, const ShadePlan &plan,
+                 DeviceCounters *cnt);
+}
+namespace shade_fast {
+int launch_shade(cudaStream_t stream, int smCount, int64_t nPaths, const DScene *dS, const DSampler *dH,
+                 const PathArrays &A, const RenderParams &R, int qi, int betaIn, const ShadePlan &plan,
+                 DeviceCounters *cnt);
+}
 }  // namespace sptx
 
 static std::string g_last_error;
@@ -72,6 +79,10 @@ struct sptx_ctx {
     sptx_counters counters;
     bool profileKernels = false;
     bool countVisits = false;
+    // K3's arithmetic: the reference's roundings, or FMA contraction + approximate division /
+    // square root (csrc/shade.cu).  SPTX_EXACT=1 in the environment makes exact the default.
+    bool shadeExact = false;
+    ShadePlan shadePlan;
     std::vector<cudaEvent_t> evPool;
     int smCount = 148;
 };
@@ -243,6 +254,11 @@ extern "C" int sptx_create(int device, sptx_ctx **out) {
     // Traversal keeps a 64-entry stack per thread in local memory.
     cudaDeviceSetLimit(cudaLimitStackSize, 2048);
     ctx->profileKernels = getenv("SPTX_PROFILE_KERNELS") != nullptr;
+    {
+        const char *ex = getenv("SPTX_EXACT");
+        ctx->shadeExact = ex && ex[0] && ex[0] != '0';
+    }
+    for (int c = 0; c < kShadeClasses; ++c) ctx->shadePlan.variant[c] = -1;
     *out = ctx;
     return SPTX_OK;
 }
@@ -275,6 +291,10 @@ extern "C" int sptx_set_option(sptx_ctx *ctx, const char *name, int64_t value) {
     if (!ctx || !name) return fail(ctx, SPTX_EINVAL, "sptx_set_option: NULL argument");
     if (!strcmp(name, "count_visits")) {
         ctx->countVisits = value != 0;
+        return SPTX_OK;
+    }
+    if (!strcmp(name, "shade_exact")) {  // 1: K3 with the reference's roundings; 0: the fast build of K3
+        ctx->shadeExact = value != 0;
         return SPTX_OK;
     }
     return fail(ctx, SPTX_EINVAL, "sptx_set_option: unknown option %s", name);
@@ -505,10 +525,27 @@ extern "C" int sptx_upload_scene(sptx_ctx *ctx, const sptx_scene_desc *sc) {
             matClass[(size_t)m] = (uint8_t)(1 + k % (kShadeClasses - 1));
         }
         std::vector<uint8_t> primClass((size_t)std::max<int64_t>(sc->n_prims, 1), 1);
+        // per class: the lobe types and the largest number of non-specular lobes of the materials
+        // its primitives use -> the K3 variant that shades the class
+        int classLobes[kShadeClasses] = {0}, classTerms[kShadeClasses] = {0};
+        bool classUsed[kShadeClasses] = {false};
         for (int64_t i = 0; i < sc->n_prims; ++i) {
             const int m = sc->prims[i].material;
-            primClass[(size_t)i] = m >= 0 ? matClass[(size_t)m] : (uint8_t)1;
+            const int cls = m >= 0 ? matClass[(size_t)m] : 1;
+            primClass[(size_t)i] = (uint8_t)cls;
+            if (sc->prims[i].kind == SPTX_PRIM_INSTANCE) continue;  // never the primitive of a hit
+            classUsed[cls] = true;
+            if (m < 0) continue;
+            int nonSpecular = 0;
+            for (int l = 0; l < sc->materials[m].n_lobes; ++l) {
+                const int ty = sc->lobes[sc->materials[m].first_lobe + l].type;
+                classLobes[cls] |= 1 << ty;
+                if (!((kSpecularLobes >> ty) & 1)) ++nonSpecular;
+            }
+            classTerms[cls] = std::max(classTerms[cls], nonSpecular);
         }
+        for (int c = 0; c < kShadeClasses; ++c)
+            ctx->shadePlan.variant[c] = (c > 0 && classUsed[c]) ? shade_variant_for(classLobes[c], classTerms[c]) : -1;
         if ((rc = upload(ctx, pool, primClass.data(), (int64_t)primClass.size(), &S.prim_class))) return rc;
     }
     if ((rc = upload(ctx, pool, sc->spectra, SPTX_SPECTRUM_STRIDE * sc->n_spectra, &S.spectra))) return rc;
@@ -924,9 +961,11 @@ static int render_pixels(sptx_ctx *ctx, int s0, int s1, const int *dSampleList =
                         k_intersect<false><<<g, kBlock, 0, ctx->stream>>>(ctx->S, A, qi, ctx->dCnt);
                     toc();
                     tic(2);
-                    launch_shade(ctx->stream, ctx->smCount, nPaths, ctx->dS, ctx->dH, A, R, qi, betaIn,
-                                 ctx->dCnt);
+                    const int nk = (ctx->shadeExact ? shade_exact::launch_shade : shade_fast::launch_shade)(
+                        ctx->stream, ctx->smCount, nPaths, ctx->dS, ctx->dH, A, R, qi, betaIn, ctx->shadePlan,
+                        ctx->dCnt);
                     toc();
+                    launches += nk - 1;
                     if (bounce < maxDepth) {
                         tic(3);
                         if (cv) {

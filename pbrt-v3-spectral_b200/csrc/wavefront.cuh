@@ -5,8 +5,8 @@
 // One "pass" carries nPix * S paths (S consecutive sample numbers of every
 // pixel of the render region); path id = s * nPix + pixel, so the film kernel
 // can add a pixel's samples in sample order, exactly like FilmTile::AddSample.
-// All per-path arrays are structure-of-arrays; spectra are bin-major
-// ([31][P]) so a warp reads 32 consecutive floats per bin.
+// All per-path arrays are structure-of-arrays; spectra are path-major ([P][32] floats, one
+// 128-byte line per path and quantity) so a thread moves its row as eight float4.
 #pragma once
 #include "light.cuh"
 #include "sampler.cuh"
@@ -19,15 +19,15 @@ struct PathArrays {
     float4 *rayA, *rayB;
     // closest hit of the path ray: {prim, inst, b0, b1} {b2, t, -, -}
     float4 *hitA, *hitB;
-    float *beta[2];  // [31][P], ping-pong per bounce
-    float *L;        // [31][P]
+    float *beta[2];  // [P][32], ping-pong per bounce
+    float *L;        // [P][32]
     uint64_t *sindex;  // Halton index of the path's sample
     uint32_t *info;    // bounces | specularBounce << 8 | dim << 16
     float2 *pfilm;
     // next-event estimation, pending until the resolve kernel
     float4 *shA, *shB;    // shadow ray {o.xyz, d.x} {d.y, d.z, tMax, lightPdfSel}
     float4 *misA, *misB;  // MIS ray {o.xyz, d.x} {d.y, d.z, bits(light), bits(flags)}
-    float *fa, *fb;       // [31][P] contributions of the two MIS strategies
+    float *fa, *fb;       // [P][32] contributions of the two MIS strategies
     // queues of path ids
     int *q[2];
     int *qNee;
@@ -44,6 +44,28 @@ constexpr int kShadeClasses = 8;  // class 0 = no hit
 constexpr int kClassCounter0 = 8;
 enum { NEE_HAS_SHADOW = 1, NEE_HAS_MIS = 2, NEE_MIS_REACHED_LIGHT = 4 };
 enum { ERR_DIM_OVERFLOW = 1, ERR_INTERACTION = 2, ERR_TERMS = 4 };
+
+// The kernel variants: lobe types a variant's code can evaluate, and how many non-specular lobes
+// (terms of BSDF::f) one of its materials may have.  sptx_upload_scene maps every shading class to
+// the first variant that covers its materials (shade_variant_for).
+constexpr int kNumShadeVariants = 4;
+constexpr int kVariantLobes[kNumShadeVariants] = {
+    1 << SPTX_LOBE_LAMBERT,                                    // matte
+    kSpecularLobes,                                            // glass, mirror: no light sampling
+    (1 << SPTX_LOBE_LAMBERT) | (1 << SPTX_LOBE_MICROFACET_REFL),  // plastic, metal
+    kAllLobes};
+constexpr int kVariantTerms[kNumShadeVariants] = {1, 1, 2, kMaxTerms};
+
+// Which variant K3 runs for each shading class (-1: no primitive of the scene is in the class).
+struct ShadePlan {
+    int variant[kShadeClasses];
+};
+// First variant whose lobe set covers `lobeMask` and whose term list holds `nonSpecular` terms.
+inline int shade_variant_for(int lobeMask, int nonSpecular) {
+    for (int v = 0; v < kNumShadeVariants; ++v)
+        if ((lobeMask & ~kVariantLobes[v]) == 0 && nonSpecular <= kVariantTerms[v]) return v;
+    return kNumShadeVariants - 1;
+}
 
 struct RenderParams {
     int nPix;          // pixels in the render region

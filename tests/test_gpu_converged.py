@@ -12,13 +12,14 @@ pytestmark = pytest.mark.gpu
 TOLERANCE = 0.005   # north_star: "< 0.5 % at 4096 spp"
 
 
+@pytest.mark.parametrize("mode", ["fast", "exact"])
 @pytest.mark.parametrize("name", ["converged_cornell", "converged_lens"])
-def test_converged_radiance_matches_the_reference_render(capi, name):
+def test_converged_radiance_matches_the_reference_render(capi, name, mode):
     g = golden(name)
     w, h = [int(v) for v in g["res"]]
     spp = int(g["spp"])
     assert spp == 4096
-    ctx = capi.Context(0)
+    ctx = capi.Context(0, exact=(mode == "exact"))   # both builds of K3 (csrc/shade.cu)
     sf = capi.SceneFile(blob_path(name))
     ctx.upload(sf)
     sf.close()
