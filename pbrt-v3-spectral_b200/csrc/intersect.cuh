@@ -190,60 +190,133 @@ struct SphereHit {
     Ray oray;    // object-space ray
 };
 
+// A value with a bound on how far the reference's EFloat interval reaches from it:
+// lo >= v - r and hi <= v + r for the interval [lo, hi] core/efloat.h computes for the same
+// expression.  The bound is propagated with plain float operations (no directed rounding): every
+// EFloat operation widens its exact interval result by at most one rounding (half an ulp of the
+// endpoint) plus one NextFloatUp / NextFloatDown step (one ulp), i.e. by less than 3 * 2^-24 of the
+// endpoint's magnitude; kRbU = 2^-21 covers that five times over and also absorbs the roundings of
+// the bound's own arithmetic.  Used to decide Sphere::Intersect's four interval comparisons from
+// the value parts; the EFloat arithmetic itself runs only when a value lies within its bound of
+// the threshold (a ray that starts on the sphere, a hit exactly at tMax).
+struct RB {
+    float v, r;
+};
+constexpr float kRbU = 0x1p-21f;
+SPTX_DEV RB rb_make(float v, float err) { return RB{v, err + kRbU * (fabsf(v) + err)}; }
+SPTX_DEV RB rb_add(RB a, RB b, float v) {
+    const float w = a.r + b.r;
+    return RB{v, w + kRbU * (fabsf(a.v) + fabsf(b.v) + w)};
+}
+SPTX_DEV RB rb_mul(RB a, RB b, float v) {
+    const float aa = fabsf(a.v), ab = fabsf(b.v);
+    return RB{v, aa * b.r + ab * a.r + a.r * b.r + kRbU * ((aa + a.r) * (ab + b.r))};
+}
+SPTX_DEV RB rb_div(RB a, RB b, float v) {
+    const float den = fabsf(b.v) - b.r;
+    // the divisor's interval may come close to zero (or contain it): no usable bound
+    if (!(den > .5f * fabsf(b.v))) return RB{v, kInf};
+    const float q = fabsf(v);
+    const float w = (a.r + q * b.r) / den;
+    return RB{v, w + kRbU * (q + w)};
+}
+
 // Sphere::Intersect / IntersectP up to the clipping tests,
 // shapes/sphere.cpp:49-107 (== :158-215).
 SPTX_NOINL bool sphere_test(const sptx_sphere &sp, const Ray &wr, SphereHit *h) {
     V3 oErr, dErr;
     Ray ray = xf_ray_err(sp.w2o, wr, &oErr, &dErr);
-    {
-        // Early out on the value parts alone: Quadratic(EFloat...) decides "no real
-        // root" from the float values of a, b, c in double (core/efloat.h:266-270);
-        // the error bounds play no part in that decision.
-        const V3 o = ray.o, d = ray.d;
-        const float av = d.x * d.x + d.y * d.y + d.z * d.z;
-        const float bv = 2.f * (d.x * o.x + d.y * o.y + d.z * o.z);
-        const float cv = o.x * o.x + o.y * o.y + o.z * o.z - sp.radius * sp.radius;
-        const double discrim = (double)bv * (double)bv - 4. * (double)av * (double)cv;
-        if (discrim < 0.) return false;
-        // The roots' value parts, with the float operations of Quadratic(EFloat...): an interval
-        // contains its value (lo <= v <= hi), so "t0.hi > tMax" holds whenever t0.v > tMax and
-        // "t1.lo <= 0" whenever t1.v <= 0 -- those rays are rejected before any interval work
-        // (every shadow ray aimed at a sphere light ends just short of it: t0.v > tMax).
-        const float rd = (float)sqrt(discrim);
-        const float q = (bv < 0) ? -.5f * (bv - rd) : -.5f * (bv + rd);
-        float t0v = q / av, t1v = cv / q;
-        if (t0v > t1v) {
-            const float t = t0v;
-            t0v = t1v;
-            t1v = t;
-        }
-        if (t0v > ray.tMax || t1v <= 0) return false;
+    // The value parts of a, b, c and of the roots, with the float operations of the EFloat
+    // operators and of Quadratic(EFloat...) (core/efloat.h:266-286).
+    const V3 o = ray.o, d = ray.d;
+    const float dxx = d.x * d.x, dyy = d.y * d.y, dzz = d.z * d.z;
+    const float av = dxx + dyy + dzz;
+    const float dox = d.x * o.x, doy = d.y * o.y, doz = d.z * o.z;
+    const float bh = dox + doy + doz;
+    const float bv = 2.f * bh;
+    const float oxx = o.x * o.x, oyy = o.y * o.y, ozz = o.z * o.z;
+    const float oo = oxx + oyy + ozz, rr = sp.radius * sp.radius;
+    const float cv = oo - rr;
+    // Quadratic decides "no real root" from the value parts alone, in double.
+    const double discrim = (double)bv * (double)bv - 4. * (double)av * (double)cv;
+    if (discrim < 0.) return false;
+    const double rootDiscrim = sqrt(discrim);
+    const float rd = (float)rootDiscrim;
+    const float qs = (bv < 0) ? bv - rd : bv + rd;
+    const float q = -.5f * qs;
+    float t0v = q / av, t1v = cv / q;
+    const bool swapped = t0v > t1v;
+    if (swapped) {
+        const float t = t0v;
+        t0v = t1v;
+        t1v = t;
     }
-    EF ox = ef(ray.o.x, oErr.x), oy = ef(ray.o.y, oErr.y), oz = ef(ray.o.z, oErr.z);
-    EF dx = ef(ray.d.x, dErr.x), dy = ef(ray.d.y, dErr.y), dz = ef(ray.d.z, dErr.z);
-    EF a = dx * dx + dy * dy + dz * dz;
-    EF b = ef(2.f) * (dx * ox + dy * oy + dz * oz);
-    EF c = ox * ox + oy * oy + oz * oz - ef(sp.radius) * ef(sp.radius);
-    EF t0, t1;
-    if (!ef_quadratic(a, b, c, &t0, &t1)) return false;
-    if (t0.hi > ray.tMax || t1.lo <= 0) return false;
-    EF ts = t0;
-    if (ts.lo <= 0) {
-        ts = t1;
-        if (ts.hi > ray.tMax) return false;
+    // An interval contains its value (lo <= v <= hi): "t0.hi > tMax" holds whenever t0.v > tMax and
+    // "t1.lo <= 0" whenever t1.v <= 0 (every shadow ray aimed at a sphere light ends just short of
+    // it: t0.v > tMax).
+    if (t0v > ray.tMax || t1v <= 0) return false;
+    // The comparisons left: t0.hi > tMax, t1.lo <= 0, t0.lo <= 0, t1.hi > tMax.
+    bool useT1, t1Over;
+    bool decided = false;
+    {
+        const RB ox = rb_make(o.x, oErr.x), oy = rb_make(o.y, oErr.y), oz = rb_make(o.z, oErr.z);
+        const RB dx = rb_make(d.x, dErr.x), dy = rb_make(d.y, dErr.y), dz = rb_make(d.z, dErr.z);
+        const RB a = rb_add(rb_add(rb_mul(dx, dx, dxx), rb_mul(dy, dy, dyy), dxx + dyy), rb_mul(dz, dz, dzz), av);
+        const RB bs = rb_add(rb_add(rb_mul(dx, ox, dox), rb_mul(dy, oy, doy), dox + doy), rb_mul(dz, oz, doz), bh);
+        const RB b = rb_mul(RB{2.f, 0.f}, bs, bv);
+        const RB cs = rb_add(rb_add(rb_mul(ox, ox, oxx), rb_mul(oy, oy, oyy), oxx + oyy), rb_mul(oz, oz, ozz), oo);
+        const RB c = rb_add(cs, rb_mul(RB{sp.radius, 0.f}, RB{sp.radius, 0.f}, rr), cv);
+        const RB frd = rb_make(rd, (float)((double)kMachineEpsilon * rootDiscrim));
+        const RB qq = rb_mul(RB{-.5f, 0.f}, rb_add(b, frd, qs), q);
+        RB ta = rb_div(qq, a, q / av), tb = rb_div(c, qq, cv / q);
+        if (swapped) {
+            const RB t = ta;
+            ta = tb;
+            tb = t;
+        }
+        // slack for the bound's own roundings and for results in the denormal range
+        const float r0 = ta.r * 1.01f + 1e-30f, r1 = tb.r * 1.01f + 1e-30f;
+        const bool d1 = t0v + r0 <= ray.tMax;        // then t0.hi <= tMax for certain
+        const bool d2 = t1v - r1 > 0.f;              // then t1.lo > 0 for certain
+        const bool d3 = t0v <= 0.f || t0v - r0 > 0.f;  // t0.lo <= 0 known either way
+        const bool d4 = t1v > ray.tMax || t1v + r1 <= ray.tMax;
+        if (d1 && d2 && d3 && d4) {
+            decided = true;
+            useT1 = t0v <= 0.f;
+            t1Over = t1v > ray.tMax;
+        }
+    }
+    if (!decided) {
+        EF ox = ef(ray.o.x, oErr.x), oy = ef(ray.o.y, oErr.y), oz = ef(ray.o.z, oErr.z);
+        EF dx = ef(ray.d.x, dErr.x), dy = ef(ray.d.y, dErr.y), dz = ef(ray.d.z, dErr.z);
+        EF a = dx * dx + dy * dy + dz * dz;
+        EF b = ef(2.f) * (dx * ox + dy * oy + dz * oz);
+        EF c = ox * ox + oy * oy + oz * oz - ef(sp.radius) * ef(sp.radius);
+        EF t0, t1;
+        if (!ef_quadratic(a, b, c, &t0, &t1)) return false;
+        if (t0.hi > ray.tMax || t1.lo <= 0) return false;
+        useT1 = t0.lo <= 0;
+        t1Over = t1.hi > ray.tMax;
+        t0v = t0.v;
+        t1v = t1.v;
+    }
+    float tsv = t0v;
+    if (useT1) {
+        if (t1Over) return false;
+        tsv = t1v;
     }
     const float radius = sp.radius;
-    V3 pHit = ray.o + ray.d * ts.v;
+    V3 pHit = ray.o + ray.d * tsv;
     pHit = pHit * (radius / length(pHit));
     if (pHit.x == 0 && pHit.y == 0) pHit.x = 1e-5f * radius;
     float phi = atan2f(pHit.y, pHit.x);
     if (phi < 0) phi += 2 * kPi;
     if ((sp.z_min > -radius && pHit.z < sp.z_min) || (sp.z_max < radius && pHit.z > sp.z_max) ||
         phi > sp.phi_max) {
-        if (ts.v == t1.v) return false;
-        if (t1.hi > ray.tMax) return false;
-        ts = t1;
-        pHit = ray.o + ray.d * ts.v;
+        if (tsv == t1v) return false;
+        if (t1Over) return false;
+        tsv = t1v;
+        pHit = ray.o + ray.d * tsv;
         pHit = pHit * (radius / length(pHit));
         if (pHit.x == 0 && pHit.y == 0) pHit.x = 1e-5f * radius;
         phi = atan2f(pHit.y, pHit.x);
@@ -254,7 +327,7 @@ SPTX_NOINL bool sphere_test(const sptx_sphere &sp, const Ray &wr, SphereHit *h) 
     }
     h->pHit = pHit;
     h->phi = phi;
-    h->tHit = ts.v;
+    h->tHit = tsv;
     h->oray = ray;
     return true;
 }
