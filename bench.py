@@ -37,7 +37,7 @@ GEN = os.path.join(ROOT, "scenes", "_gen")
 RES_W = RES_H = 1024   # --workload c2 (default); c5 = 3840 x 2160, 4096 spp (set_workload)
 SPP_TOTAL = 1024
 SPP_STEP = 64
-REF_SPP_STEP = 2       # reference arm: sample numbers per step (bounded sample)
+REF_SPP_STEP = 8       # reference arm: sample numbers per step (bounded sample; a step is seconds)
 CPU_BASELINE_SPP = 8   # cpu_baseline leg of our arm
 METRIC = "spectral_msamples_per_s"
 UNIT = "Msamples/s"
@@ -189,9 +189,8 @@ def bench_ours(args):
     torch.cuda.synchronize()
     if dist:
         dist.barrier()
-    clocks = ClockSampler(local)
-    if rank == 0:
-        clocks.start()
+    clocks = ClockSampler(local)   # every rank samples its own GPU
+    clocks.start()
     t0 = time.perf_counter()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     for k in range(K):
@@ -199,6 +198,7 @@ def bench_ours(args):
     c = ctx.counters()
     dev_ms = c["render_ms"]
     reduce_ms = 0.0
+    reduce_wall_ms = 0.0
     if dist:
         # the one exchange step of the path: per-rank films -> rank 0, summed in rank order by one
         # kernel reading the peers over NVLink (sptx_film_merge_peers); NCCL reduce if asked for
@@ -217,7 +217,11 @@ def bench_ours(args):
         dev_ms += reduce_ms
     torch.cuda.synchronize()
     wall_ms = (time.perf_counter() - t0) * 1e3
-    clk = clocks.stop() if rank == 0 else None
+    clk = clocks.stop()
+    clk_all = [clk]
+    if dist:
+        clk_all = [None] * world
+        dist.all_gather_object(clk_all, clk)
     if dist:
         t = torch.tensor([dev_ms, wall_ms], device=f"cuda:{local}", dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -244,16 +248,29 @@ def bench_ours(args):
     if dist:
         dist.barrier()
     t0 = time.perf_counter()
-    e2e_parts = [0.0, 0.0, 0.0]
+    e2e_parts = [0.0, 0.0, 0.0, 0.0]
     for k in range(e2e_steps):
         ta = time.perf_counter()
         ctx.upload(sf)                      # host arrays -> HBM (also a fresh, cleared film)
         tb = time.perf_counter()
         ctx.render(*step_range(k))
         tc = time.perf_counter()
-        contrib, weight = ctx.film_download(w, h, out=host_film)  # device film -> host
+        if dist:
+            # the product of a multi-GPU step is the MERGED film on the host: handle exchange,
+            # barriers, the peer-memory merge kernel on rank 0 -- all inside the timed region
+            if os.environ.get("SPTX_BENCH_NCCL_REDUCE"):
+                part.reduce_film(film, dist, dst=0)
+                torch.cuda.synchronize()
+            else:
+                part.merge_films_over_peers(ctx, dist, dst=0)
+        tm = time.perf_counter()
+        if rank == 0:
+            contrib, weight = ctx.film_download(w, h, out=host_film)  # device film -> host
         td = time.perf_counter()
-        e2e_parts = [e2e_parts[0] + tb - ta, e2e_parts[1] + tc - tb, e2e_parts[2] + td - tc]
+        e2e_parts = [e2e_parts[0] + tb - ta, e2e_parts[1] + tc - tb, e2e_parts[2] + tm - tc,
+                     e2e_parts[3] + td - tm]
+    if dist:
+        dist.barrier()
     e2e_s = time.perf_counter() - t0
     if dist:
         t = torch.tensor([e2e_s], device=f"cuda:{local}", dtype=torch.float64)
@@ -285,20 +302,45 @@ def bench_ours(args):
         algo = {"intersect": bytes_int, "resolve": bytes_res, "shade": bytes_shade}
         peak, peak_src = peaks()
         name = names[dom]
-        per_launch_ms = kms[dom] / max(kcnt[dom], 1)
+        # per kernel: algorithmic bytes of one launch / its average launch time (CUDA events on the
+        # render stream).  K3's "launch" is one bounce = its per-class launches together.
+        rooflines = {}
+        for kn in ("intersect", "shade", "resolve"):
+            i = names.index(kn)
+            ms1 = kms[i] / max(kcnt[i], 1)
+            b1 = algo[kn] / steps_counted / max(launches_per_step[kn], 1)
+            ach = b1 / (ms1 * 1e-3) * 1e-9
+            rooflines[kn] = {"bound": "hbm", "kernel": "k_" + kn, "achieved": ach, "peak": peak, "unit": "GB/s",
+                             "frac": ach / peak, "algorithmic_bytes_per_launch": b1, "avg_launch_ms": ms1}
+        # the traversal working set of this scene (100 KB of nodes and leaf blocks) is L2 / L1
+        # resident: only 48 B per ray (ray in, hit out) are HBM traffic -- say so beside the number
+        for kn, nrays in (("intersect", rays_int), ("resolve", rays_res)):
+            rooflines[kn]["note"] = ("node / primitive bytes are cache hits for this scene; HBM carries the "
+                                     "rays and hit records only")
+            rooflines[kn]["hbm_bytes_per_launch_rays_and_hits"] = 48.0 * nrays / steps_counted / max(
+                launches_per_step[kn], 1)
         roof = None
-        if name in algo:
-            per_launch_bytes = algo[name] / steps_counted / max(launches_per_step[name], 1)
-            achieved = per_launch_bytes / (per_launch_ms * 1e-3) * 1e-9
-            traffic = None
+        if name in rooflines:
+            roof = dict(rooflines[name])
+            traffic, traffic_src = None, None
             tpath = os.path.join(ROOT, "profiles", f"k_{name}_traffic.json")
-            if os.path.exists(tpath):   # dram bytes per launch from the committed ncu --set full capture
-                traffic = json.load(open(tpath)).get("dram_bytes_per_launch")
-            roof = {"bound": "hbm", "kernel": "k_" + name, "achieved": achieved, "peak": peak, "unit": "GB/s",
-                    "frac": achieved / peak, "traffic": traffic, "algorithmic_bytes_per_launch": per_launch_bytes,
-                    "peak_source": peak_src,
-                    "avg_launch_ms": per_launch_ms,
-                    "note": "algorithmic bytes per SURVEY.md 8(d); traversal working set is L2-resident for this scene"}
+            if os.path.exists(tpath):   # dram bytes per launch from a committed ncu --set full capture
+                tj = json.load(open(tpath))
+                traffic = tj.get("dram_bytes_per_launch")
+                traffic_src = "static capture, not measured by this run: " + tj.get("source", tpath)
+            roof.update({"traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
+                         "note": "algorithmic bytes per SURVEY.md 8(d); K3 launch = one bounce (all shading classes)"})
+        # SURVEY 8(d) whole-sample roofline: B_sample = sum of B_ray + n_vertices * B_vertex + B_film
+        samples_step = float(RES_W * RES_H * SPP_STEP)
+        b_sample = (bytes_int + bytes_res + bytes_shade) / steps_counted / samples_step + 256.0
+        ach_sample = b_sample * samples_step / (dev_ms / K * 1e-3) * 1e-9
+        roofline_sample = {"bound": "hbm", "bytes_per_sample": b_sample, "achieved": ach_sample, "peak": peak,
+                           "unit": "GB/s", "frac": ach_sample / peak,
+                           "msamples_per_s_at_peak": peak * 1e9 / b_sample * 1e-6,
+                           "rays_per_sample": (rays_int + rays_res) / steps_counted / samples_step,
+                           "vertices_per_sample": cc["path_vertices"] / steps_counted / samples_step,
+                           "note": "SURVEY.md 8(d): traversal bytes from the counted visit counts of this run, "
+                                   "996 B per path vertex, 256 B of film per sample"}
         kernels = {names[i]: {"ms_per_step": kms[i] / K, "launches_per_step": kcnt[i] / K,
                               "share": kms[i] / max(sum(kms[:6]), 1e-9)} for i in range(6)}
         # ---- CPU baseline: the reference renderer on this box's host cores, bounded sample ----
@@ -322,10 +364,13 @@ def bench_ours(args):
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "steps": e2e_steps,
                     "ms_per_step": {n: 1e3 * v / e2e_steps
-                                    for n, v in zip(("upload", "render", "film_download"), e2e_parts)}},
+                                    for n, v in zip(("upload", "render", "film_merge", "film_download"), e2e_parts)},
+                    "product": "merged film on rank 0's host" if world > 1 else "film on the host"},
             "gpu_launches": int(c["kernel_launches"]),
-            "clocks": clk, "roofline": roof, "cpu_baseline": cpu, "kernels": kernels,
+            "clocks": clk, "clocks_per_rank": clk_all if world > 1 else None, "roofline": roof, "rooflines": rooflines, "roofline_sample": roofline_sample,
+            "cpu_baseline": cpu, "kernels": kernels, "configs": other_configs(args) if world == 1 else None,
             "wall_ms_per_step": wall_ms / K, "film_reduce_ms": reduce_ms,
+            "film_reduce_wall_ms": reduce_wall_ms if world > 1 else None,
             "film_reduce": ("nccl reduce" if os.environ.get("SPTX_BENCH_NCCL_REDUCE") else
                             "one kernel over NVLink peer memory (sptx_film_merge_peers)") if world > 1 else None,
             "rays_per_sample": (c["closest_hit_rays"] + c["shadow_rays"]) / max(c["camera_rays"], 1),
@@ -338,6 +383,29 @@ def bench_ours(args):
         dist.destroy_process_group()
     if line:
         emit(json.dumps(line))
+
+
+def other_configs(args):
+    """The other single-GPU configurations of BASELINE.json, measured by this run (bounded sizes):
+    C1 killeroo 400x400x64 and C3 RealisticCamera 2048x2048 (16 of its 256 spp) in Msamples/s, C4
+    (2.0e7 instanced triangles) in Mrays/s for 2^22-ray batches with the reference's BVHAccel loop
+    on the host cores beside it.  Skipped with --no-configs; a missing blob is reported, not fatal."""
+    if args.no_configs:
+        return None
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    out = {}
+    try:
+        bc = importlib.import_module("bench_configs")
+        out["l2_read_gbs_measured"] = bc.l2_peak()
+        for key, fn in (("c1", lambda: bc.c1()), ("c3", lambda: bc.c3(spp=16, cpu=False)),
+                        ("c4", lambda: bc.c4(n=1 << 22, n_cpu=1 << 18))):
+            try:
+                out[key] = fn()
+            except Exception as exc:   # a configuration is reported, never a gate for the bench line
+                out[key] = {"unavailable": str(exc)[:300]}
+    except Exception as exc:
+        out["unavailable"] = str(exc)[:300]
+    return out
 
 
 def bench_reference(args):
@@ -376,6 +444,7 @@ def main():
     ap.add_argument("--steps", type=int, default=SPP_TOTAL // SPP_STEP)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-configs", action="store_true", help="skip the C1 / C3 / C4 legs of the line")
     ap.add_argument("--workload", default="c2", choices=["c2", "c5"],
                     help="c2: 1024x1024 at 1024 spp (default, the metric's configuration); "
                          "c5: 3840x2160 at 4096 spp, for --gpus 2/4/8")

@@ -29,6 +29,7 @@
 #include <mutex>
 #include <sstream>
 #include <string>
+#include <thread>
 #include <vector>
 #include <glog/logging.h>
 
@@ -95,15 +96,62 @@ void GpuPathIntegrator::Render(const Scene &scene) {
         if (std::getenv("SPTX_DUMP_ONLY")) return;
     }
 
-    int device = 0;
-    if (const char *d = std::getenv("SPTX_DEVICE")) device = std::atoi(d);
-    sptx_ctx *ctx = nullptr;
-    if (sptx_create(device, &ctx) != 0) Die(nullptr, "sptx_create");
-    if (sptx_upload_scene(ctx, &flat.desc) != 0) Die(ctx, "sptx_upload_scene");
-    if (sptx_film_clear(ctx) != 0) Die(ctx, "sptx_film_clear");
+    // One context per GPU.  SPTX_DEVICES=0,1,... (or SPTX_DEVICE=n for one) names them; every
+    // context gets the whole scene and a contiguous block of the sample numbers of every pixel
+    // (HaltonSampler::GetIndexForSample is a pure function of the sample number), each driven
+    // by its own host thread -- the analogue of ParallelFor2D over tiles
+    // (src/core/integrator.cpp:235-241) -- and the per-GPU films are summed into the first one
+    // through peer access (Film::MergeFilmTile, src/core/film.cpp:124-142).
+    std::vector<int> devices;
+    if (const char *ds = std::getenv("SPTX_DEVICES")) {
+        for (const char *p = ds; *p;) {
+            char *end = nullptr;
+            long v = std::strtol(p, &end, 10);
+            if (end == p) break;
+            devices.push_back((int)v);
+            p = (*end == ',') ? end + 1 : end;
+        }
+    }
+    if (devices.empty()) {
+        int device = 0;
+        if (const char *d = std::getenv("SPTX_DEVICE")) device = std::atoi(d);
+        devices.push_back(device);
+    }
+    const int spp = (int)sampler->samplesPerPixel;
+    if ((int)devices.size() > 8 || (int)devices.size() > std::max(spp, 1)) {
+        Error("GpuPathIntegrator: SPTX_DEVICES names %d contexts (at most 8, and at most one per sample)",
+              (int)devices.size());
+        ExitNow();
+    }
+    const int nCtx = (int)devices.size();
+    if (nCtx > 1 && flat.desc.sampler.type == SPTX_SAMPLER_RANDOM) {
+        Error("GpuPathIntegrator: the RandomSampler's tile streams cannot be cut by sample number; "
+              "use one device");
+        ExitNow();
+    }
+    std::vector<sptx_ctx *> ctxs((size_t)nCtx, nullptr);
+    for (int k = 0; k < nCtx; ++k) {
+        if (sptx_create(devices[k], &ctxs[k]) != 0) Die(nullptr, "sptx_create");
+        if (sptx_upload_scene(ctxs[k], &flat.desc) != 0) Die(ctxs[k], "sptx_upload_scene");
+        if (sptx_film_clear(ctxs[k]) != 0) Die(ctxs[k], "sptx_film_clear");
+    }
+    sptx_ctx *ctx = ctxs[0];
     auto t0 = std::chrono::steady_clock::now();
-    if (sptx_render(ctx, nullptr, 0, (int)sampler->samplesPerPixel) != 0)
-        Die(ctx, "sptx_render");
+    {
+        std::vector<std::thread> workers;
+        std::vector<int> rcs((size_t)nCtx, 0);
+        const int base = spp / nCtx, extra = spp % nCtx;
+        int s0 = 0;
+        for (int k = 0; k < nCtx; ++k) {
+            const int s1 = s0 + base + (k < extra ? 1 : 0);
+            workers.emplace_back([&, k, s0, s1] { rcs[k] = sptx_render(ctxs[k], nullptr, s0, s1); });
+            s0 = s1;
+        }
+        for (auto &w : workers) w.join();
+        for (int k = 0; k < nCtx; ++k)
+            if (rcs[k] != 0) Die(ctxs[k], "sptx_render");
+    }
+    if (nCtx > 1 && sptx_film_merge_contexts(ctxs.data(), nCtx, 0) != 0) Die(ctx, "sptx_film_merge_contexts");
     auto t1 = std::chrono::steady_clock::now();
 
     // Film pixels back into the reference's Film, then its own writer.
@@ -128,18 +176,26 @@ void GpuPathIntegrator::Render(const Scene &scene) {
     }
     sptx_counters c;
     std::memset(&c, 0, sizeof(c));
-    sptx_get_counters(ctx, &c);
+    for (int k = 0; k < nCtx; ++k) {   // rays summed over the contexts, device time = the slowest
+        sptx_counters ck;
+        std::memset(&ck, 0, sizeof(ck));
+        sptx_get_counters(ctxs[k], &ck);
+        c.camera_rays += ck.camera_rays;
+        c.closest_hit_rays += ck.closest_hit_rays;
+        c.shadow_rays += ck.shadow_rays;
+        c.render_ms = std::max(c.render_ms, ck.render_ms);
+    }
     double wall = std::chrono::duration<double>(t1 - t0).count();
     double nSamples = (double)c.camera_rays;
     fprintf(stderr,
-            "GpuPathIntegrator: %.0f camera samples, %.3f s device "
+            "GpuPathIntegrator: %d GPU context(s), %.0f camera samples, %.3f s device "
             "(%.2f Msamples/s), %.3f s wall; rays: %llu closest-hit, %llu "
             "shadow\n",
-            nSamples, c.render_ms * 1e-3,
+            nCtx, nSamples, c.render_ms * 1e-3,
             c.render_ms > 0 ? nSamples / (c.render_ms * 1e3) : 0.0, wall,
             (unsigned long long)c.closest_hit_rays,
             (unsigned long long)c.shadow_rays);
-    sptx_destroy(ctx);
+    for (sptx_ctx *k : ctxs) sptx_destroy(k);
     film->WriteImage();
 }
 

@@ -347,6 +347,11 @@ int sptx_intersect_batch_device(sptx_ctx *ctx, const void *d_rays, int64_t n,
 int sptx_intersect_batch_noalloc(sptx_ctx *ctx, const sptx_ray *rays, int64_t n,
                                  sptx_hit *hits, int any_hit);
 
+/* Measurement hook (no counterpart in the reference): read bandwidth of an L2-resident buffer of
+ * `bytes`, swept `reps` times, in GB/s -- the roofline denominator of traversal when the BVH
+ * working set lives in L2 (bench.py, tools/bench_configs.py). */
+int sptx_measure_l2(sptx_ctx *ctx, int64_t bytes, int reps, double *gbs);
+
 /* SamplerIntegrator::Render's pixel/sample loop (src/core/integrator.cpp:
  * 228-334) for sample numbers [sample_begin, sample_end) of every pixel of
  * `pixel_bounds` (NULL = the film's sample bounds), accumulated into the
@@ -378,6 +383,22 @@ int sptx_film_device_ptr(sptx_ctx *ctx, void **d_film, int64_t *n_floats);
 int sptx_film_export(sptx_ctx *ctx, void *handle);
 int sptx_film_merge_peers(sptx_ctx *ctx, const void *handles, int n_ranks, int self,
                           double *planes);
+/* The same merge shaped as a reduce-scatter: EVERY rank calls it (between two barriers of the
+ * caller) and sums its own 1/n_ranks slice of the film over all ranks, in rank order (same result
+ * bit for bit), writing the sums into rank `dst`'s film over NVLink.  Each link carries 1/n_ranks of
+ * a film per peer instead of rank dst pulling n_ranks - 1 whole films through its own ingress.
+ * Mapped peer films stay open in the context between calls. */
+int sptx_film_reduce_scatter(sptx_ctx *ctx, const void *handles, int n_ranks, int self, int dst);
+/* One process driving one context per GPU (GpuPathIntegrator::Render with SPTX_DEVICES; SURVEY
+ * 8(b) "threading"): the films of ctxs[0..n) are summed in that order into ctxs[dst]'s film, each
+ * device summing its own slice through peer access (no IPC handles, no NCCL).  Replaces
+ * Film::MergeFilmTile (src/core/film.cpp:124-142) across the render threads' films. */
+int sptx_film_merge_contexts(sptx_ctx *const *ctxs, int n, int dst);
+/* SURVEY 8(b)'s NCCL form of the exchange step, for hosts that already hold a communicator:
+ * ncclReduce(sum, float32, W*H*32 floats) of the device film onto `root`, on the context's
+ * stream; `nccl_comm` is an ncclComm_t.  libnccl.so.2 is looked up at run time (no link-time
+ * dependency).  A single thread driving several devices wraps its calls in ncclGroupStart / End. */
+int sptx_film_reduce(sptx_ctx *ctx, void *nccl_comm, int root);
 /* Film pixels to host: contrib [H][W][31] float32, weight [H][W] float32. */
 int sptx_film_download(sptx_ctx *ctx, float *contrib, float *weight);
 /* Film::WriteImage's spectral branch (src/core/film.cpp:226-306) up to the

@@ -21,9 +21,10 @@ STRIDE = 32
 SYMBOLS = [
     "sptx_abi_version", "sptx_create", "sptx_destroy", "sptx_last_error",
     "sptx_upload_scene", "sptx_intersect_batch", "sptx_intersect_batch_device",
-    "sptx_intersect_batch_noalloc",
+    "sptx_intersect_batch_noalloc", "sptx_measure_l2",
     "sptx_render", "sptx_render_tiles", "sptx_film_clear", "sptx_film_device_ptr",
-    "sptx_film_export", "sptx_film_merge_peers",
+    "sptx_film_export", "sptx_film_merge_peers", "sptx_film_reduce_scatter", "sptx_film_merge_contexts",
+    "sptx_film_reduce",
     "sptx_film_download", "sptx_film_pack_dat", "sptx_write_dat",
     "sptx_get_counters", "sptx_reset_counters", "sptx_set_wavefront_size", "sptx_set_option",
     "sptx_sampler_eval", "sptx_camera_rays", "sptx_debug_radiance",
@@ -82,6 +83,7 @@ def lib():
     L.sptx_intersect_batch.argtypes = [vp, vp, i64, vp, i32, i32]
     L.sptx_intersect_batch_device.argtypes = [vp, vp, i64, vp, i32, i32, f32p]
     L.sptx_intersect_batch_noalloc.argtypes = [vp, vp, i64, vp, i32]
+    L.sptx_measure_l2.argtypes = [vp, i64, i32, C.POINTER(C.c_double)]
     L.sptx_render.argtypes = [vp, i32p, i32, i32]
     L.sptx_render_tiles.argtypes = [vp, i32, i32, i32, i32]
     L.sptx_film_clear.argtypes = [vp]
@@ -90,6 +92,9 @@ def lib():
     L.sptx_film_pack_dat.argtypes = [vp, vp]
     L.sptx_film_export.argtypes = [vp, vp]
     L.sptx_film_merge_peers.argtypes = [vp, vp, i32, i32, vp]
+    L.sptx_film_reduce_scatter.argtypes = [vp, vp, i32, i32, i32]
+    L.sptx_film_merge_contexts.argtypes = [C.POINTER(vp), i32, i32]
+    L.sptx_film_reduce.argtypes = [vp, vp, i32]
     L.sptx_write_dat.argtypes = [C.c_char_p, i32, i32, vp]
     L.sptx_get_counters.argtypes = [vp, C.POINTER(Counters)]
     L.sptx_reset_counters.argtypes = [vp]
@@ -214,6 +219,12 @@ class Context:
                                                     int(any_hit)), "sptx_intersect_batch_noalloc")
         return hits
 
+    def measure_l2(self, nbytes=32 << 20, reps=200):
+        """GB/s of 128-bit reads from an L2-resident buffer (sptx_measure_l2)."""
+        gbs = C.c_double()
+        self._ck(lib().sptx_measure_l2(self.h, int(nbytes), int(reps), C.byref(gbs)), "sptx_measure_l2")
+        return gbs.value
+
     def intersect_device(self, d_rays, n, d_hits, any_hit=False, counters=False):
         ms = C.c_float()
         self._ck(lib().sptx_intersect_batch_device(self.h, d_rays, int(n), d_hits, int(any_hit),
@@ -252,6 +263,17 @@ class Context:
         buf = C.create_string_buffer(IPC_HANDLE_BYTES)
         self._ck(lib().sptx_film_export(self.h, buf), "sptx_film_export")
         return buf.raw
+
+    def film_reduce_scatter(self, handles, rank, dst=0):
+        """This rank's slice of the multi-GPU film sum, written into rank dst's film
+        (sptx_film_reduce_scatter); every rank calls it between two barriers."""
+        buf = b"".join(bytes(h) for h in handles)
+        self._ck(lib().sptx_film_reduce_scatter(self.h, buf, len(handles), int(rank), int(dst)),
+                 "sptx_film_reduce_scatter")
+
+    def film_reduce_nccl(self, comm, root=0):
+        """ncclReduce of the device film onto `root` (sptx_film_reduce); comm = ncclComm_t value."""
+        self._ck(lib().sptx_film_reduce(self.h, C.c_void_p(comm), int(root)), "sptx_film_reduce")
 
     def film_merge_peers(self, handles, self_rank, pack=None):
         """Sums the films of all ranks (rank order) into this rank's film with one kernel reading
@@ -306,6 +328,14 @@ class Context:
         self._ck(lib().sptx_debug_radiance(self.h, _ptr(px), _ptr(py), _ptr(sample), px.shape[0],
                                            _ptr(L), _ptr(pw)), "sptx_debug_radiance")
         return L, pw
+
+
+def merge_contexts(contexts, dst=0):
+    """Films of several contexts of THIS process summed into contexts[dst]'s (sptx_film_merge_contexts)."""
+    arr = (C.c_void_p * len(contexts))(*[c.h for c in contexts])
+    rc = lib().sptx_film_merge_contexts(arr, len(contexts), int(dst))
+    if rc != 0:
+        raise SptxError(f"sptx_film_merge_contexts -> {rc}: {lib().sptx_last_error(contexts[dst].h).decode()}")
 
 
 def write_dat(path, planes):

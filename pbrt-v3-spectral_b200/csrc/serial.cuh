@@ -1,4 +1,4 @@
-// serial.cuh -- the RandomSampler path: one warp lane per 16x16 tile.
+// serial.cuh -- the RandomSampler and ZeroTwoSequenceSampler paths: one warp lane per 16x16 tile.
 //
 // RandomSampler is ONE PCG32 stream per tile (SamplerIntegrator::Render clones
 // the sampler with seed = tile.y * nTiles.x + tile.x, core/integrator.cpp:
@@ -42,6 +42,90 @@ struct Pcg32 {
         p.y = uniform_float();
         return p;
     }
+    SPTX_DEV float get1d() { return uniform_float(); }
+    SPTX_DEV void start_pixel() {}  // RandomSampler::StartPixel draws nothing (no array requests)
+    SPTX_DEV void start_sample(int) {}
+    // RNG::UniformUInt32(b), core/rng.h:86-103
+    SPTX_DEV uint32_t next_bounded(uint32_t b) {
+        const uint32_t threshold = (~b + 1u) % b;
+        while (true) {
+            const uint32_t r = next();
+            if (r >= threshold) return r % b;
+        }
+    }
+};
+
+// ZeroTwoSequenceSampler (samplers/zerotwosequence.cpp:43-70) + PixelSampler (core/sampler.cpp:
+// 107-135): at the start of every pixel the first nDims 1D and nDims 2D dimensions of all of the
+// pixel's samples are generated from the tile's RNG stream -- a scrambled van der Corput / 2D
+// Sobol' (0,2)-sequence in Gray-code order (core/lowdiscrepancy.h:112-139, 153-228), shuffled with
+// RNG::UniformUInt32(b) draws (core/sampling.h:151-157) -- and dimensions past nDims come straight
+// from the RNG.  The tables ([nDims][spp] floats and [nDims][spp] points) live in a per-tile
+// slice of a global scratch buffer.
+struct ZeroTwoSampler {
+    Pcg32 rng;
+    int nDims, spp;
+    float *t1;   // [nDims][spp]
+    float2 *t2;  // [nDims][spp]
+    int cur1, cur2, index;
+    SPTX_DEV void set_sequence(uint64_t seq) { rng.set_sequence(seq); }
+    SPTX_DEV static float to_float(uint32_t v) {
+        const float f = (float)v * 0x1p-32f;
+        return (kOneMinusEpsilon < f) ? kOneMinusEpsilon : f;
+    }
+    // Shuffle(samp, count, nDimensions = 1, rng)
+    template <typename T>
+    SPTX_DEV void shuffle(T *samp, int count) {
+        for (int i = 0; i < count; ++i) {
+            const int other = i + (int)rng.next_bounded((uint32_t)(count - i));
+            const T tmp = samp[i];
+            samp[i] = samp[other];
+            samp[other] = tmp;
+        }
+    }
+    SPTX_DEV void start_pixel() {
+        for (int d = 0; d < nDims; ++d) {  // VanDerCorput(1, spp, ...)
+            float *p = t1 + (size_t)d * spp;
+            uint32_t v = rng.next();  // scramble
+            for (uint32_t i = 0; i < (uint32_t)spp; ++i) {
+                p[i] = to_float(v);
+                v ^= 0x80000000u >> __ffs((int)(i + 1)) - 1;  // CVanDerCorput[CountTrailingZeros(i + 1)]
+            }
+            for (int i = 0; i < spp; ++i) (void)rng.next_bounded(1u);  // Shuffle(samples + i, 1, 1, rng)
+            shuffle(p, spp);
+        }
+        for (int d = 0; d < nDims; ++d) {  // Sobol2D(1, spp, ...)
+            float2 *p = t2 + (size_t)d * spp;
+            uint32_t v0 = rng.next(), v1 = rng.next();
+            for (uint32_t i = 0; i < (uint32_t)spp; ++i) {
+                p[i] = make_float2(to_float(v0), to_float(v1));
+                const int k = __ffs((int)(i + 1)) - 1;
+                v0 ^= 0x80000000u >> k;  // CSobol[0][k]
+                // CSobol[1][k]: column k of the second Sobol' matrix = row k of Pascal's triangle
+                // mod 2, top bit first (core/lowdiscrepancy.h:207-219)
+                uint32_t c1 = 0x80000000u;
+                for (int j = 0; j < k; ++j) c1 ^= c1 >> 1;
+                v1 ^= c1;
+            }
+            for (int i = 0; i < spp; ++i) (void)rng.next_bounded(1u);
+            shuffle(p, spp);
+        }
+    }
+    SPTX_DEV void start_sample(int s) {
+        index = s;
+        cur1 = cur2 = 0;
+    }
+    SPTX_DEV float get1d() {
+        if (cur1 < nDims) return t1[(size_t)(cur1++) * spp + index];
+        return rng.uniform_float();
+    }
+    SPTX_DEV V2 get2d() {
+        if (cur2 < nDims) {
+            const float2 v = t2[(size_t)(cur2++) * spp + index];
+            return V2{v.x, v.y};
+        }
+        return rng.get2d();
+    }
 };
 
 struct SerialParams {
@@ -52,10 +136,13 @@ struct SerialParams {
     int maxDepth;
     float rrThreshold;
     float wavelength;
+    int nDims;      // ZeroTwoSequenceSampler: nSampledDimensions
+    float *tables;  // ZeroTwoSequenceSampler: [nTiles][nDims][spp] floats + [nTiles][nDims][spp] points
 };
 
 // PathIntegrator::Li, integrators/path.cpp:64-188, for one camera ray.
-SPTX_DEV void li_serial(const DScene &S, const SerialParams &P, Pcg32 &rng, Ray ray, float *L,
+template <typename SMP>
+SPTX_DEV void li_serial(const DScene &S, const SerialParams &P, SMP &rng, Ray ray, float *L,
                         unsigned long long *nClosest,
                         unsigned long long *nShadow, unsigned long long *nVert) {
     float beta[SPTX_SPECTRUM_STRIDE];
@@ -88,7 +175,7 @@ SPTX_DEV void li_serial(const DScene &S, const SerialParams &P, Pcg32 &rng, Ray 
         // UniformSampleOneLight, core/integrator.cpp:85-106
         if (bsdf_num_components(S, bs, noSpec) > 0 && S.n_lights > 0) {
             float lightPdfSel;
-            const int lightNum = select_light(S, it.p, rng.uniform_float(), &lightPdfSel);
+            const int lightNum = select_light(S, it.p, rng.get1d(), &lightPdfSel);
             if (lightPdfSel != 0) {
                 const V2 uLight = rng.get2d();
                 const V2 uScattering = rng.get2d();
@@ -203,7 +290,7 @@ SPTX_DEV void li_serial(const DScene &S, const SerialParams &P, Pcg32 &rng, Ray 
         }
         if (maxBeta < P.rrThreshold && bounces > 3) {
             float q = fmaxf(.05f, 1.f - maxBeta);
-            if (rng.uniform_float() < q) break;
+            if (rng.get1d() < q) break;
             const float inv = 1.f - q;
             for (int b = 0; b < SPTX_NBINS; ++b) beta[b] = beta[b] / inv;
         }
@@ -211,6 +298,17 @@ SPTX_DEV void li_serial(const DScene &S, const SerialParams &P, Pcg32 &rng, Ray 
 }
 
 // SamplerIntegrator::Render's tile loop (core/integrator.cpp:245-330) for one tile per warp.
+template <typename SMP>
+SPTX_DEV void sampler_init(SMP &, const SerialParams &, int) {}
+SPTX_DEV void sampler_init(ZeroTwoSampler &s, const SerialParams &P, int tile) {
+    s.nDims = P.nDims;
+    s.spp = P.spp;
+    s.t1 = P.tables + (size_t)tile * P.nDims * P.spp * 3;
+    s.t2 = reinterpret_cast<float2 *>(s.t1 + (size_t)P.nDims * P.spp);
+    s.cur1 = s.cur2 = s.index = 0;
+}
+
+template <typename SMP>
 __global__ void __launch_bounds__(32)
 k_render_serial(const DScene *__restrict__ Sp, DCamera C, DFilm F, SerialParams P, DeviceCounters *cnt,
                 int part, int nParts) {
@@ -219,7 +317,8 @@ k_render_serial(const DScene *__restrict__ Sp, DCamera C, DFilm F, SerialParams 
     const int tile = blockIdx.x;
     if (tile % nParts != part) return;  // tiles are dealt to ranks as sptx_render_tiles does
     const int tx = tile % P.nTilesX, ty = tile / P.nTilesX;
-    Pcg32 rng;
+    SMP rng;
+    sampler_init(rng, P, tile);
     rng.set_sequence((uint64_t)(ty * P.nTilesX + tx));
     const int tileSize = 16;
     const int x0 = P.sb[0] + tx * tileSize, x1 = min(x0 + tileSize, P.sb[2]);
@@ -228,13 +327,16 @@ k_render_serial(const DScene *__restrict__ Sp, DCamera C, DFilm F, SerialParams 
     float L[SPTX_SPECTRUM_STRIDE];
     for (int y = y0; y < y1; ++y)
         for (int x = x0; x < x1; ++x) {
-            // (RandomSampler::StartPixel draws nothing: the path integrator requests no arrays)
+            // tileSampler->StartPixel(pixel) comes before the pixel-bounds test (core/integrator.cpp:
+            // 262-271): a ZeroTwoSequenceSampler draws its tables for skipped pixels too
+            rng.start_pixel();
             if (!(x >= P.pb[0] && x < P.pb[2] && y >= P.pb[1] && y < P.pb[3])) continue;
             for (int s = 0; s < P.spp; ++s) {
+                rng.start_sample(s);
                 // Sampler::GetCameraSample, core/sampler.cpp:46-52
                 const V2 u = rng.get2d();
                 const V2 pFilm{(float)x + u.x, (float)y + u.y};
-                (void)rng.uniform_float();  // time
+                (void)rng.get1d();  // time
                 const V2 pLens = rng.get2d();
                 Ray ray{mk(0, 0, 0), mk(0, 0, 1), kInf};
                 const float w = camera_ray(C, pFilm, pLens, P.wavelength, &ray);

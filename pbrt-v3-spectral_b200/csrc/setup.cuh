@@ -166,6 +166,32 @@ k_film_merge_pack(PeerFilms P, float *own, int64_t nPix, float scale, double *pl
     }
 }
 
+// The same sum shaped as a reduce-scatter: every rank runs this over ITS slice of the film
+// (float4 index range [q0, q1)), reads the slice from all ranks (its own film locally, the peers
+// through NVLink), adds them in rank order -- the order of k_film_merge_pack, so the result is the
+// same bit for bit -- and writes the sum into the destination rank's film.  Each NVLink carries
+// 1/N of a film per peer instead of rank 0 pulling N - 1 whole films through its own ingress.
+__global__ void __launch_bounds__(256)
+k_film_reduce_slice(PeerFilms P, float *dst, int64_t q0, int64_t q1) {
+    for (int64_t q = q0 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < q1;
+         q += (int64_t)gridDim.x * blockDim.x) {
+        float4 v[8];
+#pragma unroll
+        for (int r = 0; r < 8; ++r)
+            if (r < P.n) v[r] = reinterpret_cast<const float4 *>(P.film[r])[q];
+        float4 acc = v[0];
+#pragma unroll
+        for (int r = 1; r < 8; ++r)
+            if (r < P.n) {
+                acc.x += v[r].x;
+                acc.y += v[r].y;
+                acc.z += v[r].z;
+                acc.w += v[r].w;
+            }
+        reinterpret_cast<float4 *>(dst)[q] = acc;
+    }
+}
+
 __global__ void k_sampler_eval(DSampler H, const int *px, const int *py, const int *sample,
                                const int *dim, int64_t n, float *out) {
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;

@@ -68,6 +68,13 @@ struct sptx_ctx {
     int pixelsKey[8] = {-1, 0, 0, 0, 0, 0, 0, 0};  // what dPixels holds: {kind, bounds / partition ...}
     // grow-only device scratch of the entry points that stage host data (ray batches, .dat planes):
     // no cudaMalloc / cudaFree per call (both are device-wide synchronisation points)
+    // peer films mapped through CUDA IPC, kept open between merges (opening a handle costs
+    // milliseconds; the handle of a film stays the same while its allocation lives)
+    struct PeerMap {
+        unsigned char handle[SPTX_IPC_HANDLE_BYTES];
+        void *ptr;
+    };
+    std::vector<PeerMap> peerMaps;
     void *scratch[3] = {nullptr, nullptr, nullptr};
     size_t scratchBytes[3] = {0, 0, 0};
     DFilm F;
@@ -275,6 +282,7 @@ extern "C" void sptx_destroy(sptx_ctx *ctx) {
     if (ctx->dFilmSplit) cudaFree(ctx->dFilmSplit);
     if (ctx->dLacc) cudaFree(ctx->dLacc);
     if (ctx->dPixels) cudaFree(ctx->dPixels);
+    for (auto &m : ctx->peerMaps) cudaIpcCloseMemHandle(m.ptr);
     for (void *s : ctx->scratch)
         if (s) cudaFree(s);
     if (ctx->dH) cudaFree(ctx->dH);
@@ -1143,6 +1151,8 @@ extern "C" int sptx_film_download(sptx_ctx *ctx, float *contrib, float *weight) 
     return SPTX_OK;
 }
 
+static int map_peer_film(sptx_ctx *ctx, const unsigned char *handle, void **out);
+
 extern "C" int sptx_film_export(sptx_ctx *ctx, void *handle) {
     if (!ctx || !handle) return fail(ctx, SPTX_EINVAL, "sptx_film_export: NULL argument");
     if (!ctx->haveScene) return fail(ctx, SPTX_ESTATE, "sptx_film_export: no scene uploaded");
@@ -1173,12 +1183,7 @@ extern "C" int sptx_film_merge_peers(sptx_ctx *ctx, const void *handles, int n_r
             P.film[r] = ctx->F.pixels;
             continue;
         }
-        cudaIpcMemHandle_t h;
-        memcpy(&h, (const char *)handles + (size_t)r * SPTX_IPC_HANDLE_BYTES, sizeof(h));
-        cudaError_t e = cudaIpcOpenMemHandle(&mapped[r], h, cudaIpcMemLazyEnablePeerAccess);
-        if (e != cudaSuccess)
-            rc = fail(ctx, SPTX_ECUDA, "sptx_film_merge_peers: mapping the film of rank %d: %s", r,
-                      cudaGetErrorString(e));
+        rc = map_peer_film(ctx, (const unsigned char *)handles + (size_t)r * SPTX_IPC_HANDLE_BYTES, &mapped[r]);
         P.film[r] = (const float *)mapped[r];
     }
     double *dPlanes = nullptr;
@@ -1198,9 +1203,139 @@ extern "C" int sptx_film_merge_peers(sptx_ctx *ctx, const void *handles, int n_r
         if (rc == SPTX_OK && cudaEventElapsedTime(&ms, ctx->ev2, ctx->ev3) == cudaSuccess) ctx->counters.film_ms += ms;
         ctx->counters.kernel_launches += 1;
     }
-    for (int r = 0; r < n_ranks; ++r)
-        if (mapped[r]) cudaIpcCloseMemHandle(mapped[r]);
     return rc;
+}
+
+// Maps the film behind `handle` (a peer rank's sptx_film_export) or returns the mapping made earlier.
+static int map_peer_film(sptx_ctx *ctx, const unsigned char *handle, void **out) {
+    for (auto &m : ctx->peerMaps)
+        if (!memcmp(m.handle, handle, SPTX_IPC_HANDLE_BYTES)) {
+            *out = m.ptr;
+            return SPTX_OK;
+        }
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, sizeof(h));
+    void *p = nullptr;
+    cudaError_t e = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess)
+        return fail(ctx, SPTX_ECUDA, "mapping a peer film: %s", cudaGetErrorString(e));
+    sptx_ctx::PeerMap m;
+    memcpy(m.handle, handle, SPTX_IPC_HANDLE_BYTES);
+    m.ptr = p;
+    ctx->peerMaps.push_back(m);
+    *out = p;
+    return SPTX_OK;
+}
+
+static int reduce_slice(sptx_ctx *ctx, const PeerFilms &P, float *dst, int n_ranks, int self) {
+    const int64_t nQuads = (int64_t)ctx->F.width * ctx->F.height * SPTX_SPECTRUM_STRIDE / 4;
+    const int64_t q0 = nQuads * self / n_ranks, q1 = nQuads * (self + 1) / n_ranks;
+    if (q1 > q0) {
+        cudaEventRecord(ctx->ev2, ctx->stream);
+        k_film_reduce_slice<<<grid_for(ctx, q1 - q0, 256), 256, 0, ctx->stream>>>(P, dst, q0, q1);
+        cudaEventRecord(ctx->ev3, ctx->stream);
+    }
+    CK(cudaStreamSynchronize(ctx->stream));
+    CK(cudaGetLastError());
+    float ms = 0.f;
+    if (q1 > q0 && cudaEventElapsedTime(&ms, ctx->ev2, ctx->ev3) == cudaSuccess) ctx->counters.film_ms += ms;
+    ctx->counters.kernel_launches += 1;
+    return SPTX_OK;
+}
+
+extern "C" int sptx_film_reduce_scatter(sptx_ctx *ctx, const void *handles, int n_ranks, int self, int dst) {
+    if (!ctx || !handles) return fail(ctx, SPTX_EINVAL, "sptx_film_reduce_scatter: NULL argument");
+    if (!ctx->haveScene) return fail(ctx, SPTX_ESTATE, "sptx_film_reduce_scatter: no scene uploaded");
+    if (n_ranks < 1 || n_ranks > 8 || self < 0 || self >= n_ranks || dst < 0 || dst >= n_ranks)
+        return fail(ctx, SPTX_EINVAL, "sptx_film_reduce_scatter: rank %d of %d to %d (at most 8 ranks)", self,
+                    n_ranks, dst);
+    CK(cudaSetDevice(ctx->device));
+    PeerFilms P;
+    P.n = n_ranks;
+    for (int r = 0; r < n_ranks; ++r) {
+        if (r == self) {
+            P.film[r] = ctx->F.pixels;
+            continue;
+        }
+        void *p = nullptr;
+        int rc = map_peer_film(ctx, (const unsigned char *)handles + (size_t)r * SPTX_IPC_HANDLE_BYTES, &p);
+        if (rc) return rc;
+        P.film[r] = (const float *)p;
+    }
+    return reduce_slice(ctx, P, const_cast<float *>(P.film[dst]), n_ranks, self);
+}
+
+// One process, one context per GPU (what GpuPathIntegrator::Render does with SPTX_DEVICES): the
+// films meet through peer access instead of IPC handles.
+extern "C" int sptx_film_merge_contexts(sptx_ctx *const *ctxs, int n, int dst) {
+    if (!ctxs || n < 1 || n > 8 || dst < 0 || dst >= n)
+        return fail(nullptr, SPTX_EINVAL, "sptx_film_merge_contexts: %d contexts, destination %d (at most 8)", n, dst);
+    PeerFilms P;
+    P.n = n;
+    for (int r = 0; r < n; ++r) {
+        sptx_ctx *c = ctxs[r];
+        if (!c || !c->haveScene) return fail(c, SPTX_ESTATE, "sptx_film_merge_contexts: context %d has no scene", r);
+        if (c->F.width != ctxs[0]->F.width || c->F.height != ctxs[0]->F.height)
+            return fail(c, SPTX_EINVAL, "sptx_film_merge_contexts: films differ in size");
+        P.film[r] = c->F.pixels;
+    }
+    for (int r = 0; r < n; ++r) {   // every device may read every other device's film
+        sptx_ctx *ctx = ctxs[r];
+        CK(cudaSetDevice(ctx->device));
+        CK(cudaStreamSynchronize(ctx->stream));
+        for (int q = 0; q < n; ++q) {
+            if (ctxs[q]->device == ctx->device) continue;
+            int can = 0;
+            CK(cudaDeviceCanAccessPeer(&can, ctx->device, ctxs[q]->device));
+            if (!can)
+                return fail(ctx, SPTX_EUNSUPPORTED, "sptx_film_merge_contexts: device %d cannot access device %d",
+                            ctx->device, ctxs[q]->device);
+            cudaError_t e = cudaDeviceEnablePeerAccess(ctxs[q]->device, 0);
+            if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled)
+                return fail(ctx, SPTX_ECUDA, "cudaDeviceEnablePeerAccess: %s", cudaGetErrorString(e));
+            cudaGetLastError();
+        }
+    }
+    for (int r = 0; r < n; ++r) {   // (slices are disjoint: the launches of different devices overlap)
+        int rc = reduce_slice(ctxs[r], P, ctxs[dst]->F.pixels, n, r);
+        if (rc) return rc;
+    }
+    return SPTX_OK;
+}
+
+// ---- NCCL film reduce (sptx_film_reduce(ctx, ncclComm_t, root)) ------------------------
+// For hosts that already hold an NCCL communicator: one ncclReduce(sum, float32) of the film onto
+// `root` on the context's stream.  libnccl is looked up at run time (the library has no link-time
+// dependency on it); the peer-memory merges above need no NCCL at all.
+#include <dlfcn.h>
+extern "C" int sptx_film_reduce(sptx_ctx *ctx, void *nccl_comm, int root) {
+    if (!ctx || !nccl_comm) return fail(ctx, SPTX_EINVAL, "sptx_film_reduce: NULL argument");
+    if (!ctx->haveScene) return fail(ctx, SPTX_ESTATE, "sptx_film_reduce: no scene uploaded");
+    typedef int (*reduce_fn)(const void *, void *, size_t, int, int, int, void *, cudaStream_t);
+    typedef const char *(*err_fn)(int);
+    static reduce_fn ncclReduceP = nullptr;
+    static err_fn ncclErrP = nullptr;
+    if (!ncclReduceP) {
+        void *lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+        if (!lib) lib = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+        if (!lib) return fail(ctx, SPTX_EUNSUPPORTED, "sptx_film_reduce: libnccl.so.2 not found (%s)", dlerror());
+        ncclReduceP = (reduce_fn)dlsym(lib, "ncclReduce");
+        ncclErrP = (err_fn)dlsym(lib, "ncclGetErrorString");
+        if (!ncclReduceP) return fail(ctx, SPTX_EUNSUPPORTED, "sptx_film_reduce: ncclReduce not in libnccl");
+    }
+    CK(cudaSetDevice(ctx->device));
+    const size_t count = (size_t)ctx->F.width * ctx->F.height * SPTX_SPECTRUM_STRIDE;
+    if (count == 0) return SPTX_OK;
+    cudaEventRecord(ctx->ev2, ctx->stream);
+    // ncclFloat32 = 7, ncclSum = 0 (nccl.h); in place on the root
+    const int rc = ncclReduceP(ctx->F.pixels, ctx->F.pixels, count, 7, 0, root, nccl_comm, ctx->stream);
+    cudaEventRecord(ctx->ev3, ctx->stream);
+    if (rc != 0)
+        return fail(ctx, SPTX_ECUDA, "sptx_film_reduce: ncclReduce: %s", ncclErrP ? ncclErrP(rc) : "error");
+    CK(cudaStreamSynchronize(ctx->stream));
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, ctx->ev2, ctx->ev3) == cudaSuccess) ctx->counters.film_ms += ms;
+    return SPTX_OK;
 }
 
 extern "C" int sptx_film_pack_dat(sptx_ctx *ctx, double *planes) {
@@ -1374,6 +1509,45 @@ extern "C" int sptx_intersect_batch_noalloc(sptx_ctx *ctx, const sptx_ray *rays,
     if (rc) return rc;
     CK(cudaMemcpyAsync(hits, dH, (size_t)n * sizeof(sptx_hit), cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
+    return SPTX_OK;
+}
+
+// ---- measurement hook: L2 read bandwidth ---------------------------------------------------------
+// The denominators of the traversal rooflines: MEASURED_PEAKS.json holds the HBM copy bandwidth, but
+// the BVH working sets of the configurations (100 KB .. 11 MB) live in the 126 MB L2.  Reads a buffer
+// of `bytes` (resident in L2 after the first sweep) `reps` times with 128-bit loads and returns GB/s.
+__global__ void k_l2_read(const float4 *buf, int64_t n4, int reps, float *sink) {
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int r = 0; r < reps; ++r)
+        for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
+            const float4 v = __ldcg(buf + i);  // cache at L2 only: every sweep goes to L2, not L1
+            acc.x += v.x;
+            acc.y += v.y;
+            acc.z += v.z;
+            acc.w += v.w;
+        }
+    if (acc.x + acc.y + acc.z + acc.w == 123.456f) *sink = acc.x;
+}
+
+extern "C" int sptx_measure_l2(sptx_ctx *ctx, int64_t bytes, int reps, double *gbs) {
+    if (!ctx || !gbs) return fail(ctx, SPTX_EINVAL, "sptx_measure_l2: NULL argument");
+    if (bytes < 4096 || bytes > ((int64_t)1 << 32) || reps < 1) return fail(ctx, SPTX_EINVAL, "sptx_measure_l2: bad size");
+    CK(cudaSetDevice(ctx->device));
+    void *buf = nullptr;
+    int rc = ctx_scratch(ctx, 1, (size_t)bytes + 16, &buf);
+    if (rc) return rc;
+    CK(cudaMemsetAsync(buf, 0, (size_t)bytes, ctx->stream));
+    const int64_t n4 = bytes / 16;
+    float *sink = (float *)((char *)buf + bytes);
+    k_l2_read<<<ctx->smCount * 8, 256, 0, ctx->stream>>>((const float4 *)buf, n4, 2, sink);  // warm-up
+    cudaEventRecord(ctx->ev0, ctx->stream);
+    k_l2_read<<<ctx->smCount * 8, 256, 0, ctx->stream>>>((const float4 *)buf, n4, reps, sink);
+    cudaEventRecord(ctx->ev1, ctx->stream);
+    CK(cudaStreamSynchronize(ctx->stream));
+    CK(cudaGetLastError());
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
+    *gbs = (double)n4 * 16.0 * reps / (ms * 1e-3) * 1e-9;
     return SPTX_OK;
 }
 

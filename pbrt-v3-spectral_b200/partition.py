@@ -68,17 +68,27 @@ def gather_handles(handle, dist=None):
     return [bytes(t.cpu().numpy().tobytes()) for t in out]
 
 
-def merge_films_over_peers(ctx, dist=None, dst=0, pack=None):
-    """The exchange step of a sample-partitioned render: every rank exports its device film, rank
-    `dst` maps the peers and sums all films in rank order with ONE kernel reading them over NVLink
-    (sptx_film_merge_peers), optionally producing the .dat planes in the same pass.  Barriers keep
-    the peers' films alive and quiescent around the merge.  Returns the planes on `dst` (or None)."""
+def merge_films_over_peers(ctx, dist=None, dst=0, pack=None, shape="reduce_scatter"):
+    """The exchange step of a sample-partitioned render: every rank exports its device film and
+    the films are summed in rank order over NVLink peer memory into rank `dst`'s film.
+    shape "reduce_scatter" (default): every rank sums its own 1/N slice of the film over all ranks
+    and writes it into dst's film (sptx_film_reduce_scatter) -- each link carries 1/N of a film;
+    shape "gather": dst alone maps the peers and sums whole films with one kernel, fused with the
+    .dat pack (sptx_film_merge_peers) -- dst's ingress carries N - 1 films.
+    Both give the same bits.  Barriers keep the films alive and quiescent around the merge.
+    Returns the .dat planes on `dst` when `pack` = (width, height) is given (else None)."""
     if dist is None or not dist.is_initialized() or dist.get_world_size() == 1:
         return ctx.film_pack_dat(*pack) if pack is not None else None
     handles = gather_handles(ctx.film_export(), dist)   # all renders of this rank are complete here
     dist.barrier()
     planes = None
-    if dist.get_rank() == dst:
-        planes = ctx.film_merge_peers(handles, dst, pack)
+    if shape == "gather":
+        if dist.get_rank() == dst:
+            planes = ctx.film_merge_peers(handles, dst, pack)
+        dist.barrier()
+        return planes
+    ctx.film_reduce_scatter(handles, dist.get_rank(), dst)
     dist.barrier()
+    if dist.get_rank() == dst and pack is not None:
+        planes = ctx.film_pack_dat(*pack)
     return planes

@@ -50,6 +50,30 @@ def test_pbrt_b200_writes_the_reference_dat(capi, name, tmp_path):
     assert rel_rmse[ref_mean > 0].max() < 0.005, f"{name}: per-bin relRMSE {rel_rmse.max():.4%}"
 
 
+def test_pbrt_b200_on_several_contexts_writes_the_single_context_dat(capi, tmp_path):
+    """Multi-GPU through the reference's own entry point: SPTX_DEVICES=0,0,0 makes
+    GpuPathIntegrator::Render drive three contexts (all on cuda:0 here; one per GPU on a multi-GPU
+    box) from one host thread each, partition the sample numbers, and sum the films through peer
+    access (sptx_film_merge_contexts) before the reference's Film::WriteImage.  C5's geometry
+    (16:9 spectral Cornell box) at a reduced size; the .dat equals the single-context one up to
+    the float summation order of the partial films."""
+    if not os.path.exists(EXE):
+        pytest.skip("host/_build/pbrt_b200 not built in this tree (needs the reference's sources)")
+    scene = str(tmp_path / "c5small.pbrt")
+    subprocess.check_call([sys.executable, os.path.join(ROOT, "scenes", "gen_scenes.py"), "cornell", scene,
+                           "res=480x270", "spp=10"])
+    dats = {}
+    for tag, devs in (("one", "0"), ("three", "0,0,0")):
+        env = dict(os.environ, SPTX_DEVICES=devs)
+        r = subprocess.run([EXE, "--quiet", scene], cwd=str(tmp_path), capture_output=True, text=True,
+                           timeout=300, env=env)
+        assert r.returncode == 0, r.stdout + r.stderr
+        assert f"{len(devs.split(','))} GPU context(s)" in r.stderr
+        dats[tag] = capi.read_dat(str(tmp_path / "c5small.dat"))
+        os.remove(str(tmp_path / "c5small.dat"))
+    np.testing.assert_allclose(dats["three"], dats["one"], rtol=1e-5, atol=1e-5 * dats["one"].mean())
+
+
 def test_pbrt_b200_reports_unsupported_scenes(tmp_path):
     """features outside the hot path are an error, never a silent approximation."""
     if not os.path.exists(EXE):

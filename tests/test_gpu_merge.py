@@ -19,7 +19,7 @@ W = H = 64
 SPP_EACH = 4
 
 
-def _worker(rank, world, port, q):
+def _worker(rank, world, port, q, shape):
     import torch.distributed as dist
     capi = importlib.import_module("pbrt-v3-spectral_b200.capi")
     part = importlib.import_module("pbrt-v3-spectral_b200.partition")
@@ -30,7 +30,12 @@ def _worker(rank, world, port, q):
     sf = capi.SceneFile(os.path.join(ROOT, "scenes", "_gen", "cornell64.sptx"))
     ctx.upload(sf)
     ctx.render(*part.sample_block(0, rank, world, SPP_EACH))
-    planes = part.merge_films_over_peers(ctx, dist, dst=0, pack=(W, H))
+    planes = part.merge_films_over_peers(ctx, dist, dst=0, pack=(W, H), shape=shape)
+    if shape == "reduce_scatter":   # a second merge reuses the mapped peer films (and adds the peers again)
+        ctx.film_clear()
+        dist.barrier()
+        ctx.render(*part.sample_block(0, rank, world, SPP_EACH))
+        planes = part.merge_films_over_peers(ctx, dist, dst=0, pack=(W, H), shape=shape)
     if rank == 0:
         merged = ctx.film_download(W, H)
         q.put((planes, merged[0], merged[1], ctx.film_pack_dat(W, H)))
@@ -40,7 +45,8 @@ def _worker(rank, world, port, q):
     dist.destroy_process_group()
 
 
-def test_two_rank_merge_equals_single_render(capi):
+@pytest.mark.parametrize("shape", ["gather", "reduce_scatter"])
+def test_two_rank_merge_equals_single_render(capi, shape):
     import torch.multiprocessing as mp
     world = 2
     with socket.socket() as s:
@@ -48,7 +54,7 @@ def test_two_rank_merge_equals_single_render(capi):
         port = s.getsockname()[1]
     mpc = mp.get_context("spawn")
     q = mpc.Queue()
-    procs = [mpc.Process(target=_worker, args=(r, world, port, q)) for r in range(world)]
+    procs = [mpc.Process(target=_worker, args=(r, world, port, q, shape)) for r in range(world)]
     for p in procs:
         p.start()
     planes, contrib, weight, packed = q.get(timeout=300)
@@ -68,3 +74,57 @@ def test_two_rank_merge_equals_single_render(capi):
     assert weight.min() >= world * SPP_EACH
     sf.close()
     ctx.close()
+
+
+def test_contexts_of_one_process_merge(capi):
+    """sptx_film_merge_contexts: what GpuPathIntegrator::Render does with SPTX_DEVICES -- one
+    context per GPU in one process (both on cuda:0 here), sample numbers split between them, films
+    summed through peer access into the first context's film."""
+    part = importlib.import_module("pbrt-v3-spectral_b200.partition")
+    blob = os.path.join(ROOT, "scenes", "_gen", "cornell64.sptx")
+    ctxs = [capi.Context(0) for _ in range(3)]
+    for c in ctxs:
+        sf = capi.SceneFile(blob)
+        c.upload(sf)
+        sf.close()
+    spp = 10
+    for c, (s0, s1) in zip(ctxs, part.split_samples(spp, len(ctxs))):
+        c.render(s0, s1)
+    capi.merge_contexts(ctxs, dst=0)
+    merged, wsum = ctxs[0].film_download(W, H)
+    one = capi.Context(0)
+    sf = capi.SceneFile(blob)
+    one.upload(sf)
+    sf.close()
+    one.render(0, spp)
+    c1, w1 = one.film_download(W, H)
+    assert np.array_equal(wsum, w1)
+    assert np.allclose(merged, c1, rtol=1e-5, atol=1e-7)
+    for c in ctxs + [one]:
+        c.close()
+
+
+def test_nccl_film_reduce_single_rank(capi):
+    """sptx_film_reduce with a one-rank communicator made with ncclCommInitAll: the
+    reduce is an in-place copy, the film is unchanged and the call goes through the context's
+    stream.  (The multi-rank form is timed by bench.py with SPTX_BENCH_NCCL_REDUCE=1.)"""
+    import ctypes as C
+    try:
+        import torch  # noqa: F401  (loads the bundled libnccl.so.2 into the process)
+        nccl = C.CDLL("libnccl.so.2")
+    except OSError:
+        pytest.skip("libnccl.so.2 not loadable on this box")
+    comm = C.c_void_p()
+    devs = (C.c_int * 1)(0)
+    assert nccl.ncclCommInitAll(C.byref(comm), 1, devs) == 0
+    ctx = capi.Context(0)
+    sf = capi.SceneFile(os.path.join(ROOT, "scenes", "_gen", "cornell64.sptx"))
+    ctx.upload(sf)
+    sf.close()
+    ctx.render(0, 4)
+    before = ctx.film_download(W, H)[0].copy()
+    ctx.film_reduce_nccl(comm.value, root=0)
+    after = ctx.film_download(W, H)[0]
+    assert np.array_equal(before, after)
+    ctx.close()
+    nccl.ncclCommDestroy(comm)

@@ -25,11 +25,21 @@ capi = importlib.import_module("pbrt-v3-spectral_b200.capi")
 GEN = os.path.join(ROOT, "scenes", "_gen")
 PEAK = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))).get("hbm_gbs", 6650.0) \
     if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else 6650.0
+L2_PEAK = None   # measured by the run itself (sptx_measure_l2, a 32 MB buffer): see l2_peak()
+
+
+def l2_peak():
+    global L2_PEAK
+    if L2_PEAK is None:
+        ctx = capi.Context(0)
+        L2_PEAK = max(ctx.measure_l2(32 << 20, 200) for _ in range(3))
+        ctx.close()
+    return L2_PEAK
 
 
 def load(name):
     ctx = capi.Context(0)
-    sf = capi.SceneFile(os.path.join(GEN, name + ".sptx"))
+    sf = capi.SceneFile(capi.unpack_blob(os.path.join(GEN, name + ".sptx")))
     ctx.upload(sf)
     sf.close()
     return ctx
@@ -80,19 +90,19 @@ def c1():
     return render_rate("killeroo400", 400, 400, 64, 8)
 
 
-def c3():
-    out = render_rate("cornell_lens2048", 2048, 2048, 256, 4)
+def c3(spp=256, cpu=True):
+    out = render_rate("cornell_lens2048", 2048, 2048, spp, 4)
     # camera-ray generation alone (K1 with lens tracing): share of the render
     out["generate_ms"] = out["kernel_ms"]["generate"]
-    out["camera_mrays_per_s"] = 2048 * 2048 * 256 / out["generate_ms"] * 1e-3
-    out["cpu_reference"] = reference_rate(["cornell_lens"], 2048, 2048, 1, 3)
+    out["camera_mrays_per_s"] = 2048 * 2048 * spp / out["generate_ms"] * 1e-3
+    if cpu:
+        out["cpu_reference"] = reference_rate(["cornell_lens"], 2048, 2048, 1, 3)
     return out
 
 
-def c4():
+def c4(n=1 << 24, n_cpu=1 << 20):
     import torch
     ctx = load("instanced_c4")
-    n = 1 << 24
     blob = open(os.path.join(GEN, "instanced_c4.sptx"), "rb").read()
     hb = int(np.frombuffer(blob[8:16], "<u8")[0])
     pos = 16 + hb
@@ -103,7 +113,8 @@ def c4():
     # coherent primary rays: the scene's own camera over a 4096x4096 sample grid
     g = np.random.Generator(np.random.Philox(key=7))
     cs = np.zeros((n, 5), np.float32)
-    side = 4096
+    side = int(round(n ** 0.5))
+    assert side * side == n, "n must be a square (the coherent batch is a side x side sample grid)"
     yy, xx = np.divmod(np.arange(n), side)
     cs[:, 0] = (xx + 0.5) * (1024.0 / side)
     cs[:, 1] = (yy + 0.5) * (1024.0 / side)
@@ -123,14 +134,20 @@ def c4():
             nodes, tests = float(hits["n_nodes"].mean()), float(hits["n_tests"].mean())
             bytes_per_ray = 48.0 + 32.0 * nodes + 48.0 * tests
             gbs = bytes_per_ray * n / (ms * 1e-3) * 1e-9
+            # The instanced BVH (11 MB) and the top level stay in L2 (126 MB): the node / triangle bytes
+            # are L2 traffic, only the rays and hit records (48 B per ray) come from HBM -- so the
+            # algorithmic rate is set against the L2 bandwidth, with the HBM share beside it.
             res["batches"][f"{name}/{'any' if any_hit else 'closest'}"] = {
                 "ms": ms, "mrays_per_s": n / ms * 1e-3, "hit_rate": float((hits["prim"] >= 0).mean()),
                 "nodes_per_ray": nodes, "tests_per_ray": tests, "algorithmic_bytes_per_ray": bytes_per_ray,
-                "achieved_gbs": gbs, "frac_of_hbm_peak": gbs / PEAK}
+                "achieved_gbs": gbs, "bound": "l2", "l2_peak_gbs": l2_peak(), "frac_of_l2_peak": gbs / l2_peak(),
+                "hbm_gbs_rays_and_hits": 48.0 * n / (ms * 1e-3) * 1e-9,
+                "frac_of_hbm_peak_rays_and_hits": 48.0 * n / (ms * 1e-3) * 1e-9 / PEAK}
     ctx.close()
     # the reference's BVHAccel::Intersect / IntersectP on the box's host cores, timed by the oracle
     # (BASELINE.md 3.3): 2^20 rays of each batch, every host thread
-    res["cpu_reference"] = c4_cpu({k: v[:1 << 20] for k, v in batches.items()})
+    if n_cpu:
+        res["cpu_reference"] = c4_cpu({k: v[:n_cpu] for k, v in batches.items()})
     return res
 
 
@@ -141,7 +158,7 @@ def c4_cpu(batches):
     exe = os.path.join(ROOT, "oracle", "_ref", "oracle_dump")
     if not os.path.exists(exe):
         return {"unavailable": "oracle/_ref/oracle_dump was not built"}
-    out = {"cores": os.cpu_count(), "rays_per_batch": 1 << 20}
+    out = {"cores": os.cpu_count(), "rays_per_batch": int(len(next(iter(batches.values()))))}
     with tempfile.TemporaryDirectory() as work:
         pbrt = os.path.join(work, "instanced_c4.pbrt")
         subprocess.check_call([sys.executable, os.path.join(ROOT, "scenes", "gen_scenes.py"), "instanced", pbrt,
