@@ -177,6 +177,10 @@ def bench_ours(args):
     ctx.upload(sf)
     film = torch.as_tensor(CudaArray(ctx.film_ptr, ctx.film_floats), device=f"cuda:{local}")
     K, W = args.steps, args.warmup
+    # the exchange step at N > 1: "reduce_scatter" (default) / "gather" = the two peer-memory merge
+    # kernels, "nccl" = a plain NCCL reduce of the film tensor, for comparison
+    merge_shape = os.environ.get("SPTX_BENCH_MERGE", "nccl" if os.environ.get("SPTX_BENCH_NCCL_REDUCE") else
+                                 "reduce_scatter")
 
     def step_range(k):
         # consecutive sample numbers; with N ranks, rank r takes the r-th block of each step
@@ -204,15 +208,15 @@ def bench_ours(args):
         # kernel reading the peers over NVLink (sptx_film_merge_peers); NCCL reduce if asked for
         f0 = ctx.counters()["film_ms"]
         t_red = time.perf_counter()
-        if os.environ.get("SPTX_BENCH_NCCL_REDUCE"):
+        if merge_shape == "nccl":
             ev0.record()
             part.reduce_film(film, dist, dst=0)
             ev1.record()
             torch.cuda.synchronize()
             reduce_ms = ev0.elapsed_time(ev1)
         else:
-            part.merge_films_over_peers(ctx, dist, dst=0)
-            reduce_ms = ctx.counters()["film_ms"] - f0 if rank == 0 else 0.0
+            part.merge_films_over_peers(ctx, dist, dst=0, shape=merge_shape)
+            reduce_ms = ctx.counters()["film_ms"] - f0   # this rank's merge kernel (max over ranks below)
         reduce_wall_ms = (time.perf_counter() - t_red) * 1e3
         dev_ms += reduce_ms
     torch.cuda.synchronize()
@@ -223,9 +227,9 @@ def bench_ours(args):
         clk_all = [None] * world
         dist.all_gather_object(clk_all, clk)
     if dist:
-        t = torch.tensor([dev_ms, wall_ms], device=f"cuda:{local}", dtype=torch.float64)
+        t = torch.tensor([dev_ms, wall_ms, reduce_ms, reduce_wall_ms], device=f"cuda:{local}", dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        dev_ms, wall_ms = float(t[0]), float(t[1])
+        dev_ms, wall_ms, reduce_ms, reduce_wall_ms = [float(v) for v in t]
     samples_total = float(RES_W * RES_H * SPP_STEP * K * world)
     value = samples_total / (dev_ms * 1e-3) * 1e-6
 
@@ -258,11 +262,11 @@ def bench_ours(args):
         if dist:
             # the product of a multi-GPU step is the MERGED film on the host: handle exchange,
             # barriers, the peer-memory merge kernel on rank 0 -- all inside the timed region
-            if os.environ.get("SPTX_BENCH_NCCL_REDUCE"):
+            if merge_shape == "nccl":
                 part.reduce_film(film, dist, dst=0)
                 torch.cuda.synchronize()
             else:
-                part.merge_films_over_peers(ctx, dist, dst=0)
+                part.merge_films_over_peers(ctx, dist, dst=0, shape=merge_shape)
         tm = time.perf_counter()
         if rank == 0:
             contrib, weight = ctx.film_download(w, h, out=host_film)  # device film -> host
@@ -371,8 +375,11 @@ def bench_ours(args):
             "cpu_baseline": cpu, "kernels": kernels, "configs": other_configs(args) if world == 1 else None,
             "wall_ms_per_step": wall_ms / K, "film_reduce_ms": reduce_ms,
             "film_reduce_wall_ms": reduce_wall_ms if world > 1 else None,
-            "film_reduce": ("nccl reduce" if os.environ.get("SPTX_BENCH_NCCL_REDUCE") else
-                            "one kernel over NVLink peer memory (sptx_film_merge_peers)") if world > 1 else None,
+            "film_reduce": {"nccl": "NCCL reduce of the film tensor (torch.distributed)",
+                            "gather": "rank 0 sums the peers' films over NVLink peer memory (sptx_film_merge_peers)",
+                            "reduce_scatter": "every rank sums its slice of all films over NVLink peer memory "
+                                              "into rank 0's film (sptx_film_reduce_scatter)"}[merge_shape]
+            if world > 1 else None,
             "rays_per_sample": (c["closest_hit_rays"] + c["shadow_rays"]) / max(c["camera_rays"], 1),
             "mrays_per_s": (c["closest_hit_rays"] + c["shadow_rays"]) / (dev_ms * 1e-3) * 1e-6,
         }

@@ -58,6 +58,7 @@
 #include "samplers/halton.h"
 #include "samplers/random.h"
 #include "samplers/sobol.h"
+#include "samplers/zerotwosequence.h"
 #include "sobolmatrices.h"
 #include "scene.h"
 #include "shapes/sphere.h"
@@ -737,10 +738,18 @@ bool FlattenScene(const Scene &scene, const Camera &camera, Sampler &sampler,
         }
     } else if (dynamic_cast<RandomSampler *>(&sampler)) {
         fsm.type = SPTX_SAMPLER_RANDOM;
+    } else if (auto *zt = dynamic_cast<ZeroTwoSequenceSampler *>(&sampler)) {
+        // ZeroTwoSequenceSampler (src/samplers/zerotwosequence.cpp): samplesPerPixel is already
+        // rounded up to a power of two; the first nSampledDimensions 1D / 2D dimensions of a
+        // pixel's samples are (0,2)-sequence tables, the rest comes from the tile's RNG
+        if (!zt->samples1DArraySizes.empty() || !zt->samples2DArraySizes.empty())
+            return fail("sampler array requests are not on the path");
+        fsm.type = SPTX_SAMPLER_ZEROTWO;
+        fsm.n_dims = (int)zt->samples1D.size();
     } else
         return fail(
             "sampler type is outside the GPU hot path (supported: halton, "
-            "sobol, random)");
+            "sobol, random, 02sequence)");
 
     // ---- integrator
     sptx_integrator &fi = out->desc.integrator;
@@ -749,12 +758,13 @@ bool FlattenScene(const Scene &scene, const Camera &camera, Sampler &sampler,
     for (int i = 0; i < 4; ++i) fi.pixel_bounds[i] = params.pixelBounds[i];
     fi.num_ca_bands = params.numCABands;
     out->desc.metadata_strategy = (uint32_t)params.metadataStrategy;
-    if (params.metadataStrategy &&
-        out->desc.sampler.type == SPTX_SAMPLER_RANDOM)
+    const bool tileSerial = out->desc.sampler.type == SPTX_SAMPLER_RANDOM ||
+                            out->desc.sampler.type == SPTX_SAMPLER_ZEROTWO;
+    if (params.metadataStrategy && tileSerial)
         return fail(
             "Integrator \"metadata\" is on the GPU hot path for the halton "
             "and sobol samplers only");
-    if (params.numCABands > 1 && out->desc.sampler.type == SPTX_SAMPLER_RANDOM)
+    if (params.numCABands > 1 && tileSerial)
         return fail(
             "spectralpath with numCABands > 1 is on the GPU hot path for the "
             "halton and sobol samplers only");

@@ -124,8 +124,9 @@ void GpuPathIntegrator::Render(const Scene &scene) {
         ExitNow();
     }
     const int nCtx = (int)devices.size();
-    if (nCtx > 1 && flat.desc.sampler.type == SPTX_SAMPLER_RANDOM) {
-        Error("GpuPathIntegrator: the RandomSampler's tile streams cannot be cut by sample number; "
+    if (nCtx > 1 && (flat.desc.sampler.type == SPTX_SAMPLER_RANDOM ||
+                     flat.desc.sampler.type == SPTX_SAMPLER_ZEROTWO)) {
+        Error("GpuPathIntegrator: a per-tile RNG stream (random, 02sequence) cannot be cut by sample number; "
               "use one device");
         ExitNow();
     }

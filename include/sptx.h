@@ -180,7 +180,13 @@ typedef struct sptx_camera {
     float pad[3];
 } sptx_camera;
 
-enum { SPTX_SAMPLER_HALTON = 0, SPTX_SAMPLER_RANDOM = 1, SPTX_SAMPLER_SOBOL = 2 };
+enum {
+    SPTX_SAMPLER_HALTON = 0,
+    SPTX_SAMPLER_RANDOM = 1,
+    SPTX_SAMPLER_SOBOL = 2,
+    SPTX_SAMPLER_ZEROTWO = 3 /* ZeroTwoSequenceSampler (src/samplers/zerotwosequence.cpp): spp is the
+                                rounded-up power of two, n_dims = nSampledDimensions; no tables */
+};
 
 /* HaltonSampler state, src/samplers/halton.cpp:65-92. */
 typedef struct sptx_sampler {

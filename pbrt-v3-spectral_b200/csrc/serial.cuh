@@ -124,7 +124,13 @@ struct ZeroTwoSampler {
             const float2 v = t2[(size_t)(cur2++) * spp + index];
             return V2{v.x, v.y};
         }
-        return rng.get2d();
+        // PixelSampler::Get2D returns Point2f(rng.UniformFloat(), rng.UniformFloat()): a constructor
+        // call, whose arguments the reference's compiler (g++, x86-64) evaluates right to left --
+        // y takes the first draw.  (RandomSampler::Get2D is a brace list: left to right.)
+        V2 p;
+        p.y = rng.uniform_float();
+        p.x = rng.uniform_float();
+        return p;
     }
 };
 

@@ -450,6 +450,10 @@ static int validate_scene(sptx_ctx *ctx, const sptx_scene_desc *sc) {
             "Sobol tables missing");
     } else if (sc->sampler.type == SPTX_SAMPLER_RANDOM) {
         REQ(sc->sampler.spp > 0, "RandomSampler needs samplesPerPixel");
+    } else if (sc->sampler.type == SPTX_SAMPLER_ZEROTWO) {
+        REQ(sc->sampler.spp > 0 && (sc->sampler.spp & (sc->sampler.spp - 1)) == 0 && sc->sampler.n_dims >= 0 &&
+                sc->sampler.n_dims <= 64,
+            "ZeroTwoSequenceSampler needs a power-of-two samplesPerPixel and 0..64 sampled dimensions");
     } else
         return fail(ctx, SPTX_EUNSUPPORTED, "sptx_upload_scene: sampler type %d", sc->sampler.type);
     if (sc->camera.type == SPTX_CAMERA_REALISTIC)
@@ -797,12 +801,17 @@ static int ensure_paths(sptx_ctx *ctx, int64_t P) {
     return SPTX_OK;
 }
 
+// Samplers whose values come from one RNG stream per tile (RandomSampler, ZeroTwoSequenceSampler).
+static bool tile_serial(const sptx_ctx *ctx) {
+    return ctx->H.s.type == SPTX_SAMPLER_RANDOM || ctx->H.s.type == SPTX_SAMPLER_ZEROTWO;
+}
+
 // RandomSampler: the tiles of SamplerIntegrator::Render, one single-lane warp each (serial.cuh).
 // The stream of a tile is stateful, so only the scene's whole sample range can be rendered.
 static int render_serial(sptx_ctx *ctx, const int32_t *bounds, int part, int nParts, int s0, int s1) {
     if (s0 != 0 || s1 != ctx->H.s.spp)
         return fail(ctx, SPTX_EUNSUPPORTED,
-                    "render: RandomSampler streams run through all %d samples of a tile; sample range "
+                    "render: RandomSampler / ZeroTwoSequenceSampler streams run through all %d samples of a tile; sample range "
                     "[%d,%d) cannot be rendered on its own", ctx->H.s.spp, s0, s1);
     if (ctx->metadataStrategy)
         return fail(ctx, SPTX_EUNSUPPORTED,
@@ -828,10 +837,24 @@ static int render_serial(sptx_ctx *ctx, const int32_t *bounds, int part, int nPa
     P.maxDepth = ctx->integ.max_depth;
     P.rrThreshold = ctx->integ.rr_threshold;
     P.wavelength = 550.f;
+    P.nDims = 0;
+    P.tables = nullptr;
     const int nTiles = P.nTilesX * P.nTilesY;
     if (nTiles <= 0) return SPTX_OK;
+    const bool zeroTwo = ctx->H.s.type == SPTX_SAMPLER_ZEROTWO;
+    if (zeroTwo) {
+        // per tile: the pixel's sample tables, [nDims][spp] floats + [nDims][spp] points
+        P.nDims = ctx->H.s.n_dims;
+        void *t = nullptr;
+        int rc = ctx_scratch(ctx, 1, std::max<size_t>(16, (size_t)nTiles * P.nDims * P.spp * 3 * sizeof(float)), &t);
+        if (rc) return rc;
+        P.tables = (float *)t;
+    }
     cudaEventRecord(ctx->ev0, ctx->stream);
-    k_render_serial<<<nTiles, 32, 0, ctx->stream>>>(ctx->dS, ctx->C, ctx->F, P, ctx->dCnt, part, nParts);
+    if (zeroTwo)
+        k_render_serial<ZeroTwoSampler><<<nTiles, 32, 0, ctx->stream>>>(ctx->dS, ctx->C, ctx->F, P, ctx->dCnt, part, nParts);
+    else
+        k_render_serial<Pcg32><<<nTiles, 32, 0, ctx->stream>>>(ctx->dS, ctx->C, ctx->F, P, ctx->dCnt, part, nParts);
     cudaEventRecord(ctx->ev1, ctx->stream);
     CK(cudaStreamSynchronize(ctx->stream));
     CK(cudaGetLastError());
@@ -1049,7 +1072,7 @@ extern "C" int sptx_render(sptx_ctx *ctx, const int32_t *pixel_bounds, int sampl
     if (sample_begin < 0 || sample_end < sample_begin)
         return fail(ctx, SPTX_EINVAL, "sptx_render: bad sample range [%d,%d)", sample_begin, sample_end);
     CK(cudaSetDevice(ctx->device));
-    if (ctx->H.s.type == SPTX_SAMPLER_RANDOM) return render_serial(ctx, pixel_bounds, 0, 1, sample_begin, sample_end);
+    if (tile_serial(ctx)) return render_serial(ctx, pixel_bounds, 0, 1, sample_begin, sample_end);
     int b[4];
     for (int i = 0; i < 4; ++i) b[i] = ctx->F.f.sample_bounds[i];
     auto clip = [&](const int32_t *o) {
@@ -1078,7 +1101,7 @@ extern "C" int sptx_render_tiles(sptx_ctx *ctx, int part, int n_parts, int sampl
     if (n_parts < 1 || part < 0 || part >= n_parts)
         return fail(ctx, SPTX_EINVAL, "sptx_render_tiles: part %d of %d", part, n_parts);
     CK(cudaSetDevice(ctx->device));
-    if (ctx->H.s.type == SPTX_SAMPLER_RANDOM) return render_serial(ctx, nullptr, part, n_parts, sample_begin, sample_end);
+    if (tile_serial(ctx)) return render_serial(ctx, nullptr, part, n_parts, sample_begin, sample_end);
     // Tiles as SamplerIntegrator::Render cuts them (core/integrator.cpp:232-257).
     const int *sb = ctx->F.f.sample_bounds;
     const int *pb = ctx->integ.pixel_bounds;
@@ -1558,7 +1581,7 @@ extern "C" int sptx_sampler_eval(sptx_ctx *ctx, const int32_t *px, const int32_t
     if (!ctx) return fail(nullptr, SPTX_EINVAL, "sptx_sampler_eval: ctx is NULL");
     if (!ctx->haveScene) return fail(ctx, SPTX_ESTATE, "sptx_sampler_eval: no scene uploaded");
     if (n <= 0) return SPTX_OK;
-    if (ctx->H.s.type == SPTX_SAMPLER_RANDOM)
+    if (tile_serial(ctx))
         return fail(ctx, SPTX_EUNSUPPORTED, "sptx_sampler_eval: only for the Halton and Sobol samplers (a RandomSampler value depends on the whole tile before it)");
     CK(cudaSetDevice(ctx->device));
     std::vector<void *> pool;
@@ -1612,7 +1635,7 @@ extern "C" int sptx_debug_radiance(sptx_ctx *ctx, const int32_t *px, const int32
     if (!ctx) return fail(nullptr, SPTX_EINVAL, "sptx_debug_radiance: ctx is NULL");
     if (!ctx->haveScene) return fail(ctx, SPTX_ESTATE, "sptx_debug_radiance: no scene uploaded");
     if (n <= 0) return SPTX_OK;
-    if (ctx->H.s.type == SPTX_SAMPLER_RANDOM)
+    if (tile_serial(ctx))
         return fail(ctx, SPTX_EUNSUPPORTED, "sptx_debug_radiance: only for the Halton and Sobol samplers (a RandomSampler value depends on the whole tile before it)");
     CK(cudaSetDevice(ctx->device));
     std::vector<int2> pixels((size_t)n);

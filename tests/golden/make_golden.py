@@ -194,10 +194,19 @@ def make(name):
               f"{int(ok.sum())}/{n_cam} camera rays, Li mean {lv[:, :31].mean():.4f}, dat mean {dat.mean():.4f}")
 
 
+# Samplers fed by one RNG stream per tile: name -> (gen_scenes arguments, resolution, spp)
+TILE_SERIAL = {
+    "cornell_random": (["cornell", "res=48x40", "spp=4", "sampler=random"], (48, 40), 4),
+    # ZeroTwoSequenceSampler; 6 spp is rounded up to 8 by the sampler, and the
+    # path leaves the 4 sampled dimensions after the first bounce (RNG draws from then on)
+    "cornell_02seq": (["cornell", "res=48x40", "spp=6", "sampler=02sequence"], (48, 40), 8),
+}
+
+
 def make_random(name="cornell_random"):
-    """RandomSampler fixture: the reference's render only (its values are not a function of
-    (pixel, sample, dimension), so there is nothing else to query)."""
-    gen = ["cornell", "res=48x40", "spp=4", "sampler=random"]
+    """RandomSampler / ZeroTwoSequenceSampler fixtures: the reference's render only (their values are
+    not a function of (pixel, sample, dimension), so there is nothing else to query)."""
+    gen, res, spp = TILE_SERIAL[name]
     with tempfile.TemporaryDirectory() as work:
         pbrt = os.path.join(work, name + ".pbrt")
         run([sys.executable, os.path.join(ROOT, "scenes", "gen_scenes.py"), gen[0], pbrt] + gen[1:])
@@ -209,7 +218,7 @@ def make_random(name="cornell_random"):
         import importlib
         capi = importlib.import_module("pbrt-v3-spectral_b200.capi")
         dat = capi.read_dat(os.path.join(work, name + ".dat")).astype(np.float32)
-    np.savez_compressed(os.path.join(GOLD, name + ".npz"), res=np.array([48, 40]), spp=np.array(4), dat=dat)
+    np.savez_compressed(os.path.join(GOLD, name + ".npz"), res=np.array(res), spp=np.array(spp), dat=dat)
     print(f"{name}: dat mean {dat.mean():.4f}")
 
 
@@ -348,11 +357,11 @@ def read_root_bounds(blob):
 
 
 if __name__ == "__main__":
-    names = sys.argv[1:] or list(SCENES) + ["cornell_random"] + list(BAND_SCENES) + list(META_SCENES) + ["visits"]
+    names = sys.argv[1:] or list(SCENES) + list(TILE_SERIAL) + list(BAND_SCENES) + list(META_SCENES) + ["visits"]
     for n in names:
         if n == "visits":
             make_visits()
-        elif n == "cornell_random":
+        elif n in TILE_SERIAL:
             make_random(n)
         elif n in BAND_SCENES:
             make_bands(n)

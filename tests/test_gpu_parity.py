@@ -169,3 +169,36 @@ def test_random_sampler_reproduces_the_reference_stream(capi):
         ctx.sampler_eval(np.array([1]), np.array([1]), np.array([0]), np.array([2]))
     sf.close()
     ctx.close()
+
+
+def test_zerotwo_sampler_reproduces_the_reference_stream(capi):
+    """ZeroTwoSequenceSampler (src/samplers/zerotwosequence.cpp): per pixel the
+    first four 1D / 2D dimensions of every sample are scrambled, shuffled (0,2)-sequence tables drawn
+    from the tile's RNG stream, later dimensions are RNG draws -- reproduced tile by tile
+    (csrc/serial.cuh).  Same stream -> the render matches like Halton's does."""
+    g = golden("cornell_02seq")
+    ctx = capi.Context(0)
+    sf = capi.SceneFile(blob_path("cornell_02seq"))
+    ctx.upload(sf)
+    w, h = [int(v) for v in g["res"]]
+    spp = int(g["spp"])
+    assert spp == 8   # "pixelsamples" 6, rounded up to a power of two by the sampler
+    ctx.render(0, spp)
+    planes = ctx.film_pack_dat(w, h)
+    ref = g["dat"].astype(np.float64)
+    tot_ref, tot_mine = ref.sum(axis=0), planes.sum(axis=0)
+    flipped = np.abs(tot_mine - tot_ref) > 1e-3 * np.maximum(tot_ref, ref.mean() * ref.shape[0])
+    assert flipped.sum() <= 2, f"{flipped.sum()} pixels differ"
+    keep = ~flipped
+    rel_rmse = np.sqrt((((planes - ref) ** 2)[:, keep]).mean(axis=1)) / np.maximum(ref[:, keep].mean(axis=1), 1e-12)
+    assert rel_rmse.max() < 0.005, f"per-bin relRMSE {rel_rmse.max():.4%}"
+    # tile partitions (multi-GPU partitioning A) give the same film
+    whole = ctx.film_download(w, h)[0].copy()
+    ctx.film_clear()
+    for part in range(2):
+        ctx.render_tiles(part, 2, 0, spp)
+    assert np.allclose(ctx.film_download(w, h)[0], whole, rtol=1e-5, atol=1e-7)
+    with pytest.raises(capi.SptxError, match="ZeroTwoSequenceSampler"):
+        ctx.render(0, spp - 1)
+    sf.close()
+    ctx.close()
