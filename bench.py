@@ -182,9 +182,14 @@ def bench_ours(args):
     merge_shape = os.environ.get("SPTX_BENCH_MERGE", "nccl" if os.environ.get("SPTX_BENCH_NCCL_REDUCE") else
                                  "reduce_scatter")
 
+    # SPTX_BENCH_EMULATE="r,N": a single GPU renders the sample numbers rank r of N would get
+    # (used to separate "larger Halton indices" from "more GPUs" in the scaling numbers)
+    emu = os.environ.get("SPTX_BENCH_EMULATE")
+    emu_rank, emu_world = [int(v) for v in emu.split(",")] if (emu and world == 1) else (rank, world)
+
     def step_range(k):
         # consecutive sample numbers; with N ranks, rank r takes the r-th block of each step
-        return part.sample_block(k, rank, world, SPP_STEP, SPP_TOTAL)
+        return part.sample_block(k, emu_rank, emu_world, SPP_STEP, SPP_TOTAL)
 
     for k in range(W):
         ctx.render(*step_range(k))
@@ -364,7 +369,8 @@ def bench_ours(args):
                        "spp_per_step": SPP_STEP, "partition": "sample numbers across ranks + film merge on rank 0"
                        if world > 1 else "single GPU",
                        "l2": "path state of a pass (4.2 M paths, ~3.7 GB) exceeds L2 between launches",
-                       "shade_arithmetic": ctx.shade_arithmetic},
+                       "shade_arithmetic": ctx.shade_arithmetic,
+                       "sample_numbers_of_rank": [emu_rank, emu_world] if emu else None},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "steps": e2e_steps,
                     "ms_per_step": {n: 1e3 * v / e2e_steps

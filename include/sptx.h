@@ -353,6 +353,13 @@ int sptx_intersect_batch_device(sptx_ctx *ctx, const void *d_rays, int64_t n,
 int sptx_intersect_batch_noalloc(sptx_ctx *ctx, const sptx_ray *rays, int64_t n,
                                  sptx_hit *hits, int any_hit);
 
+/* sptx_set_option(ctx, "device_bvh", 1): the next sptx_upload_scene ignores the scene's node array
+ * and builds every aggregate's BVH on the device (Morton codes, radix sort, parallel LBVH; csrc/lbvh.cuh)
+ * instead of taking the host build of BVHAccel::BVHAccel (src/accelerators/bvh.cpp:183-225, HLBVHBuild
+ * :404-638).  Primitive ids reported by sptx_intersect_batch stay the caller's.  Device time of the
+ * last build in milliseconds (0 when the host's tree was used): */
+double sptx_bvh_build_ms(const sptx_ctx *ctx);
+
 /* Measurement hook (no counterpart in the reference): read bandwidth of an L2-resident buffer of
  * `bytes`, swept `reps` times, in GB/s -- the roofline denominator of traversal when the BVH
  * working set lives in L2 (bench.py, tools/bench_configs.py). */

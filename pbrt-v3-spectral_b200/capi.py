@@ -21,7 +21,7 @@ STRIDE = 32
 SYMBOLS = [
     "sptx_abi_version", "sptx_create", "sptx_destroy", "sptx_last_error",
     "sptx_upload_scene", "sptx_intersect_batch", "sptx_intersect_batch_device",
-    "sptx_intersect_batch_noalloc", "sptx_measure_l2",
+    "sptx_intersect_batch_noalloc", "sptx_measure_l2", "sptx_bvh_build_ms",
     "sptx_render", "sptx_render_tiles", "sptx_film_clear", "sptx_film_device_ptr",
     "sptx_film_export", "sptx_film_merge_peers", "sptx_film_reduce_scatter", "sptx_film_merge_contexts",
     "sptx_film_reduce",
@@ -84,6 +84,8 @@ def lib():
     L.sptx_intersect_batch_device.argtypes = [vp, vp, i64, vp, i32, i32, f32p]
     L.sptx_intersect_batch_noalloc.argtypes = [vp, vp, i64, vp, i32]
     L.sptx_measure_l2.argtypes = [vp, i64, i32, C.POINTER(C.c_double)]
+    L.sptx_bvh_build_ms.argtypes = [vp]
+    L.sptx_bvh_build_ms.restype = C.c_double
     L.sptx_render.argtypes = [vp, i32p, i32, i32]
     L.sptx_render_tiles.argtypes = [vp, i32, i32, i32, i32]
     L.sptx_film_clear.argtypes = [vp]
@@ -218,6 +220,10 @@ class Context:
         self._ck(lib().sptx_intersect_batch_noalloc(self.h, _ptr(rays), rays.shape[0], _ptr(hits),
                                                     int(any_hit)), "sptx_intersect_batch_noalloc")
         return hits
+
+    def bvh_build_ms(self):
+        """Device time of the last on-device BVH build (set_option("device_bvh", 1)), else 0."""
+        return lib().sptx_bvh_build_ms(self.h)
 
     def measure_l2(self, nbytes=32 << 20, reps=200):
         """GB/s of 128-bit reads from an L2-resident buffer (sptx_measure_l2)."""

@@ -128,7 +128,8 @@ k_ray_batch(DScene S, const sptx_ray *rays, int64_t n, sptx_hit *hits) {
         } else {
             HitRec h;
             scene_intersect<COUNT>(S, ray, &h, &tc);
-            out.prim = h.prim;
+            // (a BVH built on the device orders the primitives its own way: callers see their ids)
+            out.prim = (h.prim >= 0 && S.prim_ids) ? S.prim_ids[h.prim] : h.prim;
             out.instance = h.inst;
             out.b0 = h.b0;
             out.b1 = h.b1;

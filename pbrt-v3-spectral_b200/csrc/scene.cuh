@@ -20,6 +20,7 @@ struct DScene {
     const float4 *leafv;  // 3 x float4 per primitive
     const sptx_prim *prims;
     const uint8_t *prim_class;  // shading class of the primitive's material (1..kShadeClasses-1)
+    const int *prim_ids;  // device-built BVHs reorder the primitives: index the caller knows (or NULL)
     const sptx_mesh *meshes;
     const sptx_triangle *triangles;
     const float *positions, *normals, *tangents, *uvs;

@@ -13,6 +13,7 @@
 
 #include "setup.cuh"
 #include "serial.cuh"
+#include "lbvh.cuh"
 
 using namespace sptx;
 
@@ -90,6 +91,10 @@ struct sptx_ctx {
     // square root (csrc/shade.cu).  SPTX_EXACT=1 in the environment makes exact the default.
     bool shadeExact = false;
     ShadePlan shadePlan;
+    // "device_bvh": sptx_upload_scene ignores the scene's node array and builds the BVHs on the
+    // device (csrc/lbvh.cuh); build_ms = device time of the last build
+    bool deviceBvh = false;
+    double bvhBuildMs = 0.0;
     std::vector<cudaEvent_t> evPool;
     int smCount = 148;
 };
@@ -301,12 +306,18 @@ extern "C" int sptx_set_option(sptx_ctx *ctx, const char *name, int64_t value) {
         ctx->countVisits = value != 0;
         return SPTX_OK;
     }
+    if (!strcmp(name, "device_bvh")) {  // takes effect at the next sptx_upload_scene
+        ctx->deviceBvh = value != 0;
+        return SPTX_OK;
+    }
     if (!strcmp(name, "shade_exact")) {  // 1: K3 with the reference's roundings; 0: the fast build of K3
         ctx->shadeExact = value != 0;
         return SPTX_OK;
     }
     return fail(ctx, SPTX_EINVAL, "sptx_set_option: unknown option %s", name);
 }
+
+extern "C" double sptx_bvh_build_ms(const sptx_ctx *ctx) { return ctx ? ctx->bvhBuildMs : 0.0; }
 
 extern "C" int sptx_set_wavefront_size(sptx_ctx *ctx, int64_t max_paths) {
     if (!ctx) return fail(nullptr, SPTX_EINVAL, "ctx is NULL");
@@ -466,6 +477,152 @@ static int validate_scene(sptx_ctx *ctx, const sptx_scene_desc *sc) {
     return SPTX_OK;
 }
 
+// ---- BVH build on the device (csrc/lbvh.cuh) ------------------------------------------------------
+// Builds aggregate `b` (primitives [primBase, primBase + n) of the scene tables) into `nodesOut`
+// (2n - 1 records), permuting the primitive tables into Morton order.  Scratch comes from `pool`
+// (released with the scene).  Returns the root bounds in rootBounds[6].
+static int lbvh_build_one(sptx_ctx *ctx, std::vector<void *> &pool, DScene &S, int primBase, int n,
+                          const float *dInstBounds, sptx_bvh_node *nodesOut, sptx_prim *primsTmp, float4 *leafvTmp,
+                          uint8_t *classTmp, int *idsTmp, float rootBounds[6]) {
+    int rc;
+    float *bmin, *bmax, *nbmin, *nbmax;
+    uint32_t *codes, *codesSorted;
+    int *order, *orderSorted, *left, *right, *parent, *flag, *size, *axis, *dfs, *frontier[2], *scal;
+    const int nn = 2 * n - 1;
+    if ((rc = dalloc(ctx, pool, 3 * (int64_t)n, &bmin)) || (rc = dalloc(ctx, pool, 3 * (int64_t)n, &bmax)) ||
+        (rc = dalloc(ctx, pool, 3 * (int64_t)nn, &nbmin)) || (rc = dalloc(ctx, pool, 3 * (int64_t)nn, &nbmax)) ||
+        (rc = dalloc(ctx, pool, (int64_t)n, &codes)) || (rc = dalloc(ctx, pool, (int64_t)n, &codesSorted)) ||
+        (rc = dalloc(ctx, pool, (int64_t)n, &order)) || (rc = dalloc(ctx, pool, (int64_t)n, &orderSorted)) ||
+        (rc = dalloc(ctx, pool, (int64_t)n, &left)) || (rc = dalloc(ctx, pool, (int64_t)n, &right)) ||
+        (rc = dalloc(ctx, pool, (int64_t)nn, &parent)) || (rc = dalloc(ctx, pool, (int64_t)n, &flag)) ||
+        (rc = dalloc(ctx, pool, (int64_t)nn, &size)) || (rc = dalloc(ctx, pool, (int64_t)n, &axis)) ||
+        (rc = dalloc(ctx, pool, (int64_t)nn, &dfs)) || (rc = dalloc(ctx, pool, (int64_t)n, &frontier[0])) ||
+        (rc = dalloc(ctx, pool, (int64_t)n, &frontier[1])) || (rc = dalloc(ctx, pool, 8, &scal)))
+        return rc;
+    cudaStream_t st = ctx->stream;
+    const int B = 256, G = (n + B - 1) / B;
+    // centroid bounds as ordered ints: min = +inf, max = -inf
+    const int init[8] = {0x7f800000, 0x7f800000, 0x7f800000, (int)(0xff800000u ^ 0x7fffffffu),
+                         (int)(0xff800000u ^ 0x7fffffffu), (int)(0xff800000u ^ 0x7fffffffu), 0, 0};
+    CK(cudaMemcpyAsync(scal, init, sizeof(init), cudaMemcpyHostToDevice, st));
+    k_lbvh_prim_bounds<<<G, B, 0, st>>>(S, primBase, n, dInstBounds, bmin, bmax, scal, scal + 3);
+    k_lbvh_morton<<<G, B, 0, st>>>(n, bmin, bmax, scal, scal + 3, codes, order);
+    size_t tmpBytes = 0;
+    cub::DeviceRadixSort::SortPairs(nullptr, tmpBytes, codes, codesSorted, order, orderSorted, n, 0, 30, st);
+    void *tmp = nullptr;
+    if ((rc = dalloc(ctx, pool, (int64_t)tmpBytes + 16, (char **)&tmp))) return rc;
+    cub::DeviceRadixSort::SortPairs(tmp, tmpBytes, codes, codesSorted, order, orderSorted, n, 0, 30, st);
+    CK(cudaMemsetAsync(flag, 0, (size_t)n * sizeof(int), st));
+    k_lbvh_tree<<<G, B, 0, st>>>(n, codesSorted, left, right, parent, axis);
+    k_lbvh_fit<<<G, B, 0, st>>>(n, orderSorted, bmin, bmax, left, right, parent, flag, nbmin, nbmax, size);
+    // depth-first numbering, one launch per level
+    const int zero = 0;
+    CK(cudaMemcpyAsync(dfs, &zero, sizeof(int), cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(frontier[0], &zero, sizeof(int), cudaMemcpyHostToDevice, st));
+    int nFront = 1, cur = 0;
+    for (int level = 0; nFront > 0; ++level) {
+        if (level > 128) return fail(ctx, SPTX_ECUDA, "device BVH build: tree deeper than 128 levels");
+        CK(cudaMemsetAsync(scal + 6, 0, sizeof(int), st));
+        k_lbvh_number<<<(nFront + B - 1) / B, B, 0, st>>>(n, nFront, frontier[cur], frontier[cur ^ 1], scal + 6, left,
+                                                         right, size, dfs);
+        CK(cudaMemcpyAsync(&nFront, scal + 6, sizeof(int), cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        cur ^= 1;
+    }
+    k_lbvh_emit<<<(nn + B - 1) / B, B, 0, st>>>(n, left, right, axis, dfs, nbmin, nbmax, nodesOut);
+    k_lbvh_permute<<<G, B, 0, st>>>(n, primBase, orderSorted, S.prims, S.leafv, S.prim_class, S.prim_ids, primsTmp,
+                                    leafvTmp, classTmp, idsTmp);
+    // permuted tables back in place (this aggregate's range only)
+    CK(cudaMemcpyAsync(const_cast<sptx_prim *>(S.prims) + primBase, primsTmp + primBase, (size_t)n * sizeof(sptx_prim),
+                       cudaMemcpyDeviceToDevice, st));
+    CK(cudaMemcpyAsync(const_cast<float4 *>(S.leafv) + 3 * (size_t)primBase, leafvTmp + 3 * (size_t)primBase,
+                       (size_t)n * 3 * sizeof(float4), cudaMemcpyDeviceToDevice, st));
+    CK(cudaMemcpyAsync(const_cast<uint8_t *>(S.prim_class) + primBase, classTmp + primBase, (size_t)n,
+                       cudaMemcpyDeviceToDevice, st));
+    CK(cudaMemcpyAsync(const_cast<int *>(S.prim_ids) + primBase, idsTmp + primBase, (size_t)n * sizeof(int),
+                       cudaMemcpyDeviceToDevice, st));
+    float rb[6];
+    CK(cudaMemcpyAsync(rb, nbmin, 3 * sizeof(float), cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(rb + 3, nbmax, 3 * sizeof(float), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    CK(cudaGetLastError());
+    memcpy(rootBounds, rb, sizeof(rb));
+    return SPTX_OK;
+}
+
+__global__ void k_iota(int *p, int64_t n) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+        p[i] = (int)i;
+}
+// All aggregates of the scene, object BVHs first (the top level needs their root bounds).
+// Replaces S.nodes / S.bvhs; sets S.prim_ids; S.wb_* = the top level's root bounds.
+static int lbvh_build_scene(sptx_ctx *ctx, std::vector<void *> &pool, DScene &S, const sptx_scene_desc *sc) {
+    int rc;
+    const int64_t nPrims = sc->n_prims;
+    int *ids;
+    if ((rc = dalloc(ctx, pool, std::max<int64_t>(nPrims, 1), &ids))) return rc;
+    k_iota<<<grid_for(ctx, std::max<int64_t>(nPrims, 1)), kBlock, 0, ctx->stream>>>(ids, nPrims);
+    S.prim_ids = ids;
+    sptx_prim *primsTmp;
+    float4 *leafvTmp;
+    uint8_t *classTmp;
+    int *idsTmp;
+    if ((rc = dalloc(ctx, pool, std::max<int64_t>(nPrims, 1), &primsTmp)) ||
+        (rc = dalloc(ctx, pool, 3 * std::max<int64_t>(nPrims, 1), &leafvTmp)) ||
+        (rc = dalloc(ctx, pool, std::max<int64_t>(nPrims, 1), &classTmp)) ||
+        (rc = dalloc(ctx, pool, std::max<int64_t>(nPrims, 1), &idsTmp)))
+        return rc;
+    std::vector<sptx_bvh> bvhs(sc->bvhs, sc->bvhs + sc->n_bvhs);
+    int64_t totalNodes = 0;
+    for (auto &b : bvhs) {
+        b.node_base = (int32_t)totalNodes;
+        b.n_nodes = b.n_prims >= 2 ? 2 * b.n_prims - 1 : 0;  // 0 or 1 primitive: node-less aggregate
+        totalNodes += b.n_nodes;
+    }
+    sptx_bvh_node *nodes;
+    if ((rc = dalloc(ctx, pool, std::max<int64_t>(totalNodes, 1), &nodes))) return rc;
+    std::vector<float> instBounds(6 * (size_t)sc->n_bvhs, 0.f);
+    float *dInstBounds;
+    if ((rc = dalloc(ctx, pool, 6 * (int64_t)sc->n_bvhs, &dInstBounds))) return rc;
+    cudaEventRecord(ctx->ev2, ctx->stream);
+    for (int pass = 0; pass < 2; ++pass)   // object aggregates (index > 0), then the scene's
+        for (int64_t k = (pass == 0 ? 1 : 0); k < (pass == 0 ? sc->n_bvhs : 1); ++k) {
+            const sptx_bvh &b = bvhs[(size_t)k];
+            float rb[6] = {0, 0, 0, 0, 0, 0};
+            if (pass == 1)
+                CK(cudaMemcpyAsync(dInstBounds, instBounds.data(), instBounds.size() * sizeof(float),
+                                   cudaMemcpyHostToDevice, ctx->stream));
+            if (b.n_prims >= 2) {
+                if ((rc = lbvh_build_one(ctx, pool, S, b.prim_base, b.n_prims, dInstBounds, nodes + b.node_base,
+                                         primsTmp, leafvTmp, classTmp, idsTmp, rb)))
+                    return rc;
+            } else if (b.n_prims == 1) {
+                // one primitive: its bounds through the same kernel (scratch of 2 x 3 floats + 6 ints)
+                float *bb;
+                int *cc;
+                if ((rc = dalloc(ctx, pool, 6, &bb)) || (rc = dalloc(ctx, pool, 6, &cc))) return rc;
+                k_lbvh_prim_bounds<<<1, 32, 0, ctx->stream>>>(S, b.prim_base, 1, dInstBounds, bb, bb + 3, cc, cc + 3);
+                CK(cudaMemcpyAsync(rb, bb, 6 * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+                CK(cudaStreamSynchronize(ctx->stream));
+            }
+            for (int a = 0; a < 6; ++a) instBounds[6 * (size_t)k + a] = rb[a];
+        }
+    cudaEventRecord(ctx->ev3, ctx->stream);
+    CK(cudaStreamSynchronize(ctx->stream));
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, ctx->ev2, ctx->ev3);
+    ctx->bvhBuildMs = ms;
+    S.nodes = reinterpret_cast<const float4 *>(nodes);
+    const sptx_bvh *dB;
+    if ((rc = upload(ctx, pool, bvhs.data(), (int64_t)bvhs.size(), &dB))) return rc;
+    S.bvhs = dB;
+    for (int a = 0; a < 3; ++a) {
+        S.wb_min[a] = instBounds[a];
+        S.wb_max[a] = instBounds[3 + a];
+    }
+    return SPTX_OK;
+}
+
 // SampledSpectrum::y() on the host (core/spectrum.h:415-421).
 static float host_y(const sptx_scene_desc *sc, const float *row, float scale) {
     float yy = 0.f;
@@ -583,6 +740,13 @@ extern "C" int sptx_upload_scene(sptx_ctx *ctx, const sptx_scene_desc *sc) {
             S.wb_min[i] = root.bmin[i];
             S.wb_max[i] = root.bmax[i];
         }
+    }
+
+    S.prim_ids = nullptr;
+    ctx->bvhBuildMs = 0.0;
+    if (ctx->deviceBvh) {
+        if ((rc = lbvh_build_scene(ctx, pool, S, sc))) return rc;
+        mark("device BVH build");
     }
 
     // ---- light selection (core/lightdistrib.cpp:48-66) ----

@@ -79,8 +79,9 @@ def merge_films_over_peers(ctx, dist=None, dst=0, pack=None, shape="reduce_scatt
     Returns the .dat planes on `dst` when `pack` = (width, height) is given (else None)."""
     if dist is None or not dist.is_initialized() or dist.get_world_size() == 1:
         return ctx.film_pack_dat(*pack) if pack is not None else None
-    handles = gather_handles(ctx.film_export(), dist)   # all renders of this rank are complete here
-    dist.barrier()
+    # film_export drains this rank's render stream, and the all_gather returns only once every rank
+    # has contributed its handle: when it completes, all films are complete (no separate barrier)
+    handles = gather_handles(ctx.film_export(), dist)
     planes = None
     if shape == "gather":
         if dist.get_rank() == dst:
