@@ -37,16 +37,19 @@ def l2_peak():
     return L2_PEAK
 
 
-def load(name):
+def load(name, device_bvh=False):
     ctx = capi.Context(0)
+    if device_bvh:
+        ctx.set_option("device_bvh", 1)
     sf = capi.SceneFile(capi.unpack_blob(os.path.join(GEN, name + ".sptx")))
     ctx.upload(sf)
     sf.close()
     return ctx
 
 
-def render_rate(name, w, h, spp, warm_spp):
-    ctx = load(name)
+def render_rate(name, w, h, spp, warm_spp, device_bvh=False):
+    ctx = load(name, device_bvh)
+    build_ms = ctx.bvh_build_ms()
     ctx.render(0, warm_spp)
     ctx.film_clear()
     ctx.reset_counters()
@@ -56,7 +59,8 @@ def render_rate(name, w, h, spp, warm_spp):
     ms = c["render_ms"]
     k = {n: round(c["kernel_ms"][i], 2) for i, n in enumerate(capi.KERNEL_NAMES[:6])}
     rays = c["closest_hit_rays"] + c["shadow_rays"]
-    return {"scene": name, "res": [w, h], "spp": spp, "render_ms": ms,
+    return {"scene": name, "res": [w, h], "spp": spp, "render_ms": ms, "bvh": "device LBVH" if device_bvh else "reference SAH (host)",
+            "bvh_build_ms": build_ms,
             "msamples_per_s": w * h * spp / ms * 1e-3, "kernel_ms": k,
             "rays_per_sample": rays / max(c["camera_rays"], 1),
             "mrays_per_s_traversal": rays / max(c["traverse_ms"], 1e-9) * 1e-3}
@@ -100,16 +104,22 @@ def c3(spp=256, cpu=True):
     return out
 
 
-def c4(n=1 << 24, n_cpu=1 << 20):
+def c1_device_bvh():
+    """C1 through a BVH built on the device (csrc/lbvh.cuh) instead of the reference's SAH tree."""
+    return render_rate("killeroo400", 400, 400, 64, 8, device_bvh=True)
+
+
+def c4(n=1 << 24, n_cpu=1 << 20, device_bvh=False):
     import torch
-    ctx = load("instanced_c4")
+    ctx = load("instanced_c4", device_bvh)
     blob = open(os.path.join(GEN, "instanced_c4.sptx"), "rb").read()
     hb = int(np.frombuffer(blob[8:16], "<u8")[0])
     pos = 16 + hb
     pos += (-pos) % 16
     b = np.frombuffer(blob[pos:pos + 24], "<f4")
     lo, hi = b[:3], b[3:6]
-    res = {"scene": "instanced_c4", "rays_per_batch": n, "batches": {}}
+    res = {"scene": "instanced_c4", "rays_per_batch": n, "batches": {},
+           "bvh": "device LBVH" if device_bvh else "reference SAH (host)", "bvh_build_ms": ctx.bvh_build_ms()}
     # coherent primary rays: the scene's own camera over a 4096x4096 sample grid
     g = np.random.Generator(np.random.Philox(key=7))
     cs = np.zeros((n, 5), np.float32)
@@ -177,5 +187,7 @@ if __name__ == "__main__":
     todo = sys.argv[1:] or ["c1", "c3", "c4"]
     out = {"hbm_peak_gbs": PEAK}
     for t in todo:
-        out[t] = {"c1": c1, "c3": c3, "c4": c4}[t]()
+        out[t] = {"c1": c1, "c3": c3, "c4": c4, "c1_lbvh": c1_device_bvh,
+                  "c4_lbvh": lambda: c4(n=1 << 22, n_cpu=0, device_bvh=True),
+                  "c4_small": lambda: c4(n=1 << 22, n_cpu=0)}[t]()
     print(json.dumps(out, indent=1))
