@@ -39,6 +39,9 @@
 #include "interaction.h"
 #include "light.h"
 #include "lights/diffuse.h"
+#include "lights/infinite.h"
+#include "mipmap.h"
+#include "sampling.h"
 #include "lights/point.h"
 #include "lowdiscrepancy.h"
 #include "material.h"
@@ -567,6 +570,7 @@ void FlatScene::Finish() {
     SPTX_SET(primes, n_primes, primes, 1)
     SPTX_SET(prime_sums, n_prime_sums, primeSums, 1)
     SPTX_SET(perms, n_perms, perms, 1)
+    SPTX_SET(env_floats, n_env_floats, envFloats, 1)
 #undef SPTX_SET
 }
 
@@ -582,8 +586,6 @@ bool FlattenScene(const Scene &scene, const Camera &camera, Sampler &sampler,
 
     // ---- lights: index = position in scene.lights (light selection and
     // GetAreaLight() identity both depend on it, src/core/integrator.cpp:85-106)
-    if (!scene.infiniteLights.empty())
-        return fail("infinite lights are outside the GPU hot path");
     for (size_t i = 0; i < scene.lights.size(); ++i)
         b.lightIndex[scene.lights[i].get()] = (int)i;
 
@@ -592,6 +594,7 @@ bool FlattenScene(const Scene &scene, const Camera &camera, Sampler &sampler,
     for (size_t i = 0; i < b.pending.size(); ++i)
         if (!b.AddAggregate(b.pending[i], false)) return fail(b.err);
 
+    int illumBasisRow = -1;  // first of the seven rgbIllum2Spect* rows, added with the first infinite light
     for (size_t i = 0; i < scene.lights.size(); ++i) {
         const Light *l = scene.lights[i].get();
         sptx_light fl;
@@ -614,10 +617,66 @@ bool FlattenScene(const Scene &scene, const Camera &camera, Sampler &sampler,
             fl.pos[0] = p->pLight.x;
             fl.pos[1] = p->pLight.y;
             fl.pos[2] = p->pLight.z;
+        } else if (auto *inf = dynamic_cast<const InfiniteAreaLight *>(l)) {
+            // InfiniteAreaLight (src/lights/infinite.cpp): the radiance map's finest level as
+            // the MIPMap holds it (resampled to powers of two, already scaled by L), the
+            // Distribution2D the constructor built, and the bounding sphere of Preprocess().
+            fl.type = SPTX_LIGHT_INFINITE;
+            fl.shape = (int)out->envFloats.size();
+            fl.area = inf->worldRadius;
+            fl.pos[0] = inf->worldCenter.x;
+            fl.pos[1] = inf->worldCenter.y;
+            fl.pos[2] = inf->worldCenter.z;
+            if (illumBasisRow < 0) {
+                illumBasisRow = b.AddSpectrum(SampledSpectrum::rgbIllum2SpectWhite);
+                b.AddSpectrum(SampledSpectrum::rgbIllum2SpectCyan);
+                b.AddSpectrum(SampledSpectrum::rgbIllum2SpectMagenta);
+                b.AddSpectrum(SampledSpectrum::rgbIllum2SpectYellow);
+                b.AddSpectrum(SampledSpectrum::rgbIllum2SpectRed);
+                b.AddSpectrum(SampledSpectrum::rgbIllum2SpectGreen);
+                b.AddSpectrum(SampledSpectrum::rgbIllum2SpectBlue);
+            }
+            fl.spectrum = illumBasisRow;
+            const MIPMap<RGBSpectrum> &mip = *inf->Lmap;
+            if (mip.wrapMode != ImageWrap::Repeat || mip.noFiltering)
+                return fail("infinite light map with a wrap mode / filter outside the GPU hot path");
+            const BlockedArray<RGBSpectrum> &lvl = *mip.pyramid[0];
+            const int W = lvl.uSize(), H = lvl.vSize();
+            const Distribution2D &d2 = *inf->distribution;
+            const int nv = d2.pMarginal->Count(), nu = d2.pConditionalV[0]->Count();
+            std::vector<float> &E = out->envFloats;
+            E.push_back((float)W);
+            E.push_back((float)H);
+            E.push_back((float)nu);
+            E.push_back((float)nv);
+            E.push_back(inf->Power().y());
+            E.push_back(0.f);
+            E.push_back(0.f);
+            E.push_back(0.f);
+            float m[16];
+            Builder::CopyMatrix(inf->LightToWorld.m, m);
+            E.insert(E.end(), m, m + 16);
+            Builder::CopyMatrix(inf->WorldToLight.m, m);
+            E.insert(E.end(), m, m + 16);
+            for (int v = 0; v < H; ++v)
+                for (int u = 0; u < W; ++u) {
+                    Float rgb[3];
+                    lvl(u, v).ToRGB(rgb);
+                    E.push_back(rgb[0]);
+                    E.push_back(rgb[1]);
+                    E.push_back(rgb[2]);
+                }
+            auto addDist = [&](const Distribution1D &d) {
+                E.insert(E.end(), d.func.begin(), d.func.end());
+                E.insert(E.end(), d.cdf.begin(), d.cdf.end());
+                E.push_back(d.funcInt);
+            };
+            addDist(*d2.pMarginal);
+            for (int v = 0; v < nv; ++v) addDist(*d2.pConditionalV[v]);
         } else
             return fail(
                 "light type is outside the GPU hot path (supported: "
-                "diffuse area lights on triangles/spheres, point)");
+                "diffuse area lights on triangles/spheres, point, infinite)");
         out->lights.push_back(fl);
     }
 

@@ -54,6 +54,7 @@ struct FlatScene {
     std::vector<float> lensElements, exitPupilBounds;
     std::vector<int32_t> primes, primeSums;
     std::vector<uint16_t> perms;
+    std::vector<float> envFloats;  // infinite lights' blocks (sptx_light)
     void Finish();  // points desc at the vectors
 };
 

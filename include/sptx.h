@@ -146,11 +146,19 @@ typedef struct sptx_material {
     int32_t material_id;
 } sptx_material;
 
-enum { SPTX_LIGHT_DIFFUSE_AREA = 0, SPTX_LIGHT_POINT = 1 };
+enum { SPTX_LIGHT_DIFFUSE_AREA = 0, SPTX_LIGHT_POINT = 1, SPTX_LIGHT_INFINITE = 2 };
 enum { SPTX_METADATA_NONE = 0, SPTX_METADATA_DEPTH = 1, SPTX_METADATA_MATERIAL = 2, SPTX_METADATA_MESH = 3,
        SPTX_METADATA_COORDINATES = 4 };
 
-/* DiffuseAreaLight (src/lights/diffuse.cpp) or PointLight (src/lights/point.cpp). */
+/* DiffuseAreaLight (src/lights/diffuse.cpp), PointLight (src/lights/point.cpp) or InfiniteAreaLight
+ * (src/lights/infinite.cpp).  For an infinite light `shape` is the offset (in floats) of its block in
+ * env_floats[], `spectrum` the first of the seven consecutive rows rgbIllum2Spect{White, Cyan,
+ * Magenta, Yellow, Red, Green, Blue} (src/core/spectrum.cpp:363-392), `area` = worldRadius and
+ * `pos` = worldCenter (InfiniteAreaLight::Preprocess).  Block layout (integers as float values):
+ *   [0] W [1] H of the radiance map's level 0 (MIPMap::pyramid[0]), [2] nu [3] nv of the sampling
+ *   distribution, [4] Power().y(), [5..8) unused, [8..24) LightToWorld.m, [24..40) WorldToLight.m,
+ *   W*H RGB texels (row v, column u), then Distribution2D: the marginal's func[nv], cdf[nv+1],
+ *   funcInt, then per row v: func[nu], cdf[nu+1], funcInt (src/core/sampling.h:55-150). */
 typedef struct sptx_light {
     int32_t type;
     int32_t shape_kind; /* SPTX_PRIM_TRIANGLE / SPTX_PRIM_SPHERE (area)      */
@@ -272,6 +280,9 @@ typedef struct sptx_scene_desc {
     int64_t n_primes;     const int32_t *primes;     /* Primes[0..n_dims)     */
     int64_t n_prime_sums; const int32_t *prime_sums; /* PrimeSums[0..n_dims)  */
     int64_t n_perms;      const uint16_t *perms; /* radicalInversePermutations */
+    /* Infinite lights' blocks (see sptx_light).  Last member: scene files written before it existed
+     * are still read (sptx_scene_load fills it with 0 / NULL). */
+    int64_t n_env_floats; const float *env_floats;
 } sptx_scene_desc;
 
 /* ---- ray batches (parity test #1 and the traversal benchmark) ----------- */

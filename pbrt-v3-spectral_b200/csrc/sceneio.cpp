@@ -42,6 +42,7 @@ std::vector<Section> sections(sptx_scene_desc *d) {
     SEC(primes, d->n_primes, sizeof(int32_t));
     SEC(prime_sums, d->n_prime_sums, sizeof(int32_t));
     SEC(perms, d->n_perms, sizeof(uint16_t));
+    SEC(env_floats, d->n_env_floats, sizeof(float));
 #undef SEC
     return s;
 }
@@ -109,8 +110,10 @@ extern "C" int sptx_scene_load(const char *path, sptx_scene_desc **out) {
     fclose(f);
     uint64_t headerBytes = 0;
     if (ok && size >= 16) memcpy(&headerBytes, blob + 8, 8);
-    if (!ok || size < (long)(16 + sizeof(sptx_scene_desc)) || memcmp(blob, kMagic, 8) != 0 ||
-        headerBytes != sizeof(sptx_scene_desc)) {
+    // (files written before the env_floats member existed have a descriptor 16 bytes shorter)
+    const uint64_t kOldHeader = sizeof(sptx_scene_desc) - 16;
+    if (!ok || size < (long)(16 + kOldHeader) || memcmp(blob, kMagic, 8) != 0 ||
+        (headerBytes != sizeof(sptx_scene_desc) && headerBytes != kOldHeader)) {
         free(blob);
         g_io_error = std::string("not a flattened-scene file of this ABI: ") + path;
         return SPTX_EINVAL;
@@ -118,8 +121,9 @@ extern "C" int sptx_scene_load(const char *path, sptx_scene_desc **out) {
     // Move the descriptor to the front of the allocation (16-byte header is dropped).
     sptx_scene_desc *d = (sptx_scene_desc *)blob;
     sptx_scene_desc tmp;
-    memcpy(&tmp, blob + 16, sizeof(tmp));
-    size_t pos = 16 + sizeof(tmp);
+    memset(&tmp, 0, sizeof(tmp));
+    memcpy(&tmp, blob + 16, (size_t)headerBytes);
+    size_t pos = 16 + (size_t)headerBytes;
     if (pos % 16) pos += 16 - pos % 16;
     // the counts come from the file: none may be negative (a negative count would wrap the size
     // arithmetic below past the truncation check)
@@ -127,7 +131,7 @@ extern "C" int sptx_scene_load(const char *path, sptx_scene_desc **out) {
                               tmp.n_positions, tmp.n_normals, tmp.n_tangents, tmp.n_uvs, tmp.n_spheres,
                               tmp.n_instances, tmp.n_materials, tmp.n_lobes, tmp.n_spectra, tmp.n_lights,
                               tmp.n_lens_floats, tmp.n_pupil_floats, tmp.n_primes, tmp.n_prime_sums,
-                              tmp.n_perms};
+                              tmp.n_perms, tmp.n_env_floats};
     for (int64_t c : counts)
         if (c < 0 || c > (int64_t)size) {  // every element is at least one byte
             free(blob);
