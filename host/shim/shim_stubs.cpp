@@ -12,6 +12,7 @@
 // (src/tests/analytic_scenes.cpp:281) can still be read back by tests.
 #include <glog/logging.h>
 
+#include <cmath>
 #include <cstdio>
 #include <memory>
 #include <string>
@@ -60,10 +61,56 @@ PtexTexture<Spectrum> *CreatePtexSpectrumTexture(const Transform &,
     return nullptr;
 }
 
-std::unique_ptr<RGBSpectrum[]> ReadImage(const std::string &name, Point2i *) {
-    Error("ReadImage(\"%s\"): image reading is not built into this in-place build.",
-          name.c_str());
-    return nullptr;
+// PFM only (what the infinite-light fixtures use): "PF" / "Pf", width, height, scale (negative =
+// little endian), then float32 scanlines stored bottom to top, flipped to top-down -- the
+// semantics of the reference's ReadImagePFM (src/core/imageio.cpp:350-440).  Other formats need
+// src/core/imageio.cpp (lodepng / OpenEXR), which this in-place build leaves out.
+std::unique_ptr<RGBSpectrum[]> ReadImage(const std::string &name, Point2i *res) {
+    const size_t dot = name.rfind('.');
+    if (dot == std::string::npos || name.substr(dot) != ".pfm") {
+        Error("ReadImage(\"%s\"): only .pfm image reading is built into this in-place build.", name.c_str());
+        return nullptr;
+    }
+    FILE *fp = fopen(name.c_str(), "rb");
+    if (!fp) {
+        Error("Unable to open \"%s\".", name.c_str());
+        return nullptr;
+    }
+    char tag[8] = {0};
+    int w = 0, h = 0;
+    float scale = 0.f;
+    if (fscanf(fp, "%7s %d %d %f", tag, &w, &h, &scale) != 4 || w <= 0 || h <= 0 ||
+        (std::string(tag) != "PF" && std::string(tag) != "Pf")) {
+        fclose(fp);
+        Error("Error reading PFM file \"%s\"", name.c_str());
+        return nullptr;
+    }
+    fgetc(fp);  // the single whitespace byte that ends the header
+    const int nc = std::string(tag) == "PF" ? 3 : 1;
+    std::vector<float> data((size_t)nc * w * h);
+    const bool ok = fread(data.data(), sizeof(float), data.size(), fp) == data.size();
+    fclose(fp);
+    if (!ok) {
+        Error("Error reading PFM file \"%s\"", name.c_str());
+        return nullptr;
+    }
+    if (scale > 0)  // big-endian file on a little-endian host
+        for (float &f : data) {
+            unsigned char *b = reinterpret_cast<unsigned char *>(&f);
+            std::swap(b[0], b[3]);
+            std::swap(b[1], b[2]);
+        }
+    const float s = std::abs(scale);
+    std::unique_ptr<RGBSpectrum[]> rgb(new RGBSpectrum[(size_t)w * h]);
+    for (int y = 0; y < h; ++y)
+        for (int x = 0; x < w; ++x) {
+            const float *src = &data[(size_t)nc * ((size_t)(h - 1 - y) * w + x)];  // flip in y
+            Float c[3] = {s * src[0], s * src[nc == 3 ? 1 : 0], s * src[nc == 3 ? 2 : 0]};
+            rgb[(size_t)y * w + x] = RGBSpectrum::FromRGB(c);
+        }
+    res->x = w;
+    res->y = h;
+    return rgb;
 }
 
 RGBSpectrum *ReadImageEXR(const std::string &name, int *, int *, Bounds2i *,

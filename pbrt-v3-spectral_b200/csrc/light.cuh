@@ -5,6 +5,7 @@
 // core/sampling.h:55-109 (Distribution1D), core/lightdistrib.cpp.
 #pragma once
 #include "bsdf_eval.cuh"
+#include "sampler.cuh"  // mod_i
 
 namespace sptx {
 
@@ -17,6 +18,13 @@ struct RefPoint {
 struct LightPoint {  // Interaction returned by Shape::Sample
     V3 p, pError, n;
 };
+
+// SphericalTheta / SphericalPhi, core/geometry.h:1485-1492.
+SPTX_DEV float spherical_theta(V3 v) { return acosf(clampf(v.z, -1.f, 1.f)); }
+SPTX_DEV float spherical_phi(V3 v) {
+    const float p = atan2f(v.y, v.x);
+    return (p < 0) ? (p + 2 * kPi) : p;
+}
 
 SPTX_DEV V3 uniform_sample_sphere(V2 u) {
     float z = 1.f - 2.f * u.x;
@@ -167,9 +175,154 @@ SPTX_DEV float sphere_pdf(const DScene &S, int shape, const RefPoint &ref, V3 wi
 
 // Light::Pdf_Li (DiffuseAreaLight: shape->Pdf; PointLight: 0).
 SPTX_NOINL float light_pdf_li(const DScene &S, const sptx_light &L, const RefPoint &ref, V3 wi) {
+    if (L.type == SPTX_LIGHT_INFINITE) {
+        // InfiniteAreaLight::Pdf_Li, lights/infinite.cpp:125-133; Distribution2D::Pdf, sampling.h:135-142
+        const float *base = S.env + L.shape;
+        const int W = (int)__ldg(base), H = (int)__ldg(base + 1), nu = (int)__ldg(base + 2), nv = (int)__ldg(base + 3);
+        const V3 w = xf_vec(base + 24, wi);
+        const float theta = spherical_theta(w), phi = spherical_phi(w);
+        const float sinTheta = sinf(theta);
+        if (sinTheta == 0) return 0.f;
+        const float *marginal = base + 40 + 3 * (size_t)W * H;
+        const int iu = min(max((int)(phi * kInv2Pi * (float)nu), 0), nu - 1);
+        const int iv = min(max((int)(theta * kInvPi * (float)nv), 0), nv - 1);
+        const float *row = marginal + (2 * nv + 2) + (size_t)iv * (2 * nu + 2);
+        return (__ldg(row + iu) / __ldg(marginal + 2 * nv + 1)) / (2 * kPi * kPi * sinTheta);
+    }
     if (L.type != SPTX_LIGHT_DIFFUSE_AREA) return 0.f;
     if (L.shape_kind == SPTX_PRIM_SPHERE) return sphere_pdf(S, L.shape, ref, wi, L.area);
     return shape_pdf_generic(S, SPTX_PRIM_TRIANGLE, L.shape, ref, wi, L.area);
+}
+
+// ---- InfiniteAreaLight (lights/infinite.cpp) ---------------------------------------------------
+// Radiance in a direction = the RGB map looked up bilinearly at its finest level
+// (MIPMap::Lookup(st, width = 0) -> triangle(0, st), core/mipmap.h:247-287, wrap mode Repeat),
+// converted by SampledSpectrum::FromRGB(rgb, Illuminant) (core/spectrum.cpp:135-168): up to three
+// of the seven basis spectra with scalar weights, times .86445, clamped at zero.  A radiance value
+// is therefore carried as three (row, weight) pairs and evaluated per bin where it is consumed.
+struct EnvRgb {
+    int row[3];
+    float w[3];
+};
+struct EnvMap {  // view of one light's block in DScene::env
+    const float *base;
+    int W, H, nu, nv;
+    SPTX_DEV const float *l2w() const { return base + 8; }
+    SPTX_DEV const float *w2l() const { return base + 24; }
+    SPTX_DEV const float *texels() const { return base + 40; }
+    SPTX_DEV const float *marginal() const { return texels() + 3 * (size_t)W * H; }
+    SPTX_DEV const float *row(int v) const { return marginal() + (2 * nv + 2) + (size_t)v * (2 * nu + 2); }
+};
+SPTX_DEV EnvMap env_map(const DScene &S, const sptx_light &L) {
+    EnvMap m;
+    m.base = S.env + L.shape;
+    m.W = (int)__ldg(m.base);
+    m.H = (int)__ldg(m.base + 1);
+    m.nu = (int)__ldg(m.base + 2);
+    m.nv = (int)__ldg(m.base + 3);
+    return m;
+}
+SPTX_DEV void env_texel(const EnvMap &m, int s, int t, float rgb[3]) {
+    s = mod_i(s, m.W);  // ImageWrap::Repeat
+    t = mod_i(t, m.H);
+    const float *p = m.texels() + 3 * ((size_t)t * m.W + s);
+    rgb[0] = __ldg(p);
+    rgb[1] = __ldg(p + 1);
+    rgb[2] = __ldg(p + 2);
+}
+// FromRGB(rgb, Illuminant) as (row, weight) pairs; basis rows: White, Cyan, Magenta, Yellow, Red, Green, Blue.
+SPTX_DEV EnvRgb env_from_rgb(const float rgb[3], int basis) {
+    enum { W = 0, C = 1, M = 2, Y = 3, R = 4, G = 5, B = 6 };
+    EnvRgb e;
+    const float r = rgb[0], g = rgb[1], b = rgb[2];
+    if (r <= g && r <= b) {
+        e.row[0] = W, e.w[0] = r;
+        if (g <= b) {
+            e.row[1] = C, e.w[1] = g - r;
+            e.row[2] = B, e.w[2] = b - g;
+        } else {
+            e.row[1] = C, e.w[1] = b - r;
+            e.row[2] = G, e.w[2] = g - b;
+        }
+    } else if (g <= r && g <= b) {
+        e.row[0] = W, e.w[0] = g;
+        if (r <= b) {
+            e.row[1] = M, e.w[1] = r - g;
+            e.row[2] = B, e.w[2] = b - r;
+        } else {
+            e.row[1] = M, e.w[1] = b - g;
+            e.row[2] = R, e.w[2] = r - b;
+        }
+    } else {
+        e.row[0] = W, e.w[0] = b;
+        if (r <= g) {
+            e.row[1] = Y, e.w[1] = r - b;
+            e.row[2] = G, e.w[2] = g - r;
+        } else {
+            e.row[1] = Y, e.w[1] = g - b;
+            e.row[2] = R, e.w[2] = r - g;
+        }
+    }
+    for (int k = 0; k < 3; ++k) e.row[k] += basis;
+    return e;
+}
+// One bin of FromRGB: r = 0 + w0 B0; r += w1 B1; r += w2 B2; r *= .86445f; Clamp(0, inf).
+SPTX_DEV float env_bin1(float b0, float b1, float b2, const EnvRgb &e) {
+    float r = e.w[0] * b0;
+    r = r + e.w[1] * b1;
+    r = r + e.w[2] * b2;
+    r = r * .86445f;
+    return (r < 0.f) ? 0.f : r;  // Clamp(val, 0, Infinity)
+}
+SPTX_DEV float env_bin(const DScene &S, const EnvRgb &e, int b) {
+    return env_bin1(spec(S, e.row[0], b), spec(S, e.row[1], b), spec(S, e.row[2], b), e);
+}
+SPTX_DEV float4 env_bin4(const DScene &S, const EnvRgb &e, int c) {
+    const float4 b0 = spec4(S, e.row[0], c), b1 = spec4(S, e.row[1], c), b2 = spec4(S, e.row[2], c);
+    return make_float4(env_bin1(b0.x, b1.x, b2.x, e), env_bin1(b0.y, b1.y, b2.y, e), env_bin1(b0.z, b1.z, b2.z, e),
+                       c < 7 ? env_bin1(b0.w, b1.w, b2.w, e) : 0.f);
+}
+// Lmap->Lookup(st) with width 0: bilinear at level 0.
+SPTX_DEV EnvRgb env_lookup(const DScene &S, const sptx_light &L, const EnvMap &m, float s01, float t01) {
+    const float s = s01 * (float)m.W - 0.5f, t = t01 * (float)m.H - 0.5f;
+    const float fs = floorf(s), ft = floorf(t);
+    const int s0 = (int)fs, t0 = (int)ft;
+    const float ds = s - (float)s0, dt = t - (float)t0;
+    float a[3], b[3], c[3], d[3], rgb[3];
+    env_texel(m, s0, t0, a);
+    env_texel(m, s0, t0 + 1, b);
+    env_texel(m, s0 + 1, t0, c);
+    env_texel(m, s0 + 1, t0 + 1, d);
+    const float wa = (1 - ds) * (1 - dt), wb = (1 - ds) * dt, wc = ds * (1 - dt), wd = ds * dt;
+    for (int k = 0; k < 3; ++k) rgb[k] = wa * a[k] + wb * b[k] + wc * c[k] + wd * d[k];
+    return env_from_rgb(rgb, L.spectrum);
+}
+// InfiniteAreaLight::Le(ray), lights/infinite.cpp:92-96.
+SPTX_DEV EnvRgb env_le(const DScene &S, const sptx_light &L, V3 dir) {
+    const EnvMap m = env_map(S, L);
+    const V3 w = normalize(xf_vec(m.w2l(), dir));
+    return env_lookup(S, L, m, spherical_phi(w) * kInv2Pi, spherical_theta(w) * kInvPi);
+}
+// Distribution1D::SampleContinuous, core/sampling.h:72-89, on a {func[n], cdf[n+1], funcInt} block.
+SPTX_DEV float dist1d_sample(const float *d, int n, float u, float *pdf, int *off) {
+    const float *func = d, *cdf = d + n;
+    int first = 0, len = n + 1;  // FindInterval(cdf.size(), cdf[i] <= u)
+    while (len > 0) {
+        int half = len >> 1, middle = first + half;
+        if (__ldg(cdf + middle) <= u) {
+            first = middle + 1;
+            len -= half + 1;
+        } else
+            len = half;
+    }
+    const int offset = min(max(first - 1, 0), n - 1);
+    if (off) *off = offset;
+    float du = u - __ldg(cdf + offset);
+    const float span = __ldg(cdf + offset + 1) - __ldg(cdf + offset);
+    if (span > 0) du /= span;
+    const float funcInt = __ldg(d + 2 * n + 1);
+    if (pdf) *pdf = (funcInt > 0) ? __ldg(func + offset) / funcInt : 0.f;
+    return ((float)offset + du) / (float)n;
 }
 
 // Result of Light::Sample_Li.  The radiance is row `spectrum` scaled per bin:
@@ -181,11 +334,27 @@ struct LiSample {
     int spectrum;   // row
     float divisor;  // 0: Li[b] = row[b]; else Li[b] = row[b] / divisor
     LightPoint lp;  // sampled point (shadow-ray target)
+    bool isEnv;     // infinite light: Li = env (three basis rows with weights) instead of a row
+    EnvRgb env;
 };
 
 SPTX_DEV float li_bin(const DScene &S, const LiSample &ls, int b) {
+    if (ls.isEnv) return env_bin(S, ls.env, b);
     float v = spec(S, ls.spectrum, b);
     return ls.divisor != 0.f ? v / ls.divisor : v;
+}
+
+// Four consecutive bins of the sampled radiance (the thread-per-path form of li_bin).
+SPTX_DEV float4 li4(const DScene &S, const LiSample &ls, int c) {
+    if (ls.isEnv) return env_bin4(S, ls.env, c);
+    float4 li = spec4(S, ls.spectrum, c);
+    if (ls.divisor != 0.f) {
+        li.x = li.x / ls.divisor;
+        li.y = li.y / ls.divisor;
+        li.z = li.z / ls.divisor;
+        li.w = padless(c, li.w, ls.divisor);
+    }
+    return li;
 }
 
 SPTX_NOINL LiSample light_sample_li(const DScene &S, const sptx_light &L, const RefPoint &ref, V2 u) {
@@ -195,6 +364,31 @@ SPTX_NOINL LiSample light_sample_li(const DScene &S, const sptx_light &L, const 
     r.black = true;
     r.pdf = 0.f;
     r.wi = mk(0, 0, 0);
+    r.isEnv = false;
+    if (L.type == SPTX_LIGHT_INFINITE) {
+        // InfiniteAreaLight::Sample_Li, lights/infinite.cpp:98-123
+        const EnvMap m = env_map(S, L);
+        float pdfs[2];
+        int v;
+        const float d1 = dist1d_sample(m.marginal(), m.nv, u.y, &pdfs[1], &v);
+        const float d0 = dist1d_sample(m.row(v), m.nu, u.x, &pdfs[0], nullptr);
+        const float mapPdf = pdfs[0] * pdfs[1];
+        if (mapPdf == 0) return r;
+        const float theta = d1 * kPi, phi = d0 * 2 * kPi;
+        const float cosTheta = cosf(theta), sinTheta = sinf(theta);
+        const float sinPhi = sinf(phi), cosPhi = cosf(phi);
+        r.wi = xf_vec(m.l2w(), mk(sinTheta * cosPhi, sinTheta * sinPhi, cosTheta));
+        r.pdf = mapPdf / (2 * kPi * kPi * sinTheta);
+        if (sinTheta == 0) r.pdf = 0.f;
+        // VisibilityTester(ref, Interaction(ref.p + wi * (2 * worldRadius)))
+        r.lp.p = ref.p + r.wi * (2 * L.area);
+        r.lp.pError = mk(0, 0, 0);
+        r.lp.n = mk(0, 0, 0);
+        r.isEnv = true;
+        r.env = env_lookup(S, L, m, d0, d1);
+        r.black = false;  // blackness is checked per bin by the caller
+        return r;
+    }
     if (L.type == SPTX_LIGHT_POINT) {
         V3 pl = mk(L.pos[0], L.pos[1], L.pos[2]);
         r.wi = normalize(pl - ref.p);

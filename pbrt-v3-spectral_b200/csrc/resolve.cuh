@@ -22,7 +22,10 @@ k_mis(DScene S, PathArrays A, DeviceCounters *cnt) {
         Ray r{mk(ma.x, ma.y, ma.z), mk(ma.w, mb.x, mb.y), kInf};
         HitRec h;
         bool useB = false;
-        if (scene_intersect<COUNT>(S, r, &h, &tc)) {
+        if (!scene_intersect<COUNT>(S, r, &h, &tc)) {
+            // the sampled ray leaves the scene: an infinite light's Le(ray) (core/integrator.cpp:204-205)
+            useB = S.lights[lightNum].type == SPTX_LIGHT_INFINITE;
+        } else {
             if (S.prims[h.prim].light == lightNum) {
                 const sptx_light &Lt = S.lights[lightNum];
                 if (Lt.two_sided)

@@ -31,6 +31,9 @@ struct DScene {
     const float *spectra;
     const sptx_light *lights;
     int n_lights;
+    const float *env;       // infinite lights' blocks (sptx_light), or NULL
+    int n_infinite;         // number of infinite lights; their indices in lights[]:
+    int infinite[4];
     int n_bvhs;
     // light selection
     int light_strategy;      // effective (uniform when n_lights == 1)

@@ -174,6 +174,11 @@ SPTX_DEV void li_serial(const DScene &S, const SerialParams &P, SMP &rng, Ray ra
             if (Lt.two_sided || dot(it.n, -ray.d) > 0)
                 for (int b = 0; b < SPTX_NBINS; ++b) L[b] += beta[b] * spec(S, Lt.spectrum, b);
         }
+        if ((bounces == 0 || specularBounce) && !found)  // the infinite lights' Le(ray), path.cpp:96-99
+            for (int j = 0; j < S.n_infinite; ++j) {
+                const EnvRgb e = env_le(S, S.lights[S.infinite[j]], ray.d);
+                for (int b = 0; b < SPTX_NBINS; ++b) L[b] += beta[b] * env_bin(S, e, b);
+            }
         if (!haveIsect || bounces >= P.maxDepth) break;
         Bsdf bs;
         bsdf_init(S, it, &bs);
@@ -248,8 +253,10 @@ SPTX_DEV void li_serial(const DScene &S, const SerialParams &P, SMP &rng, Ray ra
                                 HitRec mh;
                                 ++*nClosest;
                                 bool useB = false;
-                                if (scene_intersect<false>(S, mr, &mh, &tc) &&
-                                    S.prims[mh.prim].light == lightNum) {
+                                const bool mFound = scene_intersect<false>(S, mr, &mh, &tc);
+                                if (!mFound)
+                                    useB = Lt.type == SPTX_LIGHT_INFINITE;  // Li = light.Le(ray)
+                                else if (S.prims[mh.prim].light == lightNum) {
                                     if (Lt.two_sided)
                                         useB = true;
                                     else {
@@ -258,7 +265,11 @@ SPTX_DEV void li_serial(const DScene &S, const SerialParams &P, SMP &rng, Ray ra
                                             useB = dot(li.n, -mr.d) > 0;
                                     }
                                 }
-                                if (useB)
+                                if (useB && Lt.type == SPTX_LIGHT_INFINITE) {
+                                    const EnvRgb e = env_le(S, Lt, wi2);
+                                    for (int b = 0; b < SPTX_NBINS; ++b)
+                                        Ld[b] += (fsum_bin(S, f2, b) * ad2) * env_bin(S, e, b) * weight / sPdf;
+                                } else if (useB)
                                     for (int b = 0; b < SPTX_NBINS; ++b)
                                         Ld[b] += (fsum_bin(S, f2, b) * ad2) * spec(S, Lt.spectrum, b) * weight / sPdf;
                             }

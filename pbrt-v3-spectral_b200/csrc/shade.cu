@@ -48,7 +48,8 @@ int launch_shade(cudaStream_t stream, int smCount, int64_t nPaths, const DScene 
     const int grid = (int)std::min<int64_t>((nPaths + kShadeBlock - 1) / kShadeBlock,
                                             (int64_t)smCount * kShadeBlocksPerSM);
     int launches = 1;
-    k_shade_miss<<<R.nBands > 1 ? std::max(1, std::min(grid, smCount * 4)) : 1, 256, 0, stream>>>(A, R, cnt);
+    // (class 0 has work only with bands or infinite lights; dS says which, the grid is sized for either)
+    k_shade_miss<<<std::max(1, std::min(grid, smCount * 4)), 256, 0, stream>>>(dS, A, R, betaIn, cnt);
     for (int cls = 1; cls < kShadeClasses; ++cls) {
         switch (plan.variant[cls]) {
         case 0: launch_variant<0>(stream, grid, dS, dH, A, R, qi, betaIn, cls, cnt); break;

@@ -208,13 +208,7 @@ k_shade(const DScene *__restrict__ Sp, const DSampler *__restrict__ Hp, PathArra
             const Row4 fa = row4(A.fa, i);
             bool fNon = false, liNon = false;
             for (int c = 0; c < 8; ++c) {
-                float4 fv = fsum4<LOBES>(S, f, c), li = spec4(S, ls.spectrum, c);
-                if (ls.divisor != 0.f) {
-                    li.x = li.x / ls.divisor;
-                    li.y = li.y / ls.divisor;
-                    li.z = li.z / ls.divisor;
-                    li.w = padless(c, li.w, ls.divisor);
-                }
+                float4 fv = fsum4<LOBES>(S, f, c), li = li4(S, ls, c);
                 fv.x *= ad;
                 fv.y *= ad;
                 fv.z *= ad;
@@ -257,12 +251,17 @@ k_shade(const DScene *__restrict__ Sp, const DSampler *__restrict__ Hp, PathArra
                 }
                 if (!skip) {
                     const float ad = absdot(misD, it.ns);
-                    const int leRow = S.lights[lightNum].spectrum;
+                    const sptx_light &Lm = S.lights[lightNum];
+                    const int leRow = Lm.spectrum;
+                    // an infinite light: Li = Le(ray) if the sampled ray leaves the scene (K4a decides)
+                    const bool envLight = Lm.type == SPTX_LIGHT_INFINITE;
+                    EnvRgb envLe;
+                    if (envLight) envLe = env_le(S, Lm, misD);
                     const Row4 fb = row4(A.fb, i);
                     bool fNon = false;
                     for (int c = 0; c < 8; ++c) {
                         float4 fv = fsum4<LOBES>(S, f, c);
-                        const float4 le = spec4(S, leRow, c);
+                        const float4 le = envLight ? env_bin4(S, envLe, c) : spec4(S, leRow, c);
                         fv.x *= ad;
                         fv.y *= ad;
                         fv.z *= ad;
@@ -366,16 +365,38 @@ k_shade(const DScene *__restrict__ Sp, const DSampler *__restrict__ Hp, PathArra
     if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&cnt->vertices, (unsigned long long)n);
 }
 
-// Class 0: paths whose ray left the scene.  PathIntegrator::Li ends them (there is no infinite
-// light on this path); with SpectralPathIntegrator bands the next band still needs the sampler
-// dimension the path stopped at.
-__global__ void k_shade_miss(PathArrays A, RenderParams R, DeviceCounters *cnt) {
+// Class 0: paths whose ray left the scene.  PathIntegrator::Li adds the infinite lights' emission
+// (camera rays and rays leaving a specular bounce) and ends them; with SpectralPathIntegrator bands
+// the next band still needs the sampler dimension the path stopped at.
+__global__ void k_shade_miss(const DScene *__restrict__ Sp, PathArrays A, RenderParams R, int betaIn,
+                             DeviceCounters *cnt) {
+    const DScene &S = *Sp;
     const int n = A.counters[kClassCounter0];
-    if (R.nBands > 1)
+    if (R.nBands > 1 || S.n_infinite > 0)
         for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
             const int i = A.qc[k];
             const uint32_t info = A.info[i];
-            A.info[i] = pack_info((int)(info & 0xffu), 0, (int)(info >> 16));
+            const int bounces = (int)(info & 0xffu);
+            const bool specularBounce = ((info >> 8) & 1u) != 0;
+            if (S.n_infinite > 0 && (bounces == 0 || specularBounce)) {
+                // L += beta * light->Le(ray) over scene.infiniteLights (integrators/path.cpp:96-99)
+                const float4 ra = A.rayA[i], rb = A.rayB[i];
+                const V3 d = mk(ra.w, rb.x, rb.y);
+                const Row4 Lr = row4(A.L, i), br = row4(A.beta[betaIn], i);
+                for (int j = 0; j < S.n_infinite; ++j) {
+                    const EnvRgb e = env_le(S, S.lights[S.infinite[j]], d);
+                    for (int c = 0; c < 8; ++c) {
+                        float4 l = Lr.ld(c);
+                        const float4 b = br.ldro(c), le = env_bin4(S, e, c);
+                        l.x += b.x * le.x;
+                        l.y += b.y * le.y;
+                        l.z += b.z * le.z;
+                        l.w += b.w * le.w;
+                        Lr.st(c, l);
+                    }
+                }
+            }
+            if (R.nBands > 1) A.info[i] = pack_info(bounces, 0, (int)(info >> 16));
         }
     if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&cnt->vertices, (unsigned long long)n);
 }

@@ -442,6 +442,17 @@ static int validate_scene(sptx_ctx *ctx, const sptx_scene_desc *sc) {
                 REQ(l.shape >= 0 && l.shape < sc->n_spheres, "light sphere out of range");
             else
                 return fail(ctx, SPTX_EUNSUPPORTED, "sptx_upload_scene: area light shape kind");
+        } else if (l.type == SPTX_LIGHT_INFINITE) {
+            // the block header, the two matrices, the texels and the distribution must lie inside env_floats
+            REQ(sc->env_floats && l.shape >= 0 && (int64_t)l.shape + 40 <= sc->n_env_floats, "infinite light block");
+            const float *e = sc->env_floats + l.shape;
+            const int64_t W = (int64_t)e[0], H = (int64_t)e[1], nu = (int64_t)e[2], nv = (int64_t)e[3];
+            REQ(W >= 1 && H >= 1 && nu >= 1 && nv >= 1 && W <= 65536 && H <= 65536 && nu <= 131072 && nv <= 131072,
+                "infinite light map size");
+            REQ((int64_t)l.shape + 40 + 3 * W * H + (2 * nv + 2) + nv * (2 * nu + 2) <= sc->n_env_floats,
+                "infinite light block truncated");
+            REQ(l.spectrum + 7 <= sc->n_spectra, "infinite light without its seven RGB basis rows");
+            REQ(l.area > 0, "infinite light without a world radius");
         } else if (l.type != SPTX_LIGHT_POINT)
             return fail(ctx, SPTX_EUNSUPPORTED, "sptx_upload_scene: light type %d", l.type);
     }
@@ -720,6 +731,14 @@ extern "C" int sptx_upload_scene(sptx_ctx *ctx, const sptx_scene_desc *sc) {
     if ((rc = upload(ctx, pool, sc->spectra, SPTX_SPECTRUM_STRIDE * sc->n_spectra, &S.spectra))) return rc;
     if ((rc = upload(ctx, pool, sc->lights, sc->n_lights, &S.lights))) return rc;
     S.n_lights = (int)sc->n_lights;
+    if ((rc = upload(ctx, pool, sc->env_floats, sc->n_env_floats, &S.env))) return rc;
+    S.n_infinite = 0;
+    for (int64_t i = 0; i < sc->n_lights; ++i)
+        if (sc->lights[i].type == SPTX_LIGHT_INFINITE) {
+            if (S.n_infinite == 4)
+                return fail(ctx, SPTX_EUNSUPPORTED, "sptx_upload_scene: more than 4 infinite lights");
+            S.infinite[S.n_infinite++] = (int)i;
+        }
     S.n_bvhs = (int)sc->n_bvhs;
     for (int i = 0; i < SPTX_SPECTRUM_STRIDE; ++i) S.cie_y[i] = i < SPTX_NBINS ? sc->cie_y[i] : 0.f;
     S.y_scale_num = (float)(705 - 395);  // sampledLambdaEnd - sampledLambdaStart
@@ -765,7 +784,9 @@ extern "C" int sptx_upload_scene(sptx_ctx *ctx, const sptx_scene_desc *sc) {
         std::vector<float> tab((size_t)2 * nL + 1, 0.f);
         for (int j = 0; j < nL; ++j) {
             float v = 1.f;
-            if (strategy == SPTX_LIGHTS_POWER) {
+            if (strategy == SPTX_LIGHTS_POWER && sc->lights[j].type == SPTX_LIGHT_INFINITE)
+                v = sc->env_floats[sc->lights[j].shape + 4];  // InfiniteAreaLight::Power().y(), from the flattener
+            else if (strategy == SPTX_LIGHTS_POWER) {
                 const sptx_light &l = sc->lights[j];
                 const float *row = sc->spectra + (size_t)l.spectrum * SPTX_SPECTRUM_STRIDE;
                 float tmp[SPTX_NBINS];

@@ -7,6 +7,7 @@ names:  cornell       C2: spectral Cornell box (diffuse + glass + metal), perspe
         cornell_lens  C3: the same scene through Camera "realistic" (double-Gauss lens)
         instanced     C4: N x N displaced grid mesh, instanced on a lattice
         zoo           one of every supported material / shape / light / camera feature (parity)
+        envbox        open scene under Light "infinite" (env=const | env=map), SURVEY 8(f) rank 3
         furnace_point / furnace_area   the known-answer scenes of the reference's
                       src/tests/analytic_scenes.cpp:68-165 written as scene files
 keys:   res=<w>[x<h>] spp=<n> maxdepth=<n> strategy=<uniform|power|spatial> sampler=<halton|random>
@@ -175,6 +176,49 @@ def uber_box(opts, out):
     return header(opts, cam, os.path.splitext(os.path.basename(out))[0]) + uber_world()
 
 
+def write_pfm(path, img):
+    """img [H][W][3] float32, row 0 = top; PFM stores scanlines bottom to top."""
+    h, w, _ = img.shape
+    with open(path, "wb") as f:
+        f.write(f"PF\n{w} {h}\n-1.0\n".encode())
+        f.write(np.ascontiguousarray(img[::-1].astype("<f4")).tobytes())
+
+
+def envbox(opts, out):
+    """Open scene under an InfiniteAreaLight (src/lights/infinite.cpp): a floor, a matte, a glass and
+    a metal sphere and a small area light, lit by a constant sky (env=const) or by a procedural
+    12 x 6 lat-long map (env=map; not a power of two, so the MIPMap resamples it) with a sun."""
+    name = os.path.splitext(os.path.basename(out))[0]
+    cam = 'LookAt 0 1.2 4.2  0 -.2 0  0 1 0\nCamera "perspective" "float fov" [42]'
+    s = header(opts, cam, name) + "WorldBegin\n"
+    s += "AttributeBegin\n  Rotate -90 1 0 0\n  Rotate 25 0 0 1\n"
+    if opts.get("env", "const") == "map":
+        w, h = 12, 6
+        v, u = np.meshgrid((np.arange(h) + .5) / h, (np.arange(w) + .5) / w, indexing="ij")
+        img = np.zeros((h, w, 3), np.float32)
+        img[..., 0] = .25 + .5 * u                     # horizon colours vary with azimuth
+        img[..., 1] = .35 + .3 * np.sin(3.1 * u) ** 2
+        img[..., 2] = .9 - .6 * v                      # bluer towards the zenith
+        img[v > .55] *= .15                            # dark ground half
+        img[1, 3] = (40., 36., 28.)                    # a sun
+        write_pfm(os.path.join(os.path.dirname(os.path.abspath(out)), name + "_env.pfm"), img)
+        s += f'  LightSource "infinite" "string mapname" "{name}_env.pfm" "rgb L" [1.5 1.5 1.5]\n'
+    else:
+        s += '  LightSource "infinite" "blackbody L" [6000 2.5]\n'
+    s += "AttributeEnd\n"
+    s += 'AttributeBegin\n  AreaLightSource "diffuse" "blackbody L" [3200 20]\n'
+    s += "  " + quad((-.2, 1.4, -.2), (.2, 1.4, -.2), (.2, 1.4, .2), (-.2, 1.4, .2)) + "AttributeEnd\n"
+    s += f'AttributeBegin\n  Material "matte" "spectrum Kd" {WHITE}\n'
+    s += "  " + quad((-3, -1, 3), (3, -1, 3), (3, -1, -3), (-3, -1, -3)) + "AttributeEnd\n"
+    s += (f'AttributeBegin\n  Material "matte" "spectrum Kd" {RED}\n  Translate -1 -.55 0\n'
+          '  Shape "sphere" "float radius" [.45]\nAttributeEnd\n')
+    s += ('AttributeBegin\n  Material "glass" "float index" [1.5]\n  Translate 0 -.6 .5\n'
+          '  Shape "sphere" "float radius" [.4]\nAttributeEnd\n')
+    s += ('AttributeBegin\n  Material "metal" "float roughness" [.01]\n  Translate 1 -.5 -.2\n'
+          '  Shape "sphere" "float radius" [.5]\nAttributeEnd\n')
+    return s + "WorldEnd\n"
+
+
 def cornell(opts, out):
     cam = 'LookAt 0 0 3.8  0 0 0  0 1 0\nCamera "perspective" "float fov" [39]'
     return header(opts, cam, os.path.splitext(os.path.basename(out))[0]) + cornell_world()
@@ -330,6 +374,8 @@ def main(argv):
         text = instanced(opts, out)
     elif name == "zoo":
         text = zoo(opts, out)
+    elif name == "envbox":
+        text = envbox(opts, out)
     elif name == "furnace_point":
         text = furnace(opts, out, False)
     elif name == "furnace_area":

@@ -48,6 +48,10 @@ SCENES = {
     "lobes_box": dict(gen=["lobes_box", "res=64", "spp=16"], res=(64, 64), spp=16),
     # Sampler "sobol" (SURVEY 8f rank 4); non-power-of-two resolution, so the 64x64 Sobol' grid overhangs
     "cornell_sobol": dict(gen=["cornell", "res=56x40", "spp=8", "sampler=sobol"], res=(56, 40), spp=8),
+    # Light "infinite" (SURVEY 8f rank 3): a constant sky, and a lat-long map with a sun (12 x 6,
+    # resampled by the MIPMap), next to an area light; light selection by the spatial / power tables
+    "envbox_const": dict(gen=["envbox", "res=64x48", "spp=16", "env=const"], res=(64, 48), spp=16),
+    "envbox_map": dict(gen=["envbox", "res=64x48", "spp=16", "env=map", "strategy=power"], res=(64, 48), spp=16),
     "killeroo128": dict(ref="killeroo-simple.pbrt", res=(128, 128), spp=8),
     # crop = croppedPixelBounds (ceil(res * cropwindow), core/film.cpp:57-63): the film / .dat size
     "zoo": dict(gen=["zoo", "res=96x64", "spp=8", "strategy=power"], res=(96, 64), spp=8, crop=(10, 4, 92, 58)),
