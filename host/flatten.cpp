@@ -69,6 +69,7 @@
 #include "spectrum.h"
 #include "texture.h"
 #include "textures/constant.h"
+#include "textures/imagemap.h"
 #include "transform.h"
 #undef private
 #undef protected
@@ -119,6 +120,30 @@ struct Builder {
         return !t || dynamic_cast<const ConstantTexture<T> *>(t.get());
     }
 
+    typedef ImageTexture<RGBSpectrum, Spectrum> SpectrumImage;
+    static const SpectrumImage *AsImage(const std::shared_ptr<Texture<Spectrum>> &t) {
+        return dynamic_cast<const SpectrumImage *>(t.get());
+    }
+    std::map<const void *, int> textureOffset;
+    int weightLutOffset = -1;
+    // The seven rgbIllum2Spect* rows: what SampledSpectrum::FromRGB expands an RGB value over when
+    // called without a SpectrumType (core/spectrum.h:428-429: the default is Illuminant) -- that is
+    // how InfiniteAreaLight reads its map AND how ImageTexture::convertOut turns a texel into a
+    // Spectrum (textures/imagemap.h:113-117).
+    int illumBasisRow = -1;
+    int IlluminantBasis() {
+        if (illumBasisRow < 0) {
+            illumBasisRow = AddSpectrum(SampledSpectrum::rgbIllum2SpectWhite);
+            AddSpectrum(SampledSpectrum::rgbIllum2SpectCyan);
+            AddSpectrum(SampledSpectrum::rgbIllum2SpectMagenta);
+            AddSpectrum(SampledSpectrum::rgbIllum2SpectYellow);
+            AddSpectrum(SampledSpectrum::rgbIllum2SpectRed);
+            AddSpectrum(SampledSpectrum::rgbIllum2SpectGreen);
+            AddSpectrum(SampledSpectrum::rgbIllum2SpectBlue);
+        }
+        return illumBasisRow;
+    }
+    int AddImageTexture(const SpectrumImage *t);
     bool CheckMaterialTextures(const Material *m);
     int AddMaterial(const Material *m);
     bool AddLobe(const BxDF *b);
@@ -133,15 +158,15 @@ bool Builder::CheckMaterialTextures(const Material *m) {
     // bump maps perturb the shading frame per hit and are out as well.
     if (auto *x = dynamic_cast<const MatteMaterial *>(m)) {
         if (x->bumpMap) return Fail("matte: bumpmap is not supported");
-        if (!IsConstant(x->Kd) || !IsConstant(x->sigma))
-            return Fail("matte: only constant textures are supported");
+        if ((!IsConstant(x->Kd) && !AsImage(x->Kd)) || !IsConstant(x->sigma))
+            return Fail("matte: only constant textures (and an imagemap Kd) are supported");
         return true;
     }
     if (auto *x = dynamic_cast<const PlasticMaterial *>(m)) {
         if (x->bumpMap) return Fail("plastic: bumpmap is not supported");
-        if (!IsConstant(x->Kd) || !IsConstant(x->Ks) ||
+        if ((!IsConstant(x->Kd) && !AsImage(x->Kd)) || !IsConstant(x->Ks) ||
             !IsConstant(x->roughness))
-            return Fail("plastic: only constant textures are supported");
+            return Fail("plastic: only constant textures (and an imagemap Kd) are supported");
         return true;
     }
     if (auto *x = dynamic_cast<const GlassMaterial *>(m)) {
@@ -294,11 +319,89 @@ bool Builder::AddLobe(const BxDF *b) {
     return true;
 }
 
+// One ImageTexture<RGBSpectrum, Spectrum> as a block of tex_floats (layout: include/sptx.h).
+// Returns the block's offset, or -1 (err set) for what the device does not evaluate.
+int Builder::AddImageTexture(const SpectrumImage *t) {
+    auto it = textureOffset.find(t);
+    if (it != textureOffset.end()) return it->second;
+    auto *uv = dynamic_cast<const UVMapping2D *>(t->mapping.get());
+    if (!uv) {
+        Fail("imagemap: only the \"uv\" mapping is on the GPU hot path");
+        return -1;
+    }
+    const MIPMap<RGBSpectrum> &mip = *t->mipmap;
+    if (mip.noFiltering || t->spdFlag) {
+        Fail("imagemap: noFiltering / display-primary textures are outside the GPU hot path");
+        return -1;
+    }
+    std::vector<float> &T = fs->texFloats;
+    auto putInt = [&](int v) {
+        float f;
+        std::memcpy(&f, &v, 4);
+        T.push_back(f);
+    };
+    if (weightLutOffset < 0) {  // MIPMap::weightLut, filled by the first MIPMap constructed
+        weightLutOffset = (int)T.size();
+        for (int i = 0; i < 128; ++i) T.push_back(MIPMap<RGBSpectrum>::weightLut[i]);
+    }
+    const int basisRow = IlluminantBasis();
+    const int block = (int)T.size();
+    const int nLevels = mip.Levels();
+    putInt(nLevels);
+    putInt(mip.wrapMode == ImageWrap::Repeat ? 0 : (mip.wrapMode == ImageWrap::Black ? 1 : 2));
+    putInt(mip.doTrilinear ? 1 : 0);
+    T.push_back(mip.maxAnisotropy);
+    T.push_back(uv->su);
+    T.push_back(uv->sv);
+    T.push_back(uv->du);
+    T.push_back(uv->dv);
+    putInt(basisRow);
+    putInt(weightLutOffset);
+    for (int i = 10; i < 16; ++i) T.push_back(0.f);
+    const size_t levelTable = T.size();
+    for (int l = 0; l < nLevels; ++l) {
+        putInt(mip.pyramid[l]->uSize());
+        putInt(mip.pyramid[l]->vSize());
+        putInt(0);
+    }
+    for (int l = 0; l < nLevels; ++l) {
+        const BlockedArray<RGBSpectrum> &lvl = *mip.pyramid[l];
+        const int off = (int)T.size() - block;
+        std::memcpy(&T[levelTable + 3 * l + 2], &off, 4);
+        for (int v = 0; v < lvl.vSize(); ++v)
+            for (int u = 0; u < lvl.uSize(); ++u) {
+                Float rgb[3];
+                lvl(u, v).ToRGB(rgb);
+                T.push_back(rgb[0]);
+                T.push_back(rgb[1]);
+                T.push_back(rgb[2]);
+            }
+    }
+    textureOffset[t] = block;
+    return block;
+}
+
 int Builder::AddMaterial(const Material *m) {
     if (!m) return -1;
     auto it = materialIndex.find(m);
     if (it != materialIndex.end()) return it->second;
     if (!CheckMaterialTextures(m)) return -2;
+    // An imagemap Kd (matte, plastic): the material's lobes are taken with a stand-in constant Kd
+    // (so that the diffuse lobe, which the material adds first and only for a non-black value, is
+    // there), then that lobe's R is pointed at the texture, which the device evaluates per hit.
+    std::shared_ptr<Texture<Spectrum>> *kdSlot = nullptr;
+    if (auto *x = dynamic_cast<const MatteMaterial *>(m))
+        kdSlot = const_cast<std::shared_ptr<Texture<Spectrum>> *>(&x->Kd);
+    else if (auto *x = dynamic_cast<const PlasticMaterial *>(m))
+        kdSlot = const_cast<std::shared_ptr<Texture<Spectrum>> *>(&x->Kd);
+    int texBlock = -1;
+    std::shared_ptr<Texture<Spectrum>> savedKd;
+    if (kdSlot && AsImage(*kdSlot)) {
+        texBlock = AddImageTexture(AsImage(*kdSlot));
+        if (texBlock < 0) return -2;
+        savedKd = *kdSlot;
+        *kdSlot = std::make_shared<ConstantTexture<Spectrum>>(Spectrum(.5f));
+    }
     // With constant textures the BSDF a material builds does not depend on
     // the hit, so build it once through the material's own code
     // (Material::ComputeScatteringFunctions, allowMultipleLobes = true as
@@ -309,6 +412,7 @@ int Builder::AddMaterial(const Material *m) {
                           Vector3f(0, 1, 0), Normal3f(0, 0, 0),
                           Normal3f(0, 0, 0), 0, nullptr);
     m->ComputeScatteringFunctions(&si, arena, TransportMode::Radiance, true);
+    if (savedKd) *kdSlot = savedKd;
     if (!si.bsdf) {
         Fail("material produced no BSDF");
         return -2;
@@ -324,6 +428,14 @@ int Builder::AddMaterial(const Material *m) {
     fm.material_id = m->materialId;
     for (int i = 0; i < si.bsdf->nBxDFs; ++i)
         if (!AddLobe(si.bsdf->bxdfs[i])) return -2;
+    if (texBlock >= 0) {
+        sptx_lobe &l0 = fs->lobes[(size_t)fm.first_lobe];
+        if (fm.n_lobes < 1 || l0.type != SPTX_LOBE_LAMBERT) {
+            Fail("textured Kd: the material's first lobe is not a Lambert lobe (matte with sigma != 0?)");
+            return -2;
+        }
+        l0.R = SPTX_TEX_ROW(texBlock);
+    }
     int idx = (int)fs->materials.size();
     fs->materials.push_back(fm);
     materialIndex[m] = idx;
@@ -571,6 +683,7 @@ void FlatScene::Finish() {
     SPTX_SET(prime_sums, n_prime_sums, primeSums, 1)
     SPTX_SET(perms, n_perms, perms, 1)
     SPTX_SET(env_floats, n_env_floats, envFloats, 1)
+    SPTX_SET(tex_floats, n_tex_floats, texFloats, 1)
 #undef SPTX_SET
 }
 
@@ -594,7 +707,6 @@ bool FlattenScene(const Scene &scene, const Camera &camera, Sampler &sampler,
     for (size_t i = 0; i < b.pending.size(); ++i)
         if (!b.AddAggregate(b.pending[i], false)) return fail(b.err);
 
-    int illumBasisRow = -1;  // first of the seven rgbIllum2Spect* rows, added with the first infinite light
     for (size_t i = 0; i < scene.lights.size(); ++i) {
         const Light *l = scene.lights[i].get();
         sptx_light fl;
@@ -627,16 +739,7 @@ bool FlattenScene(const Scene &scene, const Camera &camera, Sampler &sampler,
             fl.pos[0] = inf->worldCenter.x;
             fl.pos[1] = inf->worldCenter.y;
             fl.pos[2] = inf->worldCenter.z;
-            if (illumBasisRow < 0) {
-                illumBasisRow = b.AddSpectrum(SampledSpectrum::rgbIllum2SpectWhite);
-                b.AddSpectrum(SampledSpectrum::rgbIllum2SpectCyan);
-                b.AddSpectrum(SampledSpectrum::rgbIllum2SpectMagenta);
-                b.AddSpectrum(SampledSpectrum::rgbIllum2SpectYellow);
-                b.AddSpectrum(SampledSpectrum::rgbIllum2SpectRed);
-                b.AddSpectrum(SampledSpectrum::rgbIllum2SpectGreen);
-                b.AddSpectrum(SampledSpectrum::rgbIllum2SpectBlue);
-            }
-            fl.spectrum = illumBasisRow;
+            fl.spectrum = b.IlluminantBasis();
             const MIPMap<RGBSpectrum> &mip = *inf->Lmap;
             if (mip.wrapMode != ImageWrap::Repeat || mip.noFiltering)
                 return fail("infinite light map with a wrap mode / filter outside the GPU hot path");

@@ -55,6 +55,7 @@ struct FlatScene {
     std::vector<int32_t> primes, primeSums;
     std::vector<uint16_t> perms;
     std::vector<float> envFloats;  // infinite lights' blocks (sptx_light)
+    std::vector<float> texFloats;  // image textures' blocks (sptx_scene_desc::tex_floats)
     void Finish();  // points desc at the vectors
 };
 

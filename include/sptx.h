@@ -130,7 +130,8 @@ enum { SPTX_FRESNEL_NOOP = 0, SPTX_FRESNEL_DIELECTRIC = 1, SPTX_FRESNEL_CONDUCTO
 typedef struct sptx_lobe {
     int32_t type;    /* SPTX_LOBE_*                                          */
     int32_t fresnel; /* SPTX_FRESNEL_* for SPECULAR_REFL / MICROFACET_REFL   */
-    int32_t R;       /* reflectance spectrum row, -1 if unused               */
+    int32_t R;       /* reflectance spectrum row, -1 if unused, <= -2: image texture
+                        SPTX_TEX_ROW(offset) (LAMBERT / OREN_NAYAR lobes only)   */
     int32_t T;       /* transmittance spectrum row, -1 if unused             */
     int32_t fr_eta_i, fr_eta_t, fr_k; /* conductor Fresnel spectra rows      */
     float eta_a, eta_b;   /* dielectric: Fresnel etaI/etaT or lobe etaA/etaB */
@@ -283,7 +284,19 @@ typedef struct sptx_scene_desc {
     /* Infinite lights' blocks (see sptx_light).  Last member: scene files written before it existed
      * are still read (sptx_scene_load fills it with 0 / NULL). */
     int64_t n_env_floats; const float *env_floats;
+    /* Image textures (ImageTexture<RGBSpectrum, Spectrum>, src/textures/imagemap.h:80-137, with a
+     * UVMapping2D).  A lobe whose R is the value of such a texture has R = SPTX_TEX_ROW(offset),
+     * offset = where the texture's block starts in tex_floats[] (integers stored as bit patterns):
+     *   [0] levels [1] wrap (0 Repeat, 1 Black, 2 Clamp) [2] doTrilinear [3] maxAnisotropy (float)
+     *   [4..8) su sv du dv (float) [8] first of the seven rgbIllum2Spect* rows in spectra[]
+     *       (ImageTexture::convertOut's FromRGB(rgb) defaults to SpectrumType::Illuminant)
+     *   [9] offset of MIPMap::weightLut (128 floats) in tex_floats[] [10..16) unused,
+     *   then per level {uSize, vSize, offset of its RGB texels from the block start},
+     *   then the texels, level after level, row t, column s (MIPMap::pyramid, src/core/mipmap.h).
+     * Also a trailing member (older scene files are still read). */
+    int64_t n_tex_floats; const float *tex_floats;
 } sptx_scene_desc;
+#define SPTX_TEX_ROW(offset) (-2 - (int32_t)(offset))
 
 /* ---- ray batches (parity test #1 and the traversal benchmark) ----------- */
 

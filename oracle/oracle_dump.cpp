@@ -427,6 +427,29 @@ void DumpIntegrator::Render(const Scene &scene) {
             Float rayWeight = real->camera->GenerateRayDifferential(cameraSample, &ray);
             ray.ScaleDifferentials(1 / std::sqrt((Float)smp->samplesPerPixel));
             Spectrum L(0.f);
+            if (getenv("ORACLE_LI_TRACE") && (int)i < atoi(getenv("ORACLE_LI_TRACE"))) {
+                // the camera vertex as the material sees it: parameterisation, differentials
+                RayDifferential r2(ray);
+                SurfaceInteraction si;
+                if (scene.Intersect(r2, &si)) {
+                    si.ComputeDifferentials(r2);
+                    fprintf(stderr, "REFTRACE q %d %d %d p %.9g %.9g %.9g n %.9g %.9g %.9g uv %.9g %.9g\n", pixel.x,
+                            pixel.y, q[3 * i + 2], si.p.x, si.p.y, si.p.z, si.n.x, si.n.y, si.n.z, si.uv[0], si.uv[1]);
+                    fprintf(stderr, "REFTRACE   rxo %.9g %.9g %.9g rxd %.9g %.9g %.9g ryo %.9g %.9g %.9g ryd %.9g %.9g %.9g\n",
+                            r2.rxOrigin.x, r2.rxOrigin.y, r2.rxOrigin.z, r2.rxDirection.x, r2.rxDirection.y,
+                            r2.rxDirection.z, r2.ryOrigin.x, r2.ryOrigin.y, r2.ryOrigin.z, r2.ryDirection.x,
+                            r2.ryDirection.y, r2.ryDirection.z);
+                    fprintf(stderr, "REFTRACE   dpdu %.9g %.9g %.9g dpdv %.9g %.9g %.9g dudx %.9g dvdx %.9g dudy %.9g dvdy %.9g\n",
+                            si.dpdu.x, si.dpdu.y, si.dpdu.z, si.dpdv.x, si.dpdv.y, si.dpdv.z, si.dudx, si.dvdx,
+                            si.dudy, si.dvdy);
+                    si.ComputeScatteringFunctions(r2, arena, true);
+                    if (si.bsdf && si.bsdf->nBxDFs > 0) {
+                        Spectrum f = si.bsdf->f(Vector3f(si.n), Vector3f(si.n)) * Pi;
+                        fprintf(stderr, "REFTRACE   f*pi(n,n) %.9g %.9g %.9g %.9g nBxDFs %d\n", f[2], f[10], f[18], f[26],
+                                si.bsdf->nBxDFs);
+                    }
+                }
+            }
             if (rayWeight > 0) L = real->Li(ray, scene, *smp, arena, 0);
             float *o = &out[34 * i];
             for (int b = 0; b < nSpectralSamples; ++b) o[b] = L[b];

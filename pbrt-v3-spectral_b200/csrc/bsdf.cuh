@@ -32,6 +32,8 @@ enum {
     TERM_COND_R_DIV = 5, // FrCond[b](s0) * R[b] / s1       (specular reflection, conductor)
     TERM_T_S_S_DIV = 6,  // (T[b] * s0) * s1 / s2           (specular transmission)
     TERM_BLEND = 7,      // FresnelBlend::f: Rd = R, Rs = e0; diffuse and specular scalars s0..s3
+    TERM_TEX_S = 8,      // Tex[b] * s0, Tex = an image texture's value at the hit: FromRGB over the
+                         // basis rows e0, e1, e2 with weights s1, s2, s3 (tex.cuh); Lambert
 };
 
 // FresnelBlend::f for one bin, core/reflection.cpp:285-299 (+ SchlickFresnel, reflection.h):
@@ -59,6 +61,8 @@ using FSum = FSumN<kMaxTerms>;
 // A shading variant (K3 is compiled once per variant, see shade.cuh) is the set of lobe types its
 // code can evaluate: branches for other types are removed at compile time.
 constexpr int kAllLobes = (1 << (SPTX_LOBE_FRESNEL_BLEND + 1)) - 1;
+// not a lobe type: the variant's materials may have an image texture as their Lambert lobe's R
+constexpr int kTexturedLobes = 1 << 16;
 template <int LOBES>
 SPTX_DEV constexpr bool has_lobe(int type) { return ((LOBES >> type) & 1) != 0; }
 constexpr int kSpecularLobes = (1 << SPTX_LOBE_SPECULAR_REFL) | (1 << SPTX_LOBE_SPECULAR_TRANS) |
@@ -153,8 +157,28 @@ SPTX_DEV float4 spec4(const DScene &S, int row, int c) {
 SPTX_DEV float padless(int c, float x, float d) { return c < 7 ? x / d : 0.f; }
 // (term kinds a variant can meet: R_S Lambert / Lambert transmission; R_S_S Oren-Nayar /
 //  microfacet transmission; MICRO_* microfacet reflection; *_DIV the specular lobes; BLEND)
+// One bin of an image texture's value: ImageTexture::convertOut calls Spectrum::FromRGB(rgb) WITHOUT a
+// SpectrumType, and the default is Illuminant (core/spectrum.h:428-429, textures/imagemap.h:113-117):
+// r = 0 + w0 B0; r += w1 B1; r += w2 B2 over the rgbIllum2Spect* rows, r *= .86445f, Clamp(0, inf)
+// (core/spectrum.cpp:135-168, :250) -- the same expansion as an infinite light's map (light.cuh).
+SPTX_DEV float tex_bin1(float b0, float b1, float b2, float w0, float w1, float w2) {
+    float r = w0 * b0;
+    r = r + w1 * b1;
+    r = r + w2 * b2;
+    r = r * .86445f;
+    return (r < 0.f) ? 0.f : r;
+}
+SPTX_DEV float4 tex_bin4(const DScene &S, int r0, int r1, int r2, float w0, float w1, float w2, int c) {
+    const float4 b0 = spec4(S, r0, c), b1 = spec4(S, r1, c), b2 = spec4(S, r2, c);
+    return make_float4(tex_bin1(b0.x, b1.x, b2.x, w0, w1, w2), tex_bin1(b0.y, b1.y, b2.y, w0, w1, w2),
+                       tex_bin1(b0.z, b1.z, b2.z, w0, w1, w2), c < 7 ? tex_bin1(b0.w, b1.w, b2.w, w0, w1, w2) : 0.f);
+}
 template <int LOBES>
 SPTX_DEV float4 fterm4(const DScene &S, const FTerm &t, int c) {
+    if ((LOBES & kTexturedLobes) && t.kind == TERM_TEX_S) {
+        const float4 R = tex_bin4(S, t.e0, t.e1, t.e2, t.s1, t.s2, t.s3, c);
+        return make_float4(R.x * t.s0, R.y * t.s0, R.z * t.s0, R.w * t.s0);
+    }
     const float4 R = spec4(S, t.R, c);
     constexpr bool kRS = has_lobe<LOBES>(SPTX_LOBE_LAMBERT) || has_lobe<LOBES>(SPTX_LOBE_LAMBERT_TRANS);
     constexpr bool kRSS = has_lobe<LOBES>(SPTX_LOBE_OREN_NAYAR) || has_lobe<LOBES>(SPTX_LOBE_MICROFACET_TRANS);

@@ -33,7 +33,12 @@ SPTX_DEV V2 concentric_sample_disk(V2 u) {
 #endif
 }
 
-SPTX_DEV float perspective_ray(const DCamera &C, V2 pFilm, V2 pLensU, Ray *out) {
+// Offset rays of a camera sample (RayDifferential, core/geometry.h:894-930), world space.
+struct RayDiff {
+    V3 rxo, rxd, ryo, ryd;
+};
+
+SPTX_DEV float perspective_ray(const DCamera &C, V2 pFilm, V2 pLensU, Ray *out, RayDiff *rd = nullptr) {
     V3 pCamera = xf_point(C.c.raster_to_camera, mk(pFilm.x, pFilm.y, 0.f));
     Ray r;
     r.o = mk(0.f, 0.f, 0.f);
@@ -46,6 +51,35 @@ SPTX_DEV float perspective_ray(const DCamera &C, V2 pFilm, V2 pLensU, Ray *out) 
         V3 pFocus = r.o + r.d * ft;
         r.o = mk(pLens.x, pLens.y, 0.f);
         r.d = normalize(pFocus - r.o);
+    }
+    if (rd) {
+        // PerspectiveCamera::GenerateRayDifferential, cameras/perspective.cpp:119-141; dxCamera /
+        // dyCamera as the constructor computes them (:58-61)
+        const V3 c0 = xf_point(C.c.raster_to_camera, mk(0.f, 0.f, 0.f));
+        const V3 dxCamera = xf_point(C.c.raster_to_camera, mk(1.f, 0.f, 0.f)) - c0;
+        const V3 dyCamera = xf_point(C.c.raster_to_camera, mk(0.f, 1.f, 0.f)) - c0;
+        V3 rxo, rxd, ryo, ryd;
+        if (C.c.lens_radius > 0) {
+            V3 dx = normalize(pCamera + dxCamera);
+            float ft = C.c.focal_distance / dx.z;
+            V3 pFocus = ft * dx;
+            rxo = r.o;
+            rxd = normalize(pFocus - rxo);
+            V3 dy = normalize(pCamera + dyCamera);
+            ft = C.c.focal_distance / dy.z;
+            pFocus = ft * dy;
+            ryo = r.o;
+            ryd = normalize(pFocus - ryo);
+        } else {
+            rxo = ryo = r.o;
+            rxd = normalize(pCamera + dxCamera);
+            ryd = normalize(pCamera + dyCamera);
+        }
+        // CameraToWorld(RayDifferential), core/transform.h:268-277
+        rd->rxo = xf_point(C.c.camera_to_world, rxo);
+        rd->ryo = xf_point(C.c.camera_to_world, ryo);
+        rd->rxd = xf_vec(C.c.camera_to_world, rxd);
+        rd->ryd = xf_vec(C.c.camera_to_world, ryd);
     }
     *out = xf_ray(C.c.camera_to_world, r);
     return 1.f;
@@ -180,33 +214,44 @@ SPTX_DEV float realistic_generate_ray(const DCamera &C, V2 pFilmRaster, V2 pLens
 
 // Camera::GenerateRayDifferential for the realistic camera (core/camera.cpp:60-99):
 // weight 0 if the main ray or both +-0.05 px shifted rays in x or in y are vignetted.
-SPTX_DEV float realistic_ray(const DCamera &C, V2 pFilm, V2 pLensU, float wavelength, Ray *out) {
+SPTX_DEV float realistic_ray(const DCamera &C, V2 pFilm, V2 pLensU, float wavelength, Ray *out,
+                             RayDiff *rd = nullptr) {
     float wt = realistic_generate_ray(C, pFilm, pLensU, wavelength, out);
     if (wt == 0) return 0.f;
-    Ray tmp;
+    Ray tmp{out->o, out->d, kInf};
     const float eps[2] = {.05f, -.05f};
     float wtx = 0.f;
     for (int k = 0; k < 2; ++k) {
         V2 p = pFilm;
         p.x += eps[k];
         wtx = realistic_generate_ray(C, p, pLensU, wavelength, &tmp);
+        if (rd) {  // rxOrigin = o + (rx.o - o) / eps, likewise the direction (a failed trace leaves rx as it was)
+            rd->rxo = out->o + div_by(tmp.o - out->o, eps[k]);
+            rd->rxd = out->d + div_by(tmp.d - out->d, eps[k]);
+        }
         if (wtx != 0) break;
     }
     if (wtx == 0) return 0.f;
     float wty = 0.f;
+    tmp = Ray{out->o, out->d, kInf};
     for (int k = 0; k < 2; ++k) {
         V2 p = pFilm;
         p.y += eps[k];
         wty = realistic_generate_ray(C, p, pLensU, wavelength, &tmp);
+        if (rd) {
+            rd->ryo = out->o + div_by(tmp.o - out->o, eps[k]);
+            rd->ryd = out->d + div_by(tmp.d - out->d, eps[k]);
+        }
         if (wty != 0) break;
     }
     if (wty == 0) return 0.f;
     return wt;
 }
 
-SPTX_DEV float camera_ray(const DCamera &C, V2 pFilm, V2 pLensU, float wavelength, Ray *out) {
-    if (C.c.type == SPTX_CAMERA_PERSPECTIVE) return perspective_ray(C, pFilm, pLensU, out);
-    return realistic_ray(C, pFilm, pLensU, wavelength, out);
+SPTX_DEV float camera_ray(const DCamera &C, V2 pFilm, V2 pLensU, float wavelength, Ray *out,
+                          RayDiff *rd = nullptr) {
+    if (C.c.type == SPTX_CAMERA_PERSPECTIVE) return perspective_ray(C, pFilm, pLensU, out, rd);
+    return realistic_ray(C, pFilm, pLensU, wavelength, out, rd);
 }
 
 }  // namespace sptx

@@ -18,6 +18,12 @@ struct Isect {
     V3 ns, sdpdu;  // shading.n, shading.dpdu
     int material, light, prim;
 };
+// The surface parameterisation at the hit (SurfaceInteraction::uv, dpdu, dpdv): image textures only,
+// so only the textured shading variant asks for it (the others pass NULL).
+struct SurfParam {
+    V3 dpdu, dpdv;
+    V2 uv;
+};
 
 SPTX_DEV V3 ld3(const float *base, size_t i) {
     return mk(__ldg(base + 3 * i), __ldg(base + 3 * i + 1), __ldg(base + 3 * i + 2));
@@ -25,7 +31,7 @@ SPTX_DEV V3 ld3(const float *base, size_t i) {
 
 // Interaction in the space the shape lives in (world for top-level triangles).
 SPTX_NOINL void triangle_interaction(const DScene &S, int shape, V3 rayD, float b0, float b1,
-                                   float b2, Isect *it) {
+                                   float b2, Isect *it, SurfParam *sp = nullptr) {
     const sptx_triangle T = S.triangles[shape];
     const sptx_mesh M = S.meshes[T.mesh];
     V3 p0 = ld3(S.positions, (size_t)M.p_base + T.v[0]);
@@ -41,6 +47,11 @@ SPTX_NOINL void triangle_interaction(const DScene &S, int shape, V3 rayD, float 
     float zAbsSum = (fabsf(b0 * p0.z) + fabsf(b1 * p1.z) + fabsf(b2 * p2.z));
     it->pError = gamma_n(7) * mk(xAbsSum, yAbsSum, zAbsSum);
     it->p = b0 * p0 + b1 * p1 + b2 * p2;
+    if (sp) {
+        sp->dpdu = dpdu;
+        sp->dpdv = dpdv;
+        sp->uv = V2{b0 * uv[0].x + b1 * uv[1].x + b2 * uv[2].x, b0 * uv[0].y + b1 * uv[1].y + b2 * uv[2].y};
+    }
     it->wo = normalize(-rayD);
     V3 n = normalize(cross(dp02, dp12));
     V3 ns = n;
@@ -95,7 +106,8 @@ SPTX_NOINL void triangle_interaction(const DScene &S, int shape, V3 rayD, float 
 // Object-space sphere interaction moved to the sphere's parent space.  `pHit` is the refined
 // object-space hit point Sphere::Intersect computed (shapes/sphere.cpp:84-90), carried by the hit
 // record; `rayD` is the direction of the ray in the sphere's parent space.
-SPTX_NOINL bool sphere_interaction_at(const DScene &S, int shape, V3 rayD, V3 pHit, Isect *it) {
+SPTX_NOINL bool sphere_interaction_at(const DScene &S, int shape, V3 rayD, V3 pHit, Isect *it,
+                                      SurfParam *par = nullptr) {
     const sptx_sphere &sp = S.spheres[shape];
     SphereHit sh;
     sh.pHit = pHit;
@@ -122,6 +134,14 @@ SPTX_NOINL bool sphere_interaction_at(const DScene &S, int shape, V3 rayD, V3 pH
     ns = normalize(xf_normal(sp.w2o, ns));
     it->sdpdu = xf_vec(sp.o2w, dpdu);
     it->ns = faceforward(ns, it->n);
+    if (par) {
+        par->dpdu = it->sdpdu;
+        par->dpdv = xf_vec(sp.o2w, dpdv);
+        // (u, v) = (phi / phiMax, (theta - thetaMin) / (thetaMax - thetaMin)), shapes/sphere.cpp:112-114
+        float phi = atan2f(pHit.y, pHit.x);
+        if (phi < 0) phi += 2 * kPi;
+        par->uv = V2{phi / sp.phi_max, (theta - sp.theta_min) / (sp.theta_max - sp.theta_min)};
+    }
     return true;
 }
 
@@ -136,7 +156,7 @@ SPTX_NOINL bool sphere_interaction(const DScene &S, int shape, const Ray &ray, I
 
 // Scene-level interaction for a closest-hit record of world ray `ray`.
 SPTX_NOINL bool build_interaction(const DScene &S, const Ray &ray, int prim, int inst, float b0,
-                                float b1, float b2, Isect *it) {
+                                float b1, float b2, Isect *it, SurfParam *par = nullptr) {
     const sptx_prim P = S.prims[prim];
     it->material = P.material;
     it->light = P.light;
@@ -144,9 +164,9 @@ SPTX_NOINL bool build_interaction(const DScene &S, const Ray &ray, int prim, int
     Ray lr = ray;
     if (inst >= 0) lr = xf_ray(S.instances[inst].w2p, ray);
     if (P.kind == SPTX_PRIM_TRIANGLE)
-        triangle_interaction(S, P.shape, lr.d, b0, b1, b2, it);
+        triangle_interaction(S, P.shape, lr.d, b0, b1, b2, it, par);
     else  // (b0, b1, b2) of a sphere hit = its object-space hit point
-        sphere_interaction_at(S, P.shape, lr.d, mk(b0, b1, b2), it);
+        sphere_interaction_at(S, P.shape, lr.d, mk(b0, b1, b2), it, par);
     if (inst >= 0 && !S.instances[inst].is_identity) {
         // InterpolatedPrimToWorld(*isect), core/primitive.cpp:88-89
         const sptx_instance &I = S.instances[inst];
@@ -159,6 +179,10 @@ SPTX_NOINL bool build_interaction(const DScene &S, const Ray &ray, int prim, int
         V3 ns = normalize(xf_normal(I.w2p, it->ns));
         it->sdpdu = xf_vec(I.p2w, it->sdpdu);
         it->ns = faceforward(ns, it->n);
+        if (par) {
+            par->dpdu = xf_vec(I.p2w, par->dpdu);
+            par->dpdv = xf_vec(I.p2w, par->dpdv);
+        }
     }
     return true;
 }

@@ -174,8 +174,10 @@ SPTX_DEV float sphere_pdf(const DScene &S, int shape, const RefPoint &ref, V3 wi
 }
 
 // Light::Pdf_Li (DiffuseAreaLight: shape->Pdf; PointLight: 0).
+// (ENV = false: compiled for scenes without infinite lights, see shade.cu)
+template <bool ENV = true>
 SPTX_NOINL float light_pdf_li(const DScene &S, const sptx_light &L, const RefPoint &ref, V3 wi) {
-    if (L.type == SPTX_LIGHT_INFINITE) {
+    if (ENV && L.type == SPTX_LIGHT_INFINITE) {
         // InfiniteAreaLight::Pdf_Li, lights/infinite.cpp:125-133; Distribution2D::Pdf, sampling.h:135-142
         const float *base = S.env + L.shape;
         const int W = (int)__ldg(base), H = (int)__ldg(base + 1), nu = (int)__ldg(base + 2), nv = (int)__ldg(base + 3);
@@ -345,8 +347,9 @@ SPTX_DEV float li_bin(const DScene &S, const LiSample &ls, int b) {
 }
 
 // Four consecutive bins of the sampled radiance (the thread-per-path form of li_bin).
+template <bool ENV = true>
 SPTX_DEV float4 li4(const DScene &S, const LiSample &ls, int c) {
-    if (ls.isEnv) return env_bin4(S, ls.env, c);
+    if (ENV && ls.isEnv) return env_bin4(S, ls.env, c);
     float4 li = spec4(S, ls.spectrum, c);
     if (ls.divisor != 0.f) {
         li.x = li.x / ls.divisor;
@@ -357,6 +360,7 @@ SPTX_DEV float4 li4(const DScene &S, const LiSample &ls, int c) {
     return li;
 }
 
+template <bool ENV = true>
 SPTX_NOINL LiSample light_sample_li(const DScene &S, const sptx_light &L, const RefPoint &ref, V2 u) {
     LiSample r;
     r.spectrum = L.spectrum;
@@ -364,8 +368,8 @@ SPTX_NOINL LiSample light_sample_li(const DScene &S, const sptx_light &L, const 
     r.black = true;
     r.pdf = 0.f;
     r.wi = mk(0, 0, 0);
-    r.isEnv = false;
-    if (L.type == SPTX_LIGHT_INFINITE) {
+    if (ENV) r.isEnv = false;
+    if (ENV && L.type == SPTX_LIGHT_INFINITE) {
         // InfiniteAreaLight::Sample_Li, lights/infinite.cpp:98-123
         const EnvMap m = env_map(S, L);
         float pdfs[2];

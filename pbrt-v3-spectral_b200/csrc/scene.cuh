@@ -14,6 +14,8 @@
 
 namespace sptx {
 
+struct DCamera;
+
 struct DScene {
     const float4 *nodes;  // 2 x float4 per node
     const sptx_bvh *bvhs;
@@ -35,6 +37,10 @@ struct DScene {
     int n_infinite;         // number of infinite lights; their indices in lights[]:
     int infinite[4];
     int n_bvhs;
+    // image textures' blocks (sptx_scene_desc::tex_floats), or NULL; the camera (device copy), which
+    // the textured shading variant needs for the camera ray's differentials
+    const float *tex;
+    const DCamera *camera;
     // light selection
     int light_strategy;      // effective (uniform when n_lights == 1)
     const float *light_func; // uniform/power: func[n], then cdf[n+1]

@@ -43,6 +43,7 @@ std::vector<Section> sections(sptx_scene_desc *d) {
     SEC(prime_sums, d->n_prime_sums, sizeof(int32_t));
     SEC(perms, d->n_perms, sizeof(uint16_t));
     SEC(env_floats, d->n_env_floats, sizeof(float));
+    SEC(tex_floats, d->n_tex_floats, sizeof(float));
 #undef SEC
     return s;
 }
@@ -100,26 +101,31 @@ extern "C" int sptx_scene_load(const char *path, sptx_scene_desc **out) {
     fseek(f, 0, SEEK_END);
     long size = ftell(f);
     fseek(f, 0, SEEK_SET);
-    // One allocation: descriptor first, arrays behind it; sptx_scene_free frees it.
-    char *blob = (char *)malloc((size_t)size + 16);
-    if (!blob) {
+    // One allocation: descriptor first, the file image (arrays) behind it; sptx_scene_free frees it.
+    // The file is read kFront bytes in, so that the full-size descriptor at the front never
+    // overlaps the arrays of a file whose own descriptor was shorter.
+    const size_t kFront = 64;
+    char *base = (char *)malloc((size_t)size + kFront + 16);
+    if (!base) {
         fclose(f);
         return SPTX_ENOMEM;
     }
+    char *blob = base + kFront;
     bool ok = fread(blob, 1, (size_t)size, f) == (size_t)size;
     fclose(f);
     uint64_t headerBytes = 0;
     if (ok && size >= 16) memcpy(&headerBytes, blob + 8, 8);
-    // (files written before the env_floats member existed have a descriptor 16 bytes shorter)
-    const uint64_t kOldHeader = sizeof(sptx_scene_desc) - 16;
+    // (files written before the trailing env_floats / tex_floats members existed have a descriptor
+    //  16 or 32 bytes shorter)
+    const uint64_t kOldHeader = sizeof(sptx_scene_desc) - 32;
     if (!ok || size < (long)(16 + kOldHeader) || memcmp(blob, kMagic, 8) != 0 ||
-        (headerBytes != sizeof(sptx_scene_desc) && headerBytes != kOldHeader)) {
-        free(blob);
+        (headerBytes != sizeof(sptx_scene_desc) && headerBytes != kOldHeader && headerBytes != kOldHeader + 16)) {
+        free(base);
         g_io_error = std::string("not a flattened-scene file of this ABI: ") + path;
         return SPTX_EINVAL;
     }
-    // Move the descriptor to the front of the allocation (16-byte header is dropped).
-    sptx_scene_desc *d = (sptx_scene_desc *)blob;
+    // The descriptor goes to the front of the allocation.
+    sptx_scene_desc *d = (sptx_scene_desc *)base;
     sptx_scene_desc tmp;
     memset(&tmp, 0, sizeof(tmp));
     memcpy(&tmp, blob + 16, (size_t)headerBytes);
@@ -131,17 +137,17 @@ extern "C" int sptx_scene_load(const char *path, sptx_scene_desc **out) {
                               tmp.n_positions, tmp.n_normals, tmp.n_tangents, tmp.n_uvs, tmp.n_spheres,
                               tmp.n_instances, tmp.n_materials, tmp.n_lobes, tmp.n_spectra, tmp.n_lights,
                               tmp.n_lens_floats, tmp.n_pupil_floats, tmp.n_primes, tmp.n_prime_sums,
-                              tmp.n_perms, tmp.n_env_floats};
+                              tmp.n_perms, tmp.n_env_floats, tmp.n_tex_floats};
     for (int64_t c : counts)
         if (c < 0 || c > (int64_t)size) {  // every element is at least one byte
-            free(blob);
+            free(base);
             g_io_error = std::string("corrupt scene file (array count out of range): ") + path;
             return SPTX_EINVAL;
         }
     std::vector<Section> secs = sections(&tmp);
     for (Section &s : secs) {
         if (s.bytes > (size_t)size || pos > (size_t)size - s.bytes) {
-            free(blob);
+            free(base);
             g_io_error = std::string("truncated scene file: ") + path;
             return SPTX_EINVAL;
         }
@@ -149,7 +155,7 @@ extern "C" int sptx_scene_load(const char *path, sptx_scene_desc **out) {
         pos += s.bytes;
         if (s.bytes % 16) pos += 16 - s.bytes % 16;
     }
-    // sizeof(desc) + 16 <= first array offset, so this does not clobber data.
+    static_assert(sizeof(sptx_scene_desc) <= 64 + 16 + sizeof(sptx_scene_desc) - 32, "descriptor overlaps the arrays");
     memcpy(d, &tmp, sizeof(tmp));
     *out = d;
     return SPTX_OK;

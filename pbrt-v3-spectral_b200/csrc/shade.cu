@@ -1,4 +1,6 @@
-// shade.cu -- the translation unit of K3 (k_shade), compiled TWICE into libsptx.so:
+// shade.cu -- the translation unit of K3 (k_shade), compiled FOUR times into libsptx.so: two
+// arithmetic modes, each with (-DSPTX_SHADE_ENV=1, namespaces *_env) and without (=0) the code for
+// Light "infinite"; sptx_upload_scene knows whether the scene has one.
 //
 //   SPTX_SHADE_NS=shade_exact   the reference's roundings (no FMA contraction, IEEE division and
 //                               square root), like the rest of the library: per-sample radiance
@@ -11,11 +13,12 @@
 // moves (by ~1e-7 relative per sample, unbiased; north_star's bar for it is 0.5 % relative RMSE).
 // The context picks the mode at run time (sptx_set_option "shade_exact").
 #include <algorithm>
+#include <cstdio>
 
 #include "shade.cuh"
 
 #ifndef SPTX_SHADE_NS
-#error "compile with -DSPTX_SHADE_NS=shade_exact or shade_fast"
+#error "compile with -DSPTX_SHADE_NS=shade_exact | shade_fast | shade_exact_env | shade_fast_env"
 #endif
 
 namespace sptx {
@@ -56,6 +59,7 @@ int launch_shade(cudaStream_t stream, int smCount, int64_t nPaths, const DScene 
         case 1: launch_variant<1>(stream, grid, dS, dH, A, R, qi, betaIn, cls, cnt); break;
         case 2: launch_variant<2>(stream, grid, dS, dH, A, R, qi, betaIn, cls, cnt); break;
         case 3: launch_variant<3>(stream, grid, dS, dH, A, R, qi, betaIn, cls, cnt); break;
+        case 4: launch_variant<4>(stream, grid, dS, dH, A, R, qi, betaIn, cls, cnt); break;
         default: continue;  // no primitive of the scene is in this class
         }
         ++launches;

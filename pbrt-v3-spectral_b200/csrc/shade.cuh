@@ -12,6 +12,7 @@
 // The two rays EstimateDirect traces (shadow ray, BSDF-sampled MIS ray) are
 // written out with their per-bin contributions (fa, fb) and traced by K4.
 #pragma once
+#include "tex.cuh"
 #include "wavefront.cuh"
 
 namespace sptx {
@@ -75,9 +76,45 @@ __device__ unsigned long long g_stageClocks[32];
         SPTX_TICK(slot + 1);                                   \
     } while (0)
 
-#ifdef SPTX_SHADE_NS
-namespace SPTX_SHADE_NS {  // (one copy of the kernels per arithmetic mode, see shade.cu)
+// 1: the kernels handle Light "infinite" (radiance map lookups in next-event estimation and MIS);
+// 0: compiled for scenes without one -- the matte variant is 14 % shorter and the bench scene's K3
+// 6 % faster (98.7 -> 93 ms per step) without that code and its live state.
+#ifndef SPTX_SHADE_ENV
+#define SPTX_SHADE_ENV 1
 #endif
+constexpr bool kShadeEnv = SPTX_SHADE_ENV != 0;
+
+#ifdef SPTX_SHADE_NS
+namespace SPTX_SHADE_NS {  // (one copy of the kernels per arithmetic mode and ENV setting, see shade.cu)
+#endif
+
+// Terms of a textured lobe (R = SPTX_TEX_ROW(..)) get the texture's value at this hit.
+template <int MAXT>
+SPTX_DEV void tex_patch(FSumN<MAXT> *f, const EnvRgb &tv) {
+#pragma unroll
+    for (int j = 0; j < MAXT; ++j)
+        if (j < f->n && f->t[j].R <= -2) {
+            FTerm &t = f->t[j];
+            t.kind = TERM_TEX_S;
+            t.e0 = tv.row[0];
+            t.e1 = tv.row[1];
+            t.e2 = tv.row[2];
+            t.s1 = tv.w[0];
+            t.s2 = tv.w[1];
+            t.s3 = tv.w[2];
+        }
+}
+// The camera ray's offset rays, as SamplerIntegrator::Render hands them to Li: GenerateRayDifferential
+// of the path's CameraSample, then ScaleDifferentials(1 / sqrt(spp)) (core/integrator.cpp:279-283).
+// Recomputed here (camera-ray vertices of textured surfaces only) instead of carried in the path state.
+SPTX_NOINL void camera_differentials(const DScene &S, const DSampler &H, uint64_t sindex, V2 pFilm,
+                                     float wavelength, const Ray &ray, RayDiff *rd) {
+    SampleStream cs{sindex, 3};  // CameraSample: pFilm (dims 0, 1), time (2), pLens (3, 4)
+    const V2 pLens = get2d(H, cs);
+    Ray again;
+    camera_ray(*S.camera, pFilm, pLens, wavelength, &again, rd);
+    scale_differentials(ray, 1.f / sqrtf((float)H.s.spp), rd);
+}
 
 template <int LOBES, int MAXT>
 __global__ void __launch_bounds__(kShadeBlock, kShadeBlocksPerSM)
@@ -101,7 +138,9 @@ k_shade(const DScene *__restrict__ Sp, const DSampler *__restrict__ Hp, PathArra
         SampleStream st{0, 0};
         int bounces = 0, neeFlags = 0, lightNum = 0;
         float lightPdfSel = 0.f, etaScale = 1.f, rayWeight = 0.f;
+        constexpr bool kTex = (LOBES & kTexturedLobes) != 0;
         Isect it;
+        SurfParam par;
         Bsdf bs;
         FSumN<MAXT> f;
         Ray ray{mk(0, 0, 0), mk(0, 0, 1), kInf};
@@ -134,7 +173,7 @@ k_shade(const DScene *__restrict__ Sp, const DSampler *__restrict__ Hp, PathArra
 #endif
             bool haveIsect = false;
             if (prim >= 0) {
-                haveIsect = build_interaction(S, ray, prim, inst, ha.z, ha.w, hb.x, &it);
+                haveIsect = build_interaction(S, ray, prim, inst, ha.z, ha.w, hb.x, &it, kTex ? &par : nullptr);
                 if (!haveIsect) atomicOr(A.counters + 3, ERR_INTERACTION);
             }
             // isect.Le(-ray.d) -> DiffuseAreaLight::L(intr, w)
@@ -159,8 +198,45 @@ k_shade(const DScene *__restrict__ Sp, const DSampler *__restrict__ Hp, PathArra
         // ---- stage 1: BSDF frame, light choice (integrator.cpp:85-106) ----
         bool nee = false;
         V2 uLight{0, 0}, uScattering{0, 0};
+        EnvRgb texv;
         if (alive) {
             bsdf_init(S, it, &bs);
+            if (kTex && bs.n > 0) {
+                // Kd->Evaluate(*si) of MatteMaterial / PlasticMaterial::ComputeScatteringFunctions
+                // (materials/matte.cpp:49-57, plastic.cpp:49-56): the diffuse lobe is the material's first,
+                // and it is there only when the texture's value is not black
+                const int R0 = S.lobes[bs.first].R;
+                if (R0 <= -2) {
+                    RayDiff rd;
+                    if (bounces == 0) {
+                        const float2 pf = A.pfilm[i];
+                        camera_differentials(S, H, st.index, V2{pf.x, pf.y}, R.wavelength, ray, &rd);
+                    }
+                    texv = tex_evaluate(S, -2 - R0, it, par, bounces == 0 ? &rd : nullptr);
+#ifdef SPTX_TRACE_PATH
+                    if (R.sampleList && bounces == 0) {
+                        V2 ddx, ddy;
+                        uv_differentials(it, par, &rd, &ddx, &ddy);
+                        printf("DEVTRACE i %d p %.9g %.9g %.9g n %.9g %.9g %.9g uv %.9g %.9g\n", i, it.p.x, it.p.y, it.p.z,
+                               it.n.x, it.n.y, it.n.z, par.uv.x, par.uv.y);
+                        printf("DEVTRACE   rxo %.9g %.9g %.9g rxd %.9g %.9g %.9g ryo %.9g %.9g %.9g ryd %.9g %.9g %.9g\n",
+                               rd.rxo.x, rd.rxo.y, rd.rxo.z, rd.rxd.x, rd.rxd.y, rd.rxd.z, rd.ryo.x, rd.ryo.y, rd.ryo.z,
+                               rd.ryd.x, rd.ryd.y, rd.ryd.z);
+                        printf("DEVTRACE   dpdu %.9g %.9g %.9g dpdv %.9g %.9g %.9g dudx %.9g dvdx %.9g dudy %.9g dvdy %.9g\n",
+                               par.dpdu.x, par.dpdu.y, par.dpdu.z, par.dpdv.x, par.dpdv.y, par.dpdv.z, ddx.x, ddx.y, ddy.x, ddy.y);
+                        const float4 a = tex_bin4(S, texv.row[0], texv.row[1], texv.row[2], texv.w[0], texv.w[1], texv.w[2], 0);
+                        const float4 b = tex_bin4(S, texv.row[0], texv.row[1], texv.row[2], texv.w[0], texv.w[1], texv.w[2], 2);
+                        const float4 c = tex_bin4(S, texv.row[0], texv.row[1], texv.row[2], texv.w[0], texv.w[1], texv.w[2], 4);
+                        const float4 d = tex_bin4(S, texv.row[0], texv.row[1], texv.row[2], texv.w[0], texv.w[1], texv.w[2], 6);
+                        printf("DEVTRACE   Kd %.9g %.9g %.9g %.9g\n", a.z, b.z, c.z, d.z);
+                    }
+#endif
+                    if (tex_is_black(S, texv)) {
+                        bs.first += 1;
+                        bs.n -= 1;
+                    }
+                }
+            }
             if (bsdf_num_components<LOBES>(S, bs, noSpec) > 0 && S.n_lights > 0) {
                 // the five values next-event estimation consumes (Get1D, Get2D, Get2D) are pure
                 // functions of (index, dimension): evaluated together, consumed as the reference does
@@ -197,18 +273,19 @@ k_shade(const DScene *__restrict__ Sp, const DSampler *__restrict__ Hp, PathArra
             const sptx_light &Lt = S.lights[lightNum];
             delta = Lt.type == SPTX_LIGHT_POINT;
             RefPoint ref{it.p, it.pError, it.n};
-            ls = light_sample_li(S, Lt, ref, uLight);
+            ls = light_sample_li<kShadeEnv>(S, Lt, ref, uLight);
         }
         SPTX_STAGE(4);
         if (nee && ls.pdf > 0 && !ls.black) {
             bsdf_f<LOBES>(S, bs, it.wo, ls.wi, noSpec, &f);
+            if (kTex) tex_patch(&f, texv);
             const float ad = absdot(ls.wi, it.ns);
             const float scatteringPdf = bsdf_pdf<LOBES>(S, bs, it.wo, ls.wi, noSpec);
             const float weight = delta ? 1.f : power_heuristic(ls.pdf, scatteringPdf);
             const Row4 fa = row4(A.fa, i);
             bool fNon = false, liNon = false;
             for (int c = 0; c < 8; ++c) {
-                float4 fv = fsum4<LOBES>(S, f, c), li = li4(S, ls, c);
+                float4 fv = fsum4<LOBES>(S, f, c), li = li4<kShadeEnv>(S, ls, c);
                 fv.x *= ad;
                 fv.y *= ad;
                 fv.z *= ad;
@@ -238,12 +315,13 @@ k_shade(const DScene *__restrict__ Sp, const DSampler *__restrict__ Hp, PathArra
             float sPdf;
             int sType;
             bsdf_sample_f<LOBES>(S, bs, it.wo, uScattering, noSpec, &misD, &sPdf, &sType, &f);
+            if (kTex) tex_patch(&f, texv);
             if (f.n > 0 && sPdf > 0) {
                 float weight = 1.f;
                 bool skip = false;
                 if (!(sType & BSDF_SPECULAR)) {
                     RefPoint ref{it.p, it.pError, it.n};
-                    float lightPdf = light_pdf_li(S, S.lights[lightNum], ref, misD);
+                    float lightPdf = light_pdf_li<kShadeEnv>(S, S.lights[lightNum], ref, misD);
                     if (lightPdf == 0)
                         skip = true;
                     else
@@ -254,7 +332,7 @@ k_shade(const DScene *__restrict__ Sp, const DSampler *__restrict__ Hp, PathArra
                     const sptx_light &Lm = S.lights[lightNum];
                     const int leRow = Lm.spectrum;
                     // an infinite light: Li = Le(ray) if the sampled ray leaves the scene (K4a decides)
-                    const bool envLight = Lm.type == SPTX_LIGHT_INFINITE;
+                    const bool envLight = kShadeEnv && Lm.type == SPTX_LIGHT_INFINITE;
                     EnvRgb envLe;
                     if (envLight) envLe = env_le(S, Lm, misD);
                     const Row4 fb = row4(A.fb, i);
@@ -291,6 +369,7 @@ k_shade(const DScene *__restrict__ Sp, const DSampler *__restrict__ Hp, PathArra
             float pdf;
             int flags;
             bsdf_sample_f<LOBES>(S, bs, it.wo, get2d(H, st), BSDF_ALL, &wi, &pdf, &flags, &f);
+            if (kTex) tex_patch(&f, texv);
             bool fNon = false;
             float maxBeta = 0.f;
             const Row4 bIn = row4(A.beta[betaIn], i), bOut = row4(A.beta[betaIn ^ 1], i);
@@ -372,13 +451,13 @@ __global__ void k_shade_miss(const DScene *__restrict__ Sp, PathArrays A, Render
                              DeviceCounters *cnt) {
     const DScene &S = *Sp;
     const int n = A.counters[kClassCounter0];
-    if (R.nBands > 1 || S.n_infinite > 0)
+    if (R.nBands > 1 || (kShadeEnv && S.n_infinite > 0))
         for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
             const int i = A.qc[k];
             const uint32_t info = A.info[i];
             const int bounces = (int)(info & 0xffu);
             const bool specularBounce = ((info >> 8) & 1u) != 0;
-            if (S.n_infinite > 0 && (bounces == 0 || specularBounce)) {
+            if (kShadeEnv && S.n_infinite > 0 && (bounces == 0 || specularBounce)) {
                 // L += beta * light->Le(ray) over scene.infiniteLights (integrators/path.cpp:96-99)
                 const float4 ra = A.rayA[i], rb = A.rayB[i];
                 const V3 d = mk(ra.w, rb.x, rb.y);

@@ -17,17 +17,18 @@
 
 using namespace sptx;
 
-namespace sptx {  // shade.cu, compiled once per arithmetic mode
-namespace shade_exact {
-int launch_shade(cudaStream_t stream, int smCount, int64_t nPaths, const DScene *dS, const DSampler *dH,
-                 const PathArrays &A, const RenderParams &R, int qi, int betaIn, const ShadePlan &plan,
-                 DeviceCounters *cnt);
-}
-namespace shade_fast {
-int launch_shade(cudaStream_t stream, int smCount, int64_t nPaths, const DScene *dS, const DSampler *dH,
-                 const PathArrays &A, const RenderParams &R, int qi, int betaIn, const ShadePlan &plan,
-                 DeviceCounters *cnt);
-}
+namespace sptx {  // shade.cu, compiled once per arithmetic mode, with and without Light "infinite"
+#define SPTX_DECLARE_SHADE(ns)                                                                                  \
+    namespace ns {                                                                                              \
+    int launch_shade(cudaStream_t stream, int smCount, int64_t nPaths, const DScene *dS, const DSampler *dH,   \
+                     const PathArrays &A, const RenderParams &R, int qi, int betaIn, const ShadePlan &plan,    \
+                     DeviceCounters *cnt);                                                                      \
+    }
+SPTX_DECLARE_SHADE(shade_exact)
+SPTX_DECLARE_SHADE(shade_fast)
+SPTX_DECLARE_SHADE(shade_exact_env)
+SPTX_DECLARE_SHADE(shade_fast_env)
+#undef SPTX_DECLARE_SHADE
 }  // namespace sptx
 
 static std::string g_last_error;
@@ -57,6 +58,7 @@ struct sptx_ctx {
     // descriptors to non-inlined device functions does not copy them to each thread's stack
     DScene *dS = nullptr;
     DSampler *dH = nullptr;
+    DCamera *dC = nullptr;
     // pinned staging for film downloads, and the device pixel list of the last render region
     float *dFilmSplit = nullptr;  // [P][31] contrib + [P] weight, the download layout
     size_t dFilmSplitFloats = 0;
@@ -291,6 +293,7 @@ extern "C" void sptx_destroy(sptx_ctx *ctx) {
     for (void *s : ctx->scratch)
         if (s) cudaFree(s);
     if (ctx->dH) cudaFree(ctx->dH);
+    if (ctx->dC) cudaFree(ctx->dC);
     cudaEventDestroy(ctx->ev0);
     cudaEventDestroy(ctx->ev1);
     cudaEventDestroy(ctx->ev2);
@@ -412,11 +415,39 @@ static int validate_scene(sptx_ctx *ctx, const sptx_scene_desc *sc) {
             return fail(ctx, SPTX_EUNSUPPORTED,
                         "sptx_upload_scene: material with %d non-specular lobes (max %d)", nonSpecular,
                         kMaxTerms);
+        // image textures: the value of a material's FIRST lobe, a Lambert lobe (the Kd of matte / plastic)
+        for (int l = 0; l < m.n_lobes; ++l) {
+            const sptx_lobe &lb = sc->lobes[m.first_lobe + l];
+            if (lb.R > -2) continue;
+            if (l != 0 || lb.type != SPTX_LOBE_LAMBERT)
+                return fail(ctx, SPTX_EUNSUPPORTED,
+                            "sptx_upload_scene: an image texture on a lobe that is not the material's first, Lambert lobe");
+            if (sc->sampler.type == SPTX_SAMPLER_RANDOM || sc->sampler.type == SPTX_SAMPLER_ZEROTWO)
+                return fail(ctx, SPTX_EUNSUPPORTED,
+                            "sptx_upload_scene: image textures with the tile-serial samplers (random, 02sequence)");
+            const int64_t off = -2 - (int64_t)lb.R;
+            REQ(sc->tex_floats && off >= 0 && off + 16 <= sc->n_tex_floats, "texture block offset");
+            auto geti = [&](int64_t k) {
+                int32_t v;
+                memcpy(&v, sc->tex_floats + off + k, 4);
+                return v;
+            };
+            const int levels = geti(0);
+            REQ(levels >= 1 && levels <= 32 && off + 16 + 3 * (int64_t)levels <= sc->n_tex_floats, "texture levels");
+            REQ(geti(1) >= 0 && geti(1) <= 2, "texture wrap mode");
+            REQ(geti(8) >= 0 && (int64_t)geti(8) + 7 <= sc->n_spectra, "texture without its seven RGB basis rows");
+            REQ(geti(9) >= 0 && (int64_t)geti(9) + 128 <= sc->n_tex_floats, "texture EWA weight table");
+            for (int lv = 0; lv < levels; ++lv) {
+                const int64_t us = geti(16 + 3 * lv), vs = geti(16 + 3 * lv + 1), to = geti(16 + 3 * lv + 2);
+                REQ(us >= 1 && vs >= 1 && to >= 16 && off + to + 3 * us * vs <= sc->n_tex_floats, "texture level");
+            }
+        }
     }
     for (int64_t i = 0; i < sc->n_lobes; ++i) {
         const sptx_lobe &l = sc->lobes[i];
         REQ(l.type >= SPTX_LOBE_LAMBERT && l.type <= SPTX_LOBE_FRESNEL_BLEND, "lobe type");
-        REQ(l.R >= -1 && l.T >= -1 && l.fr_eta_i >= -1 && l.fr_eta_t >= -1 && l.fr_k >= -1 &&
+        const bool textured = l.R <= -2;  // R = SPTX_TEX_ROW(offset): checked with the materials below
+        REQ(l.T >= -1 && l.fr_eta_i >= -1 && l.fr_eta_t >= -1 && l.fr_k >= -1 &&
                 l.R < sc->n_spectra && l.T < sc->n_spectra && l.fr_eta_i < sc->n_spectra &&
                 l.fr_eta_t < sc->n_spectra && l.fr_k < sc->n_spectra,
             "lobe spectrum row out of range");
@@ -426,7 +457,7 @@ static int validate_scene(sptx_ctx *ctx, const sptx_scene_desc *sc) {
                             l.type == SPTX_LOBE_FRESNEL_BLEND;
         const bool needsR = l.type != SPTX_LOBE_SPECULAR_TRANS && l.type != SPTX_LOBE_LAMBERT_TRANS &&
                             l.type != SPTX_LOBE_MICROFACET_TRANS;
-        REQ(!needsR || l.R >= 0, "lobe without its reflectance row");
+        REQ(!needsR || l.R >= 0 || textured, "lobe without its reflectance row");
         REQ(!needsT || l.T >= 0, "lobe without its transmittance row");
         if (l.fresnel == SPTX_FRESNEL_CONDUCTOR &&
             (l.type == SPTX_LOBE_SPECULAR_REFL || l.type == SPTX_LOBE_MICROFACET_REFL))
@@ -697,7 +728,7 @@ extern "C" int sptx_upload_scene(sptx_ctx *ctx, const sptx_scene_desc *sc) {
             std::vector<int> sig;
             for (int l = 0; l < sc->materials[m].n_lobes; ++l) {
                 const sptx_lobe &L = sc->lobes[sc->materials[m].first_lobe + l];
-                sig.push_back(L.type * 16 + L.fresnel);
+                sig.push_back(L.type * 16 + L.fresnel + (L.R <= -2 ? 8 : 0));
             }
             size_t k = 0;
             while (k < sigs.size() && sigs[k] != sig) ++k;
@@ -720,18 +751,26 @@ extern "C" int sptx_upload_scene(sptx_ctx *ctx, const sptx_scene_desc *sc) {
             for (int l = 0; l < sc->materials[m].n_lobes; ++l) {
                 const int ty = sc->lobes[sc->materials[m].first_lobe + l].type;
                 classLobes[cls] |= 1 << ty;
+                if (sc->lobes[sc->materials[m].first_lobe + l].R <= -2) classLobes[cls] |= kTexturedLobes;
                 if (!((kSpecularLobes >> ty) & 1)) ++nonSpecular;
             }
             classTerms[cls] = std::max(classTerms[cls], nonSpecular);
         }
-        for (int c = 0; c < kShadeClasses; ++c)
+        for (int c = 0; c < kShadeClasses; ++c) {
             ctx->shadePlan.variant[c] = (c > 0 && classUsed[c]) ? shade_variant_for(classLobes[c], classTerms[c]) : -1;
+            if (c > 0 && classUsed[c] && ctx->shadePlan.variant[c] < 0)
+                return fail(ctx, SPTX_EUNSUPPORTED,
+                            "sptx_upload_scene: a textured material shares its shading class with lobe types the "
+                            "textured variant does not evaluate (more than %d lobe signatures in the scene)",
+                            kShadeClasses - 1);
+        }
         if ((rc = upload(ctx, pool, primClass.data(), (int64_t)primClass.size(), &S.prim_class))) return rc;
     }
     if ((rc = upload(ctx, pool, sc->spectra, SPTX_SPECTRUM_STRIDE * sc->n_spectra, &S.spectra))) return rc;
     if ((rc = upload(ctx, pool, sc->lights, sc->n_lights, &S.lights))) return rc;
     S.n_lights = (int)sc->n_lights;
     if ((rc = upload(ctx, pool, sc->env_floats, sc->n_env_floats, &S.env))) return rc;
+    if ((rc = upload(ctx, pool, sc->tex_floats, sc->n_tex_floats, &S.tex))) return rc;
     S.n_infinite = 0;
     for (int64_t i = 0; i < sc->n_lights; ++i)
         if (sc->lights[i].type == SPTX_LIGHT_INFINITE) {
@@ -918,7 +957,10 @@ extern "C" int sptx_upload_scene(sptx_ctx *ctx, const sptx_scene_desc *sc) {
     if (!ctx->dS) {
         CK(cudaMalloc(&ctx->dS, sizeof(DScene)));
         CK(cudaMalloc(&ctx->dH, sizeof(DSampler)));
+        CK(cudaMalloc(&ctx->dC, sizeof(DCamera)));
     }
+    ctx->S.camera = ctx->dC;
+    CK(cudaMemcpyAsync(ctx->dC, &ctx->C, sizeof(DCamera), cudaMemcpyHostToDevice, ctx->stream));
     CK(cudaMemcpyAsync(ctx->dS, &ctx->S, sizeof(DScene), cudaMemcpyHostToDevice, ctx->stream));
     CK(cudaMemcpyAsync(ctx->dH, &ctx->H, sizeof(DSampler), cudaMemcpyHostToDevice, ctx->stream));
     CK(cudaGetLastError());
@@ -1177,7 +1219,9 @@ static int render_pixels(sptx_ctx *ctx, int s0, int s1, const int *dSampleList =
                         k_intersect<false><<<g, kBlock, 0, ctx->stream>>>(ctx->S, A, qi, ctx->dCnt);
                     toc();
                     tic(2);
-                    const int nk = (ctx->shadeExact ? shade_exact::launch_shade : shade_fast::launch_shade)(
+                    const bool env = ctx->S.n_infinite > 0;
+                    const int nk = (ctx->shadeExact ? (env ? shade_exact_env::launch_shade : shade_exact::launch_shade)
+                                                    : (env ? shade_fast_env::launch_shade : shade_fast::launch_shade))(
                         ctx->stream, ctx->smCount, nPaths, ctx->dS, ctx->dH, A, R, qi, betaIn, ctx->shadePlan,
                         ctx->dCnt);
                     toc();

@@ -48,23 +48,27 @@ enum { ERR_DIM_OVERFLOW = 1, ERR_INTERACTION = 2, ERR_TERMS = 4 };
 // The kernel variants: lobe types a variant's code can evaluate, and how many non-specular lobes
 // (terms of BSDF::f) one of its materials may have.  sptx_upload_scene maps every shading class to
 // the first variant that covers its materials (shade_variant_for).
-constexpr int kNumShadeVariants = 4;
+constexpr int kNumShadeVariants = 5;
 constexpr int kVariantLobes[kNumShadeVariants] = {
     1 << SPTX_LOBE_LAMBERT,                                    // matte
     kSpecularLobes,                                            // glass, mirror: no light sampling
     (1 << SPTX_LOBE_LAMBERT) | (1 << SPTX_LOBE_MICROFACET_REFL),  // plastic, metal
-    kAllLobes};
-constexpr int kVariantTerms[kNumShadeVariants] = {1, 1, 2, kMaxTerms};
+    kAllLobes,
+    // matte / plastic with an imagemap Kd (the only variant that evaluates textures)
+    (1 << SPTX_LOBE_LAMBERT) | (1 << SPTX_LOBE_MICROFACET_REFL) | kTexturedLobes};
+constexpr int kVariantTerms[kNumShadeVariants] = {1, 1, 2, kMaxTerms, 2};
 
 // Which variant K3 runs for each shading class (-1: no primitive of the scene is in the class).
 struct ShadePlan {
     int variant[kShadeClasses];
 };
-// First variant whose lobe set covers `lobeMask` and whose term list holds `nonSpecular` terms.
+// First variant whose lobe set covers `lobeMask` (lobe types, | kTexturedLobes when a material of the
+// class has a textured lobe) and whose term list holds `nonSpecular` terms; -1: none does (textured
+// materials with lobes outside the textured variant).
 inline int shade_variant_for(int lobeMask, int nonSpecular) {
     for (int v = 0; v < kNumShadeVariants; ++v)
         if ((lobeMask & ~kVariantLobes[v]) == 0 && nonSpecular <= kVariantTerms[v]) return v;
-    return kNumShadeVariants - 1;
+    return (lobeMask & kTexturedLobes) ? -1 : 3;
 }
 
 struct RenderParams {

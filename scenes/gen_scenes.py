@@ -8,6 +8,7 @@ names:  cornell       C2: spectral Cornell box (diffuse + glass + metal), perspe
         instanced     C4: N x N displaced grid mesh, instanced on a lattice
         zoo           one of every supported material / shape / light / camera feature (parity)
         envbox        open scene under Light "infinite" (env=const | env=map), SURVEY 8(f) rank 3
+        texbox        Texture "imagemap" Kd on matte / plastic (lens=R: thin-lens camera), 8(f) rank 3
         furnace_point / furnace_area   the known-answer scenes of the reference's
                       src/tests/analytic_scenes.cpp:68-165 written as scene files
 keys:   res=<w>[x<h>] spp=<n> maxdepth=<n> strategy=<uniform|power|spatial> sampler=<halton|random>
@@ -68,9 +69,10 @@ def header(opts, camera, name):
     return "\n".join(s) + "\n"
 
 
-def quad(p0, p1, p2, p3):
+def quad(p0, p1, p2, p3, uv=None):
     pts = " ".join(f"{c:g}" for p in (p0, p1, p2, p3) for c in p)
-    return f'Shape "trianglemesh" "integer indices" [0 1 2 0 2 3] "point P" [{pts}]\n'
+    st = f' "float uv" [{" ".join(f"{c:g}" for c in uv)}]' if uv else ""
+    return f'Shape "trianglemesh" "integer indices" [0 1 2 0 2 3] "point P" [{pts}]{st}\n'
 
 
 def cornell_world():
@@ -216,6 +218,52 @@ def envbox(opts, out):
           '  Shape "sphere" "float radius" [.4]\nAttributeEnd\n')
     s += ('AttributeBegin\n  Material "metal" "float roughness" [.01]\n  Translate 1 -.5 -.2\n'
           '  Shape "sphere" "float radius" [.5]\nAttributeEnd\n')
+    return s + "WorldEnd\n"
+
+
+def texbox(opts, out):
+    """Image textures (src/textures/imagemap.h) as the Kd of matte and plastic: a 20 x 12 procedural
+    PFM (not a power of two, so the MIPMap resamples it) looked up with the EWA filter (floor, tiled
+    by uscale / vscale, wrap "repeat"), trilinearly (a plastic sphere, wrap "clamp") and with wrap
+    "black" (a matte sphere: outside [0,1]^2 the texture, hence the BSDF, is black).  lens=R gives
+    the camera a thin lens (the other branch of PerspectiveCamera::GenerateRayDifferential),
+    camera=realistic the double-Gauss RealisticCamera (Camera::GenerateRayDifferential)."""
+    name = os.path.splitext(os.path.basename(out))[0]
+    cam = 'LookAt 0 1.1 4.0  0 -.3 0  0 1 0\nCamera "perspective" "float fov" [40]'
+    if float(opts.get("lens", 0)) > 0:
+        cam += f' "float lensradius" [{float(opts["lens"]):g}] "float focaldistance" [4.2]'
+    if opts.get("camera") == "realistic":  # Camera::GenerateRayDifferential: offset rays traced through the lens
+        with open(os.path.join(os.path.dirname(os.path.abspath(out)), "dgauss.50mm.dat"), "w") as f:
+            f.write(DGAUSS_50MM)
+        cam = ('LookAt 0 1.1 4.0  0 -.3 0  0 1 0\nCamera "realistic" "string lensfile" "dgauss.50mm.dat" '
+               '"float aperturediameter" [8] "float focusdistance" [4.2] "bool simpleweighting" "true"')
+    s = header(opts, cam, name) + "WorldBegin\n"
+    w, h = 20, 12
+    v, u = np.meshgrid((np.arange(h) + .5) / h, (np.arange(w) + .5) / w, indexing="ij")
+    img = np.zeros((h, w, 3), np.float32)
+    check = ((np.floor(u * 5) + np.floor(v * 3)) % 2).astype(np.float32)
+    img[..., 0] = .15 + .7 * check
+    img[..., 1] = .2 + .6 * u
+    img[..., 2] = .75 - .6 * v * check
+    img[5:7, 8:12] = 0.                                 # a black patch: no diffuse lobe there
+    write_pfm(os.path.join(os.path.dirname(os.path.abspath(out)), name + "_tex.pfm"), img)
+    tex = f'"string filename" "{name}_tex.pfm"'
+    s += f'Texture "floor" "spectrum" "imagemap" {tex} "float uscale" [3] "float vscale" [2.5] "float udelta" [.25]\n'
+    s += f'Texture "ball" "spectrum" "imagemap" {tex} "bool trilinear" "true" "string wrap" "clamp" "float uscale" [2]\n'
+    s += f'Texture "patch" "spectrum" "imagemap" {tex} "string wrap" "black" "float uscale" [1.6] "float vscale" [1.6] "float vdelta" [-.3] "float maxanisotropy" [4]\n'
+    s += 'AttributeBegin\n  AreaLightSource "diffuse" "blackbody L" [5500 18]\n'
+    s += "  " + quad((-.3, 1.6, -.3), (.3, 1.6, -.3), (.3, 1.6, .3), (-.3, 1.6, .3)) + "AttributeEnd\n"
+    s += 'LightSource "point" "point from" [-2 1.5 2] "blackbody I" [4000 6]\n'
+    s += 'AttributeBegin\n  Material "matte" "texture Kd" "floor"\n'
+    s += "  " + quad((-3, -1, 3), (3, -1, 3), (3, -1, -6), (-3, -1, -6), uv=(0, 0, 1, 0, 1, 1, 0, 1)) + "AttributeEnd\n"
+    s += f'AttributeBegin\n  Material "matte" "spectrum Kd" {WHITE}\n'
+    s += "  " + quad((-3, -1, -6), (3, -1, -6), (3, 3, -6), (-3, 3, -6)) + "AttributeEnd\n"
+    s += ('AttributeBegin\n  Material "plastic" "texture Kd" "ball" "spectrum Ks" [400 .3 700 .3] "float roughness" [.08]\n'
+          '  Translate -.9 -.45 .2\n  Rotate 30 0 1 0\n  Shape "sphere" "float radius" [.55]\nAttributeEnd\n')
+    s += ('AttributeBegin\n  Material "matte" "texture Kd" "patch"\n  Translate .9 -.5 -.3\n  Rotate -70 1 0 0\n'
+          '  Shape "sphere" "float radius" [.5]\nAttributeEnd\n')
+    s += ('AttributeBegin\n  Material "glass" "float index" [1.5]\n  Translate .1 -.7 1.2\n'
+          '  Shape "sphere" "float radius" [.3]\nAttributeEnd\n')
     return s + "WorldEnd\n"
 
 
@@ -376,6 +424,8 @@ def main(argv):
         text = zoo(opts, out)
     elif name == "envbox":
         text = envbox(opts, out)
+    elif name == "texbox":
+        text = texbox(opts, out)
     elif name == "furnace_point":
         text = furnace(opts, out, False)
     elif name == "furnace_area":
