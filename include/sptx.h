@@ -446,8 +446,15 @@ int sptx_write_dat(const char *path, int width, int height, const double *planes
 
 int sptx_get_counters(sptx_ctx *ctx, sptx_counters *out);
 int sptx_reset_counters(sptx_ctx *ctx);
-/* Named integer options: "count_visits" (0/1). */
+/* Named integer options: "count_visits" (0/1), "device_bvh" (0/1), "shade_exact" (0/1), and
+ * "ray_sort" for sptx_intersect_batch / _device: 0 = rays are walked in the caller's order, 1 = in the
+ * order of a key made of the origin's cell in the scene bounds and the direction's octant (one radix
+ * sort on the device; results stay at the ray's own index and are identical), 2 (default) = like 1
+ * for batches of >= 65536 rays (smaller ones do not repay the sort).  sptx_intersect_batch_noalloc
+ * never sorts (the sort's scratch is allocated). */
 int sptx_set_option(sptx_ctx *ctx, const char *name, int64_t value);
+/* 1 when the last sptx_intersect_batch / _device call walked its rays in sorted order. */
+int sptx_last_batch_sorted(sptx_ctx *ctx);
 /* Max paths in flight per wavefront pass (0 = default). */
 int sptx_set_wavefront_size(sptx_ctx *ctx, int64_t max_paths);
 

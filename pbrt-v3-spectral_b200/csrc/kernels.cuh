@@ -110,9 +110,11 @@ k_intersect(DScene S, PathArrays A, int qi, DeviceCounters *cnt) {
 // ---- stand-alone ray batches (sptx_intersect_batch) ---------------------------
 template <bool ANY, bool COUNT>
 __global__ void __launch_bounds__(kBlock, SPTX_BATCH_BLOCKS)
-k_ray_batch(DScene S, const sptx_ray *rays, int64_t n, sptx_hit *hits) {
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
-         i += (int64_t)gridDim.x * blockDim.x) {
+k_ray_batch(DScene S, const sptx_ray *rays, const int *order, int64_t n, sptx_hit *hits) {
+    for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < n;
+         k += (int64_t)gridDim.x * blockDim.x) {
+        // `order` (or NULL): the walk order of a binned batch; results land at the ray's own index
+        const int64_t i = order ? (int64_t)order[k] : k;
         const float4 *rp = reinterpret_cast<const float4 *>(rays + i);
         float4 a = __ldg(rp), b = __ldg(rp + 1);
         Ray ray{mk(a.x, a.y, a.z), mk(b.x, b.y, b.z), a.w};

@@ -78,8 +78,8 @@ struct sptx_ctx {
         void *ptr;
     };
     std::vector<PeerMap> peerMaps;
-    void *scratch[3] = {nullptr, nullptr, nullptr};
-    size_t scratchBytes[3] = {0, 0, 0};
+    void *scratch[4] = {nullptr, nullptr, nullptr, nullptr};  // [3]: ray-sort keys, order and cub's scratch
+    size_t scratchBytes[4] = {0, 0, 0, 0};
     DFilm F;
     PathArrays A;
     sptx_integrator integ;
@@ -97,6 +97,9 @@ struct sptx_ctx {
     // device (csrc/lbvh.cuh); build_ms = device time of the last build
     bool deviceBvh = false;
     double bvhBuildMs = 0.0;
+    // "ray_sort": 0 never, 1 always, 2 (default) batches of kRaySortMin rays and more
+    int raySort = 2;
+    int lastBatchSorted = 0;
     std::vector<cudaEvent_t> evPool;
     int smCount = 148;
 };
@@ -311,6 +314,11 @@ extern "C" int sptx_set_option(sptx_ctx *ctx, const char *name, int64_t value) {
     }
     if (!strcmp(name, "device_bvh")) {  // takes effect at the next sptx_upload_scene
         ctx->deviceBvh = value != 0;
+        return SPTX_OK;
+    }
+    if (!strcmp(name, "ray_sort")) {  // sptx_intersect_batch*: order the rays by origin cell / direction first
+        if (value < 0 || value > 2) return fail(ctx, SPTX_EINVAL, "sptx_set_option: ray_sort is 0, 1 or 2");
+        ctx->raySort = (int)value;
         return SPTX_OK;
     }
     if (!strcmp(name, "shade_exact")) {  // 1: K3 with the reference's roundings; 0: the fast build of K3
@@ -1653,8 +1661,54 @@ extern "C" int sptx_reset_counters(sptx_ctx *ctx) {
 
 // ---- ray batches ----------------------------------------------------------------------------
 
-extern "C" int sptx_intersect_batch_device(sptx_ctx *ctx, const void *d_rays, int64_t n, void *d_hits,
-                                           int any_hit, int with_counters, float *ms) {
+// Ray binning (north_star (2), "incoherent batches"): a thread-per-ray walk of a deep two-level BVH
+// lives on L1 / L2 latency, and a warp of unrelated rays touches 32 unrelated node chains.  Large
+// batches are therefore walked in the order of a 32-bit key -- the origin's cell in a 32^3 grid over
+// the scene bounds (Morton order), then the direction's cell on a 16 x 16 octahedral map, then the
+// origin's position inside its cell -- found with one cub radix sort of (key, ray index); each thread
+// reads ray order[i] and writes hit order[i], so the caller's arrays keep their order and every ray's
+// result (and visit counts) is what the unsorted walk gives.  Measured on C4, 2^22 rays, sort
+// included: incoherent closest 5.81 -> 2.19 ms, any-hit 4.74 -> 1.86 ms; camera rays in scanline
+// order (one origin: the key is the direction cell) 3.09 -> 2.69 ms.  Other key layouts tried:
+// [256^3 origin][direction] 2.30 ms, [64^3 origin][direction][fine origin] 2.31 ms.
+SPTX_DEV uint32_t interleave3(uint32_t x, uint32_t y, uint32_t z, int bits) {
+    uint32_t m = 0;
+    for (int bit = bits - 1; bit >= 0; --bit)
+        m = (m << 3) | (((x >> bit) & 1u) << 2) | (((y >> bit) & 1u) << 1) | ((z >> bit) & 1u);
+    return m;
+}
+__global__ void k_ray_keys(DScene S, const sptx_ray *rays, int64_t n, uint32_t *keys, int *order) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        const float4 *rp = reinterpret_cast<const float4 *>(rays + i);
+        const float4 a = __ldg(rp), b = __ldg(rp + 1);
+        const float o[3] = {a.x, a.y, a.z};
+        uint32_t cell[3];
+        for (int k = 0; k < 3; ++k) {
+            const float ext = S.wb_max[k] - S.wb_min[k];
+            float t = ext > 0.f ? (o[k] - S.wb_min[k]) / ext : 0.f;
+            t = fminf(fmaxf(t, 0.f), 1.f);  // (NaN -> 0)
+            cell[k] = min((uint32_t)(t * 256.f), 255u);
+        }
+        const float l1 = fabsf(b.x) + fabsf(b.y) + fabsf(b.z);
+        float px = l1 > 0.f ? b.x / l1 : 0.f, py = l1 > 0.f ? b.y / l1 : 0.f;
+        if (b.z < 0.f) {  // fold the lower hemisphere outwards
+            const float qx = (1.f - fabsf(py)) * (px >= 0.f ? 1.f : -1.f), qy = (1.f - fabsf(px)) * (py >= 0.f ? 1.f : -1.f);
+            px = qx;
+            py = qy;
+        }
+        const uint32_t du = min((uint32_t)(fminf(fmaxf(px * .5f + .5f, 0.f), 1.f) * 16.f), 15u);
+        const uint32_t dv = min((uint32_t)(fminf(fmaxf(py * .5f + .5f, 0.f), 1.f) * 16.f), 15u);
+        uint32_t dm = 0;
+        for (int bit = 3; bit >= 0; --bit) dm = (dm << 2) | (((du >> bit) & 1u) << 1) | ((dv >> bit) & 1u);
+        keys[i] = (interleave3(cell[0] >> 3, cell[1] >> 3, cell[2] >> 3, 5) << 17) | (dm << 9) |
+                  interleave3(cell[0] & 7u, cell[1] & 7u, cell[2] & 7u, 3);
+        order[i] = (int)i;
+    }
+}
+constexpr int64_t kRaySortMin = 1 << 16;
+
+static int intersect_batch_impl(sptx_ctx *ctx, const void *d_rays, int64_t n, void *d_hits, int any_hit,
+                                int with_counters, float *ms, bool maySort) {
     if (!ctx) return fail(nullptr, SPTX_EINVAL, "sptx_intersect_batch: ctx is NULL");
     if (!ctx->haveScene) return fail(ctx, SPTX_ESTATE, "sptx_intersect_batch: no scene uploaded");
     if (n < 0 || (n > 0 && (!d_rays || !d_hits))) return fail(ctx, SPTX_EINVAL, "sptx_intersect_batch: bad arguments");
@@ -1666,17 +1720,45 @@ extern "C" int sptx_intersect_batch_device(sptx_ctx *ctx, const void *d_rays, in
     const sptx_ray *r = (const sptx_ray *)d_rays;
     sptx_hit *h = (sptx_hit *)d_hits;
     const int g = grid_for(ctx, n);
+    const int *order = nullptr;
+    int launches = 1;
+    ctx->lastBatchSorted = 0;
+    const bool trySort = maySort && n <= 0x7fffffff && (ctx->raySort == 1 || (ctx->raySort == 2 && n >= kRaySortMin));
+    uint32_t *keys = nullptr, *keysSorted = nullptr;
+    int *ord = nullptr, *ordSorted = nullptr;
+    void *tmp = nullptr;
+    size_t tmpBytes = 0;
+    if (trySort) {  // (scratch first: growing it drains the stream)
+        cub::DeviceRadixSort::SortPairs(nullptr, tmpBytes, keys, keysSorted, ord, ordSorted, (int)n, 0, 32, ctx->stream);
+        const size_t arr = ((size_t)n * 4 + 255) & ~(size_t)255;
+        void *base = nullptr;
+        int rc = ctx_scratch(ctx, 3, 4 * arr + tmpBytes, &base);
+        if (rc) return rc;
+        unsigned char *b = (unsigned char *)base;
+        keys = (uint32_t *)b;
+        keysSorted = (uint32_t *)(b + arr);
+        ord = (int *)(b + 2 * arr);
+        ordSorted = (int *)(b + 3 * arr);
+        tmp = b + 4 * arr;
+    }
     cudaEventRecord(ctx->ev0, ctx->stream);
+    if (trySort) {
+        k_ray_keys<<<g, kBlock, 0, ctx->stream>>>(ctx->S, r, n, keys, ord);
+        cub::DeviceRadixSort::SortPairs(tmp, tmpBytes, keys, keysSorted, ord, ordSorted, (int)n, 0, 32, ctx->stream);
+        launches += 1 + 5;  // (cub: histogram + one pass per 8 key bits)
+        order = ordSorted;
+        ctx->lastBatchSorted = 1;
+    }
     if (any_hit) {
         if (with_counters)
-            k_ray_batch<true, true><<<g, kBlock, 0, ctx->stream>>>(ctx->S, r, n, h);
+            k_ray_batch<true, true><<<g, kBlock, 0, ctx->stream>>>(ctx->S, r, order, n, h);
         else
-            k_ray_batch<true, false><<<g, kBlock, 0, ctx->stream>>>(ctx->S, r, n, h);
+            k_ray_batch<true, false><<<g, kBlock, 0, ctx->stream>>>(ctx->S, r, order, n, h);
     } else {
         if (with_counters)
-            k_ray_batch<false, true><<<g, kBlock, 0, ctx->stream>>>(ctx->S, r, n, h);
+            k_ray_batch<false, true><<<g, kBlock, 0, ctx->stream>>>(ctx->S, r, order, n, h);
         else
-            k_ray_batch<false, false><<<g, kBlock, 0, ctx->stream>>>(ctx->S, r, n, h);
+            k_ray_batch<false, false><<<g, kBlock, 0, ctx->stream>>>(ctx->S, r, order, n, h);
     }
     cudaEventRecord(ctx->ev1, ctx->stream);
     CK(cudaStreamSynchronize(ctx->stream));
@@ -1684,12 +1766,19 @@ extern "C" int sptx_intersect_batch_device(sptx_ctx *ctx, const void *d_rays, in
     float t = 0.f;
     cudaEventElapsedTime(&t, ctx->ev0, ctx->ev1);
     if (ms) *ms = t;
-    ctx->counters.kernel_launches += 1;
+    ctx->counters.kernel_launches += launches;
     ctx->counters.traverse_ms += t;
     ctx->counters.kernel_ms[6] += t;
     ctx->counters.kernel_count[6] += 1;
     return SPTX_OK;
 }
+
+extern "C" int sptx_intersect_batch_device(sptx_ctx *ctx, const void *d_rays, int64_t n, void *d_hits,
+                                           int any_hit, int with_counters, float *ms) {
+    return intersect_batch_impl(ctx, d_rays, n, d_hits, any_hit, with_counters, ms, true);
+}
+
+extern "C" int sptx_last_batch_sorted(sptx_ctx *ctx) { return ctx ? ctx->lastBatchSorted : 0; }
 
 extern "C" int sptx_intersect_batch(sptx_ctx *ctx, const sptx_ray *rays, int64_t n, sptx_hit *hits,
                                     int any_hit, int with_counters) {
@@ -1757,7 +1846,7 @@ extern "C" int sptx_intersect_batch_noalloc(sptx_ctx *ctx, const sptx_ray *rays,
     sptx_ray *dR = (sptx_ray *)base;
     sptx_hit *dH = (sptx_hit *)((unsigned char *)base + (size_t)SPTX_NOALLOC_MAX_RAYS * sizeof(sptx_ray));
     CK(cudaMemcpyAsync(dR, rays, (size_t)n * sizeof(sptx_ray), cudaMemcpyHostToDevice, ctx->stream));
-    rc = sptx_intersect_batch_device(ctx, dR, n, dH, any_hit, 0, nullptr);
+    rc = intersect_batch_impl(ctx, dR, n, dH, any_hit, 0, nullptr, false);  // (no ray sort: its scratch is cudaMalloc'd)
     if (rc) return rc;
     CK(cudaMemcpyAsync(hits, dH, (size_t)n * sizeof(sptx_hit), cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));

@@ -147,8 +147,15 @@ def c4(n=1 << 24, n_cpu=1 << 20, device_bvh=False):
             # The instanced BVH (11 MB) and the top level stay in L2 (126 MB): the node / triangle bytes
             # are L2 traffic, only the rays and hit records (48 B per ray) come from HBM -- so the
             # algorithmic rate is set against the L2 bandwidth, with the HBM share beside it.
+            binned = ctx.last_batch_sorted()
+            # the other walk order, for the record: forced on where the library left it off and vice versa
+            ctx.set_option("ray_sort", 0 if binned else 1)
+            ctx.intersect_device(d_rays.data_ptr(), n, d_hits.data_ptr(), any_hit=any_hit)
+            ms_other = min(ctx.intersect_device(d_rays.data_ptr(), n, d_hits.data_ptr(), any_hit=any_hit)
+                           for _ in range(3))
+            ctx.set_option("ray_sort", 2)
             res["batches"][f"{name}/{'any' if any_hit else 'closest'}"] = {
-                "ms": ms, "mrays_per_s": n / ms * 1e-3, "hit_rate": float((hits["prim"] >= 0).mean()),
+                "ms": ms, "rays_binned": binned, "ms_unbinned" if binned else "ms_binned": ms_other, "mrays_per_s": n / ms * 1e-3, "hit_rate": float((hits["prim"] >= 0).mean()),
                 "nodes_per_ray": nodes, "tests_per_ray": tests, "algorithmic_bytes_per_ray": bytes_per_ray,
                 "achieved_gbs": gbs, "bound": "l2", "l2_peak_gbs": l2_peak(), "frac_of_l2_peak": gbs / l2_peak(),
                 "hbm_gbs_rays_and_hits": 48.0 * n / (ms * 1e-3) * 1e-9,
