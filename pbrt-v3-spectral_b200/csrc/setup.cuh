@@ -201,7 +201,20 @@ __global__ void k_sampler_eval(DSampler H, const int *px, const int *py, const i
             index = sobol_interval_to_index(H, (uint64_t)sample[i], px[i] - H.sb[0], py[i] - H.sb[1]);
         else
             index = halton_pixel_offset(H.s, px[i], py[i]) + (uint64_t)sample[i] * (uint64_t)H.s.sample_stride;
-        out[i] = halton_sample(H, index, dim[i]);
+        const float v = halton_sample(H, index, dim[i]);
+        // the interleaved form the shading kernel uses must give the same bits
+        float v5[5], v2[2];
+        const int d5 = min(dim[i], H.s.n_dims - 5), d2 = min(dim[i], H.s.n_dims - 2);
+        bool same = true;
+        if (d5 >= 0) {
+            halton_n<5>(H, index, d5, v5);
+            same = same && __float_as_uint(v5[dim[i] - d5]) == __float_as_uint(v);
+        }
+        if (d2 >= 0) {
+            halton_n<2>(H, index, d2, v2);
+            same = same && __float_as_uint(v2[dim[i] - d2]) == __float_as_uint(v);
+        }
+        out[i] = same ? v : __int_as_float(0x7fc00000);
     }
 }
 

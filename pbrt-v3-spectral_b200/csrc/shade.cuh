@@ -37,6 +37,19 @@ SPTX_DEV bool any_nonzero4(float4 v, int c) {
 // instructions later, by which time it would otherwise be a DRAM round trip).
 SPTX_DEV void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 
+// Asynchronous global -> shared copies of one thread's own slots (LDGSTS).  The copies of a thread
+// become visible to THAT thread after its wait; no other thread reads the slots, so no barrier.
+SPTX_DEV void cp_async16(void *smem, const void *g) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(smem)), "l"(g));
+}
+SPTX_DEV void cp_async8(void *smem, const void *g) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((unsigned)__cvta_generic_to_shared(smem)), "l"(g));
+}
+SPTX_DEV void cp_async4(void *smem, const void *g) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((unsigned)__cvta_generic_to_shared(smem)), "l"(g));
+}
+SPTX_DEV void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
 // The vertex is cut into stages with a block barrier between them.  The
 // barriers are not needed for correctness: they keep the SM's warps inside the
 // same few KB of code, so that the instruction cache serves all of them from
@@ -130,11 +143,34 @@ k_shade(const DScene *__restrict__ Sp, const DSampler *__restrict__ Hp, PathArra
     long long stageClk[24] = {0};
     long long tPrev = clock64();
 #endif
+    // The path state of a chunk (ray, hit, info, sample index: 76 B per path, a scattered gather
+    // behind the queue entry) is copied into shared memory while the block still shades the chunk
+    // before it: after the stage barrier all warps start a chunk together, and they all used to
+    // wait for these loads together.
+    __shared__ float4 sState[5][kShadeBlock];
+    auto stage_state = [&](int path) {
+        const int t = (int)threadIdx.x;
+        cp_async16(&sState[0][t], A.rayA + path);
+        cp_async16(&sState[1][t], A.rayB + path);
+        cp_async16(&sState[2][t], A.hitA + path);
+        cp_async16(&sState[3][t], A.hitB + path);
+        cp_async8(&sState[4][t], A.sindex + path);
+        cp_async4(reinterpret_cast<char *>(&sState[4][t]) + 8, A.info + path);
+    };
+    int iCur = -1;
+    {
+        const int k0 = (int)blockIdx.x * (int)blockDim.x + (int)threadIdx.x;
+        if (blockIdx.x < nChunks && k0 < n) {
+            iCur = queue[k0];
+            stage_state(iCur);
+        }
+    }
     for (int chunk = blockIdx.x; chunk < nChunks; chunk += gridDim.x) {
         const int k = chunk * (int)blockDim.x + (int)threadIdx.x;
         bool alive = k < n;
         const bool valid = alive;
         int i = 0, iNext = -1;
+        int emitRow = -1;
         SampleStream st{0, 0};
         int bounces = 0, neeFlags = 0, lightNum = 0;
         float lightPdfSel = 0.f, etaScale = 1.f, rayWeight = 0.f;
@@ -146,24 +182,25 @@ k_shade(const DScene *__restrict__ Sp, const DSampler *__restrict__ Hp, PathArra
         Ray ray{mk(0, 0, 0), mk(0, 0, 1), kInf};
         // ---- stage 0: interaction, emission (path.cpp:91-112) ----
         if (alive) {
-            i = queue[k];
-#ifndef SPTX_NO_PREFETCH
+            i = iCur;
             prefetch_l2(A.beta[betaIn] + (size_t)i * SPTX_SPECTRUM_STRIDE);
-            {   // the next chunk of this block: its path state is a scattered gather, start it now
+            {   // the next chunk of this block
                 const int kn = k + (int)(gridDim.x * blockDim.x);
                 if (kn < n) iNext = queue[kn];
             }
-#endif
-            const float4 ra = A.rayA[i], rb = A.rayB[i];
-            const float4 ha = A.hitA[i], hb = A.hitB[i];
+            cp_async_wait_all();
+            const int t = (int)threadIdx.x;
+            const float4 ra = sState[0][t], rb = sState[1][t];
+            const float4 ha = sState[2][t], hb = sState[3][t];
+            const float4 sx = sState[4][t];
             ray.o = mk(ra.x, ra.y, ra.z);
             ray.d = mk(ra.w, rb.x, rb.y);
             etaScale = rb.z;
             rayWeight = rb.w;
-            const uint32_t info = A.info[i];
+            const uint32_t info = __float_as_uint(sx.z);
             bounces = (int)(info & 0xffu);
             const bool specularBounce = ((info >> 8) & 1u) != 0;
-            st.index = A.sindex[i];
+            st.index = (uint64_t)__float_as_uint(sx.x) | ((uint64_t)__float_as_uint(sx.y) << 32);
             st.dim = (int)(info >> 16);
             const int prim = __float_as_int(ha.x), inst = __float_as_int(ha.y);
 #ifdef SPTX_TRACE_PATH  // diagnosis build: the vertices of path 0 of a sptx_debug_radiance call
@@ -180,16 +217,10 @@ k_shade(const DScene *__restrict__ Sp, const DSampler *__restrict__ Hp, PathArra
             if ((bounces == 0 || specularBounce) && haveIsect && it.light >= 0) {
                 const sptx_light &Lt = S.lights[it.light];
                 if (Lt.two_sided || dot(it.n, -ray.d) > 0) {
-                    const Row4 Lr = row4(A.L, i), br = row4(A.beta[betaIn], i);
-                    for (int c = 0; c < 8; ++c) {
-                        float4 l = Lr.ld(c);
-                        const float4 b = br.ldro(c), e = spec4(S, Lt.spectrum, c);
-                        l.x += b.x * e.x;
-                        l.y += b.y * e.y;
-                        l.z += b.z * e.z;
-                        l.w += b.w * e.w;
-                        Lr.st(c, l);
-                    }
+                    // (few lanes of a warp get here, and the two rows are DRAM round trips the whole
+                    //  warp would wait for: the rows are asked for now and added at the end of the vertex)
+                    emitRow = Lt.spectrum;
+                    prefetch_l2(A.L + (size_t)i * SPTX_SPECTRUM_STRIDE);
                 }
             }
             alive = haveIsect && bounces < R.maxDepth;
@@ -252,16 +283,8 @@ k_shade(const DScene *__restrict__ Sp, const DSampler *__restrict__ Hp, PathArra
                 }
             }
         }
-#ifndef SPTX_NO_PREFETCH
-        if (iNext >= 0) {
-            prefetch_l2(A.rayA + iNext);
-            prefetch_l2(A.rayB + iNext);
-            prefetch_l2(A.hitA + iNext);
-            prefetch_l2(A.hitB + iNext);
-            prefetch_l2(A.info + iNext);
-            prefetch_l2(A.sindex + iNext);
-        }
-#endif
+        if (iNext >= 0) stage_state(iNext);  // (this thread's slots were read in stage 0)
+        iCur = iNext;
         SPTX_STAGE(2);
         // ---- stage 2: light sampling strategy (integrator.cpp:119-163) ----
         bool delta = false;
@@ -427,6 +450,19 @@ k_shade(const DScene *__restrict__ Sp, const DSampler *__restrict__ Hp, PathArra
                     if (st.dim >= H.s.n_dims) atomicOr(A.counters + 3, ERR_DIM_OVERFLOW);
                     A.info[i] = pack_info(bounces + 1, (flags & BSDF_SPECULAR) ? 1 : 0, st.dim);
                 }
+            }
+        }
+        if (emitRow >= 0) {
+            // L += beta * isect.Le(-ray.d) (path.cpp:91-95; beta is the vertex's incoming throughput)
+            const Row4 Lr = row4(A.L, i), br = row4(A.beta[betaIn], i);
+            for (int c = 0; c < 8; ++c) {
+                float4 l = Lr.ld(c);
+                const float4 b = br.ldro(c), e = spec4(S, emitRow, c);
+                l.x += b.x * e.x;
+                l.y += b.y * e.y;
+                l.z += b.z * e.z;
+                l.w += b.w * e.w;
+                Lr.st(c, l);
             }
         }
         // the next band of the sample continues the sampler stream where this path stopped

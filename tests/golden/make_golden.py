@@ -321,6 +321,27 @@ def make_bands(name):
           f"{np.array2string(dat.mean(axis=(1, 2))[[0, 7, 8, 15, 16, 23, 24, 29, 30]], precision=4)}")
 
 
+def make_halton_large():
+    """HaltonSampler values at the bench resolution (1024^2: sample stride 2 239 488) for sample
+    numbers up to 8191 -- indices on both sides of 2^32 and of 2^32 / base, where the device's
+    interleaved digit loops and its scalar 64-bit path take over from one another."""
+    rng = np.random.RandomState(20261105)
+    with tempfile.TemporaryDirectory() as work:
+        pbrt = os.path.join(work, "cornell1024.pbrt")
+        run([sys.executable, os.path.join(ROOT, "scenes", "gen_scenes.py"), "cornell", pbrt, "res=1024", "spp=1024"])
+        n = 1 << 15
+        hq = np.stack([rng.randint(0, 1024, n), rng.randint(0, 1024, n), rng.randint(0, 8192, n),
+                       rng.randint(0, 60, n)], -1).astype(np.int32)
+        hq[:4096, 2] = rng.randint(1800, 2000, 4096)     # around index = 2^32 (sample number ~1918)
+        hq[4096:8192, 2] = rng.randint(0, 64, 4096)
+        hq.tofile(os.path.join(work, "hq.bin"))
+        run([ORACLE, "--quiet", "--nthreads", "8", pbrt],
+            env={"ORACLE_HALTON_IN": "hq.bin", "ORACLE_HALTON_OUT": "hv.bin"}, cwd=work)
+        hv = np.fromfile(os.path.join(work, "hv.bin"), np.float32)
+        np.savez_compressed(os.path.join(GOLD, "halton_large.npz"), halton_q=hq, halton_v=hv)
+        print(f"halton_large: {n} values, mean {hv.mean():.4f}")
+
+
 VISIT_SCENES = ["cornell64", "killeroo128", "instanced", "zoo"]
 
 
@@ -364,10 +385,12 @@ def read_root_bounds(blob):
 
 
 if __name__ == "__main__":
-    names = sys.argv[1:] or list(SCENES) + list(TILE_SERIAL) + list(BAND_SCENES) + list(META_SCENES) + ["visits"]
+    names = sys.argv[1:] or list(SCENES) + list(TILE_SERIAL) + list(BAND_SCENES) + list(META_SCENES) + ["visits", "halton_large"]
     for n in names:
         if n == "visits":
             make_visits()
+        elif n == "halton_large":
+            make_halton_large()
         elif n in TILE_SERIAL:
             make_random(n)
         elif n in BAND_SCENES:

@@ -60,6 +60,19 @@ def test_halton_bit_exact(scene):
     assert np.array_equal(v.view(np.uint32), g["halton_v"].view(np.uint32))
 
 
+def test_halton_bit_exact_large_indices(capi, gpu_ctx):
+    """The bench resolution (stride 2 239 488) at sample numbers up to 8191: Halton indices on both
+    sides of 2^32 and of 2^32 / base (tests/golden/make_golden.py halton_large)."""
+    sf = capi.SceneFile(blob_path("cornell1024"))
+    gpu_ctx.upload(sf)
+    sf.close()
+    g = golden("halton_large")
+    q = g["halton_q"]
+    v = gpu_ctx.sampler_eval(q[:, 0], q[:, 1], q[:, 2], q[:, 3])
+    bad = np.nonzero(v.view(np.uint32) != g["halton_v"].view(np.uint32))[0]
+    assert len(bad) == 0, (len(bad), q[bad[:5]], v[bad[:5]], g["halton_v"][bad[:5]])
+
+
 def test_camera_rays(scene):
     name, g, ctx = scene
     rays, w = ctx.camera_rays(g["cam_samples"])
