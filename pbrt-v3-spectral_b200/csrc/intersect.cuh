@@ -64,15 +64,25 @@ struct TriPre {
     int kz;
     float Sx, Sy, Sz;
 };
+// Permute(v, kx, ky, kz) for the test's (kx, ky, kz) = (kz + 1, kz + 2, kz) mod 3, a rotation of the
+// components: kz = 2 -> (x, y, z), kz = 0 -> (y, z, x), kz = 1 -> (z, x, y).  Written with selp:
+// the compiler turned the nested conditional of comp() into branches (BSSY / BRA / BSYNC around
+// moves, 13 % of K2's stall samples and instructions on the bench scene, profiles/r02x).
+SPTX_DEV float selp_f(float a, float b, int pick_a) {
+    float r;
+    asm("{ .reg .pred p; setp.ne.s32 p, %3, 0; selp.f32 %0, %1, %2, p; }" : "=f"(r) : "f"(a), "f"(b), "r"(pick_a));
+    return r;
+}
+SPTX_DEV V3 rot3(V3 v, int kz) {
+    const int r0 = kz == 0, r1 = kz == 1;
+    return mk(selp_f(v.y, selp_f(v.z, v.x, r1), r0), selp_f(v.z, selp_f(v.x, v.y, r1), r0),
+              selp_f(v.x, selp_f(v.y, v.z, r1), r0));
+}
 SPTX_DEV TriPre tri_pre(V3 rd) {
     // MaxDimension(Abs(d)), core/geometry.h: (x > y) ? ((x > z) ? 0 : 2) : ((y > z) ? 1 : 2)
     float ax = fabsf(rd.x), ay = fabsf(rd.y), az = fabsf(rd.z);
     int kz = (ax > ay) ? ((ax > az) ? 0 : 2) : ((ay > az) ? 1 : 2);
-    int kx = kz + 1;
-    if (kx == 3) kx = 0;
-    int ky = kx + 1;
-    if (ky == 3) ky = 0;
-    V3 d = mk(comp(rd, kx), comp(rd, ky), comp(rd, kz));
+    V3 d = rot3(rd, kz);
     TriPre pre;
     pre.kz = kz;
     pre.Sx = -d.x / d.z;
@@ -86,13 +96,9 @@ SPTX_DEV bool tri_test_pre(V3 ro, const TriPre &pre, float tMax, V3 p0, V3 p1, V
                            float *b0o, float *b1o, float *b2o) {
     V3 p0t = p0 - ro, p1t = p1 - ro, p2t = p2 - ro;
     const int kz = pre.kz;
-    int kx = kz + 1;
-    if (kx == 3) kx = 0;
-    int ky = kx + 1;
-    if (ky == 3) ky = 0;
-    p0t = mk(comp(p0t, kx), comp(p0t, ky), comp(p0t, kz));
-    p1t = mk(comp(p1t, kx), comp(p1t, ky), comp(p1t, kz));
-    p2t = mk(comp(p2t, kx), comp(p2t, ky), comp(p2t, kz));
+    p0t = rot3(p0t, kz);
+    p1t = rot3(p1t, kz);
+    p2t = rot3(p2t, kz);
     const float Sx = pre.Sx, Sy = pre.Sy, Sz = pre.Sz;
     p0t.x += Sx * p0t.z;
     p0t.y += Sy * p0t.z;
@@ -451,6 +457,7 @@ __device__ bool traverse_bvh(const DScene &S, int bvhIndex, Ray &ray, HitRec *hi
     const float4 *nodes = S.nodes + 2 * (size_t)B.node_base;
     V3 invDir = mk(1.f / ray.d.x, 1.f / ray.d.y, 1.f / ray.d.z);
     int neg[3] = {invDir.x < 0, invDir.y < 0, invDir.z < 0};
+    const unsigned negMask = (unsigned)neg[0] | ((unsigned)neg[1] << 1) | ((unsigned)neg[2] << 2);
     int stack[64];
     int sp = 0, cur = 0;
     // "while-while": every lane first walks interior nodes until it holds a
@@ -474,13 +481,10 @@ __device__ bool traverse_bvh(const DScene &S, int bvhIndex, Ray &ray, HitRec *hi
                 }
                 int axis = (int)((meta >> 16) & 0xffu);
                 int far;
-                if (neg[axis]) {
-                    far = cur + 1;
-                    cur = offset;
-                } else {
-                    far = offset;
-                    cur = cur + 1;
-                }
+                // dirIsNeg[node->axis]: near child first (accelerators/bvh.cpp:686-692)
+                const bool negAxis = ((negMask >> axis) & 1u) != 0;
+                far = negAxis ? cur + 1 : offset;
+                cur = negAxis ? offset : cur + 1;
                 stack[sp++] = far;
                 // the far child is visited some iterations from now: have its node in L1 by then
                 asm volatile("prefetch.global.L1 [%0];" ::"l"(nodes + 2 * (size_t)far));

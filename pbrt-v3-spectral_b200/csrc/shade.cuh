@@ -183,16 +183,20 @@ k_shade(const DScene *__restrict__ Sp, const DSampler *__restrict__ Hp, PathArra
         // ---- stage 0: interaction, emission (path.cpp:91-112) ----
         if (alive) {
             i = iCur;
+            // (first: the wait is a barrier on the scoreboard the copies share with whatever else is in
+            //  flight on it, e.g. the L2 prefetch below)
+            SPTX_TICK(12);
+            cp_async_wait_all();
+            SPTX_TICK(13);
+            const int t = (int)threadIdx.x;
+            const float4 ra = sState[0][t], rb = sState[1][t];
+            const float4 ha = sState[2][t], hb = sState[3][t];
+            const float4 sx = sState[4][t];
             prefetch_l2(A.beta[betaIn] + (size_t)i * SPTX_SPECTRUM_STRIDE);
             {   // the next chunk of this block
                 const int kn = k + (int)(gridDim.x * blockDim.x);
                 if (kn < n) iNext = queue[kn];
             }
-            cp_async_wait_all();
-            const int t = (int)threadIdx.x;
-            const float4 ra = sState[0][t], rb = sState[1][t];
-            const float4 ha = sState[2][t], hb = sState[3][t];
-            const float4 sx = sState[4][t];
             ray.o = mk(ra.x, ra.y, ra.z);
             ray.d = mk(ra.w, rb.x, rb.y);
             etaScale = rb.z;
