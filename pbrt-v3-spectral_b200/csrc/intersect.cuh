@@ -340,8 +340,15 @@ SPTX_NOINL bool sphere_test(const sptx_sphere &sp, const Ray &wr, SphereHit *h) 
     V3 pHit = ray.o + ray.d * tsv;
     pHit = pHit * (radius / length(pHit));
     if (pHit.x == 0 && pHit.y == 0) pHit.x = 1e-5f * radius;
-    float phi = atan2f(pHit.y, pHit.x);
-    if (phi < 0) phi += 2 * kPi;
+    // phi = atan2(y, x), + 2 Pi when negative, lies in [0, float(2 Pi)]: a sphere whose phiMax is
+    // float(2 Pi) or more (every full sphere: Radians(360) is that float) never clips on phi, and the
+    // atan2 is needed only for the others (shapes/sphere.cpp:84-104)
+    const bool clipsPhi = sp.phi_max < 2 * kPi;
+    float phi = 0.f;
+    if (clipsPhi) {
+        phi = atan2f(pHit.y, pHit.x);
+        if (phi < 0) phi += 2 * kPi;
+    }
     if ((sp.z_min > -radius && pHit.z < sp.z_min) || (sp.z_max < radius && pHit.z > sp.z_max) ||
         phi > sp.phi_max) {
         if (tsv == t1v) return false;
@@ -350,14 +357,15 @@ SPTX_NOINL bool sphere_test(const sptx_sphere &sp, const Ray &wr, SphereHit *h) 
         pHit = ray.o + ray.d * tsv;
         pHit = pHit * (radius / length(pHit));
         if (pHit.x == 0 && pHit.y == 0) pHit.x = 1e-5f * radius;
-        phi = atan2f(pHit.y, pHit.x);
-        if (phi < 0) phi += 2 * kPi;
+        if (clipsPhi) {
+            phi = atan2f(pHit.y, pHit.x);
+            if (phi < 0) phi += 2 * kPi;
+        }
         if ((sp.z_min > -radius && pHit.z < sp.z_min) ||
             (sp.z_max < radius && pHit.z > sp.z_max) || phi > sp.phi_max)
             return false;
     }
     h->pHit = pHit;
-    h->phi = phi;
     h->tHit = tsv;
     h->oray = ray;
     return true;

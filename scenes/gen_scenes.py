@@ -237,6 +237,8 @@ def texbox(opts, out):
             f.write(DGAUSS_50MM)
         cam = ('LookAt 0 1.1 4.0  0 -.3 0  0 1 0\nCamera "realistic" "string lensfile" "dgauss.50mm.dat" '
                '"float aperturediameter" [8] "float focusdistance" [4.2] "bool simpleweighting" "true"')
+        if opts.get("ca") == "true":
+            cam += ' "bool chromaticAberrationEnabled" "true"'
     s = header(opts, cam, name) + "WorldBegin\n"
     w, h = 20, 12
     v, u = np.meshgrid((np.arange(h) + .5) / h, (np.arange(w) + .5) / w, indexing="ij")

@@ -238,6 +238,10 @@ BAND_SCENES = {
     "cornell_bands3": dict(gen=["cornell", "res=40x32", "spp=4", "bands=3"], res=(40, 32), spp=4, bands=3),
     # one band at 550 nm == Integrator "path" (cornell_bands1_path: the same file with "path")
     "cornell_bands1": dict(gen=["cornell", "res=40x32", "spp=4", "bands=1"], res=(40, 32), spp=4, bands=1),
+    # image textures under the band loop: the textured variant recomputes the camera ray's differentials
+    # per band from the sample's CameraSample (the bands share it), through the lens with aberration
+    "texbox_bands": dict(gen=["texbox", "res=40x32", "spp=4", "bands=4", "camera=realistic", "ca=true"], res=(40, 32),
+                         spp=4, bands=4),
 }
 
 

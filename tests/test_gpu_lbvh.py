@@ -29,7 +29,7 @@ def _ctx(capi, blob):
     return ctx
 
 
-@pytest.mark.parametrize("name", ["cornell64", "zoo", "killeroo128", "instanced", "furnace_area"])
+@pytest.mark.parametrize("name", ["cornell64", "zoo", "killeroo128", "instanced", "furnace_area", "texbox"])
 def test_device_built_bvh_answers_like_the_reference(capi, name):
     g = golden(name)
     ctx = _ctx(capi, blob_path(name))

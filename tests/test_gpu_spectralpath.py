@@ -12,7 +12,7 @@ from conftest import blob_path, golden
 
 pytestmark = pytest.mark.gpu
 
-BAND_SCENES = ["cornell_lens_ca", "cornell_bands3", "cornell_bands1"]
+BAND_SCENES = ["cornell_lens_ca", "cornell_bands3", "cornell_bands1", "texbox_bands"]
 
 
 @pytest.fixture(scope="module", params=BAND_SCENES)
