@@ -48,7 +48,9 @@ k_mis(DScene S, PathArrays A, DeviceCounters *cnt) {
 
 // (any-hit needs fewer registers than closest-hit: 8 resident blocks at 64 registers measured
 //  7 % faster than 6 at 80 on the bench scene, the same on C1)
-template <bool COUNT>
+// FAST (launched beside K3's fast build): Ld / lightPdf as a multiplication by the path's
+// correctly rounded reciprocal instead of an IEEE division per bin (11 % of the kernel's instructions).
+template <bool COUNT, bool FAST>
 __global__ void __launch_bounds__(kBlock, SPTX_ANYHIT_BLOCKS)
 k_resolve(DScene S, PathArrays A, int betaIn, DeviceCounters *cnt) {
     TravCounters tc{0, 0};
@@ -65,7 +67,7 @@ k_resolve(DScene S, PathArrays A, int betaIn, DeviceCounters *cnt) {
             i = A.qNee[k];
             const float4 sa = A.shA[i], sb = A.shB[i];
             const int flags = __float_as_int(A.misB[i].w);
-            lightPdfSel = sb.w;
+            lightPdfSel = FAST ? __frcp_rn(sb.w) : sb.w;
             useB = (flags & NEE_MIS_REACHED_LIGHT) != 0;
             if (flags & NEE_HAS_SHADOW) {
                 Ray r{mk(sa.x, sa.y, sa.z), mk(sa.w, sb.x, sb.y), sb.z};
@@ -104,7 +106,8 @@ k_resolve(DScene S, PathArrays A, int betaIn, DeviceCounters *cnt) {
             for (int j = 0; j < 4; ++j)
                 // (lane 31 is the row's pad word: its 0 / sel would take the division's slow path
                 //  alone, with the other 31 lanes waiting)
-                if (on[j] && lane < SPTX_NBINS) A.L[at[j]] = Lv[j] + bt[j] * (va[j] / sel[j]);
+                if (on[j] && lane < SPTX_NBINS)
+                    A.L[at[j]] = Lv[j] + bt[j] * (FAST ? va[j] * sel[j] : va[j] / sel[j]);
         }
     }
     if (COUNT) {

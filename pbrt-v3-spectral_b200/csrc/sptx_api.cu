@@ -1238,10 +1238,16 @@ static int render_pixels(sptx_ctx *ctx, int s0, int s1, const int *dSampleList =
                         tic(3);
                         if (cv) {
                             k_mis<true><<<g, kBlock, 0, ctx->stream>>>(ctx->S, A, ctx->dCnt);
-                            k_resolve<true><<<g, kBlock, 0, ctx->stream>>>(ctx->S, A, betaIn, ctx->dCnt);
+                            if (ctx->shadeExact)
+                                k_resolve<true, false><<<g, kBlock, 0, ctx->stream>>>(ctx->S, A, betaIn, ctx->dCnt);
+                            else
+                                k_resolve<true, true><<<g, kBlock, 0, ctx->stream>>>(ctx->S, A, betaIn, ctx->dCnt);
                         } else {
                             k_mis<false><<<g, kBlock, 0, ctx->stream>>>(ctx->S, A, ctx->dCnt);
-                            k_resolve<false><<<g, kBlock, 0, ctx->stream>>>(ctx->S, A, betaIn, ctx->dCnt);
+                            if (ctx->shadeExact)
+                                k_resolve<false, false><<<g, kBlock, 0, ctx->stream>>>(ctx->S, A, betaIn, ctx->dCnt);
+                            else
+                                k_resolve<false, true><<<g, kBlock, 0, ctx->stream>>>(ctx->S, A, betaIn, ctx->dCnt);
                         }
                         ++launches;
                         toc();
