@@ -453,6 +453,11 @@ int sptx_reset_counters(sptx_ctx *ctx);
  * for batches of >= 65536 rays (smaller ones do not repay the sort).  sptx_intersect_batch_noalloc
  * never sorts (the sort's scratch is allocated). */
 int sptx_set_option(sptx_ctx *ctx, const char *name, int64_t value);
+/* "sparse_voxels" 1 (takes effect at the next upload): the spatial light distribution's per-voxel tables
+ * (SpatialLightDistribution, src/core/lightdistrib.cpp:91-300) are built only for the voxels that can hold
+ * a surface point; the default does so when the full table would pass 256 MB (many lights).
+ * sptx_light_table_rows: number of voxel rows the last upload built (0: not the spatial strategy). */
+int64_t sptx_light_table_rows(sptx_ctx *ctx);
 /* 1 when the last sptx_intersect_batch / _device call walked its rays in sorted order. */
 int sptx_last_batch_sorted(sptx_ctx *ctx);
 /* Max paths in flight per wavefront pass (0 = default). */

@@ -26,7 +26,7 @@ SYMBOLS = [
     "sptx_film_export", "sptx_film_merge_peers", "sptx_film_reduce_scatter", "sptx_film_merge_contexts",
     "sptx_film_reduce",
     "sptx_film_download", "sptx_film_pack_dat", "sptx_write_dat",
-    "sptx_get_counters", "sptx_reset_counters", "sptx_set_wavefront_size", "sptx_set_option", "sptx_last_batch_sorted",
+    "sptx_get_counters", "sptx_reset_counters", "sptx_set_wavefront_size", "sptx_set_option", "sptx_last_batch_sorted", "sptx_light_table_rows",
     "sptx_sampler_eval", "sptx_camera_rays", "sptx_debug_radiance",
     "sptx_scene_save", "sptx_scene_load", "sptx_scene_free", "sptx_io_last_error",
 ]
@@ -103,6 +103,8 @@ def lib():
     L.sptx_set_wavefront_size.argtypes = [vp, i64]
     L.sptx_set_option.argtypes = [vp, C.c_char_p, i64]
     L.sptx_last_batch_sorted.argtypes = [vp]
+    L.sptx_light_table_rows.argtypes = [vp]
+    L.sptx_light_table_rows.restype = i64
     L.sptx_sampler_eval.argtypes = [vp, vp, vp, vp, vp, i64, vp]
     L.sptx_camera_rays.argtypes = [vp, vp, i64, C.c_float, vp, vp]
     L.sptx_debug_radiance.argtypes = [vp, vp, vp, vp, i64, vp, vp]
@@ -203,6 +205,10 @@ class Context:
 
     def set_wavefront_size(self, n):
         self._ck(lib().sptx_set_wavefront_size(self.h, int(n)), "sptx_set_wavefront_size")
+
+    def light_table_rows(self):
+        """Voxel rows of the spatial light distribution built by the last upload."""
+        return int(lib().sptx_light_table_rows(self.h))
 
     def last_batch_sorted(self):
         """True when the last ray batch was walked in binned order (set_option("ray_sort", ..))."""

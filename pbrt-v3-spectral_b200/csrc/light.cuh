@@ -456,6 +456,17 @@ SPTX_DEV int select_light(const DScene &S, V3 p, float u, float *pdf) {
     int pi1 = min(max((int)(o.y * (float)S.n_voxels[1]), 0), S.n_voxels[1] - 1);
     int pi2 = min(max((int)(o.z * (float)S.n_voxels[2]), 0), S.n_voxels[2] - 1);
     size_t voxel = ((size_t)pi0 * S.n_voxels[1] + pi1) * S.n_voxels[2] + pi2;
+    if (S.voxel_rows) {
+        // sparse tables (many lights): rows exist for the voxels that hold a surface.  A point in a
+        // voxel without one (none should: the marking is conservative) picks a light uniformly, which
+        // is still an unbiased choice.
+        const int r = __ldg(S.voxel_rows + voxel);
+        if (r < 0) {
+            *pdf = 1.f / (float)n;
+            return min((int)(u * (float)n), n - 1);
+        }
+        voxel = (size_t)r;
+    }
     const float *row = S.voxel_tables + voxel * (size_t)(2 * n + 2);
     return sample_discrete(row, row + n, n, __ldg(row + 2 * n + 1), u, pdf);
 }

@@ -47,6 +47,7 @@ struct DScene {
     float light_func_int;
     // spatial: per-voxel rows of (n_lights func) + (n_lights+1 cdf) + funcInt
     const float *voxel_tables;
+    const int *voxel_rows;   // sparse tables: row of a voxel (-1: no surface in it), or NULL (row = voxel)
     int n_voxels[3];
     float wb_min[3], wb_max[3];  // scene.WorldBound()
     // colour matching

@@ -43,13 +43,14 @@ __global__ void k_pixel_offsets(sptx_sampler s, int x0, int y0, int w, int h, ui
 // SpatialLightDistribution::ComputeDistribution for every voxel, eagerly
 // (core/lightdistrib.cpp:221-300).  halton5 holds RadicalInverse(d, i) for
 // d = 0..4, i = 0..127.  Row layout: func[n] | cdf[n+1] | funcInt.
-__global__ void k_voxel_tables(DScene S, const float *halton5, float *tables) {
+// voxList (sparse tables): the voxels that get a row, row r for voxList[r]; NULL: every voxel, row = voxel.
+__global__ void k_voxel_tables(DScene S, const float *halton5, float *tables, const int *voxList, int64_t nRows) {
     const int n = S.n_lights;
-    const int64_t nVox = (int64_t)S.n_voxels[0] * S.n_voxels[1] * S.n_voxels[2];
     const V3 wmin = mk(S.wb_min[0], S.wb_min[1], S.wb_min[2]);
     const V3 wmax = mk(S.wb_max[0], S.wb_max[1], S.wb_max[2]);
-    for (int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; v < nVox;
-         v += (int64_t)gridDim.x * blockDim.x) {
+    for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < nRows;
+         r += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t v = voxList ? (int64_t)voxList[r] : r;
         int pz = (int)(v % S.n_voxels[2]);
         int py = (int)((v / S.n_voxels[2]) % S.n_voxels[1]);
         int px = (int)(v / ((int64_t)S.n_voxels[2] * S.n_voxels[1]));
@@ -61,7 +62,7 @@ __global__ void k_voxel_tables(DScene S, const float *halton5, float *tables) {
         V3 c = mk(lerpf(p1.x, wmin.x, wmax.x), lerpf(p1.y, wmin.y, wmax.y), lerpf(p1.z, wmin.z, wmax.z));
         V3 vmin = mk(fminf(a.x, c.x), fminf(a.y, c.y), fminf(a.z, c.z));
         V3 vmax = mk(fmaxf(a.x, c.x), fmaxf(a.y, c.y), fmaxf(a.z, c.z));
-        float *row = tables + v * (int64_t)(2 * n + 2);
+        float *row = tables + r * (int64_t)(2 * n + 2);
         for (int j = 0; j < n; ++j) row[j] = 0.f;
         const int nSamples = 128;
         for (int i = 0; i < nSamples; ++i) {
@@ -97,6 +98,39 @@ __global__ void k_voxel_tables(DScene S, const float *halton5, float *tables) {
             for (int j = 1; j < n + 1; ++j) cdf[j] /= funcInt;
         }
         row[2 * n + 1] = funcInt;
+    }
+}
+
+// Sparse spatial light tables: the voxels a surface point can fall into.  Every leaf of the scene's
+// top-level BVH marks the voxels its bounds overlap, widened by one voxel each way (a hit point is
+// inside its primitive's bounds only up to rounding); select_light's own index arithmetic is used, so
+// a point inside the bounds maps into the marked range.
+SPTX_DEV int voxel_coord(const DScene &S, float p, int a) {
+    float o = p - S.wb_min[a];
+    if (S.wb_max[a] > S.wb_min[a]) o /= S.wb_max[a] - S.wb_min[a];
+    return min(max((int)(o * (float)S.n_voxels[a]), 0), S.n_voxels[a] - 1);
+}
+__global__ void k_voxel_mark(DScene S, int nodeBase, int nNodes, int *flags) {
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < nNodes; i += gridDim.x * blockDim.x) {
+        const float4 n0 = __ldg(S.nodes + 2 * ((size_t)nodeBase + i)), n1 = __ldg(S.nodes + 2 * ((size_t)nodeBase + i) + 1);
+        if (((unsigned)__float_as_int(n1.w) & 0xffffu) == 0) continue;  // interior node
+        const float lo[3] = {n0.x, n0.y, n0.z}, hi[3] = {n0.w, n1.x, n1.y};
+        int a0[3], a1[3];
+        for (int a = 0; a < 3; ++a) {
+            a0[a] = max(voxel_coord(S, lo[a], a) - 1, 0);
+            a1[a] = min(voxel_coord(S, hi[a], a) + 1, S.n_voxels[a] - 1);
+        }
+        for (int x = a0[0]; x <= a1[0]; ++x)
+            for (int y = a0[1]; y <= a1[1]; ++y)
+                for (int z = a0[2]; z <= a1[2]; ++z) flags[((size_t)x * S.n_voxels[1] + y) * S.n_voxels[2] + z] = 1;
+    }
+}
+// rows[v] = index of voxel v among the marked ones (or -1); list[row] = v.
+__global__ void k_voxel_rows(const int *flags, const int *scan, int64_t nVox, int *rows, int *list) {
+    for (int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; v < nVox; v += (int64_t)gridDim.x * blockDim.x) {
+        const bool on = flags[v] != 0;
+        rows[v] = on ? scan[v] : -1;
+        if (on) list[scan[v]] = (int)v;
     }
 }
 

@@ -100,6 +100,9 @@ struct sptx_ctx {
     // "ray_sort": 0 never, 1 always, 2 (default) batches of kRaySortMin rays and more
     int raySort = 2;
     int lastBatchSorted = 0;
+    // "sparse_voxels": 1 forces the sparse form of the spatial light tables (default: above 256 MB)
+    bool sparseVoxels = false;
+    int64_t voxelRows = 0;
     std::vector<cudaEvent_t> evPool;
     int smCount = 148;
 };
@@ -314,6 +317,10 @@ extern "C" int sptx_set_option(sptx_ctx *ctx, const char *name, int64_t value) {
     }
     if (!strcmp(name, "device_bvh")) {  // takes effect at the next sptx_upload_scene
         ctx->deviceBvh = value != 0;
+        return SPTX_OK;
+    }
+    if (!strcmp(name, "sparse_voxels")) {  // takes effect at the next sptx_upload_scene
+        ctx->sparseVoxels = value != 0;
         return SPTX_OK;
     }
     if (!strcmp(name, "ray_sort")) {  // sptx_intersect_batch*: order the rays by origin cell / direction first
@@ -874,12 +881,42 @@ extern "C" int sptx_upload_scene(sptx_ctx *ctx, const sptx_scene_desc *sc) {
             nVox *= S.n_voxels[i];
         }
         const int64_t rowFloats = 2 * (int64_t)nL + 2;
-        const double bytes = (double)nVox * rowFloats * 4.0;
+        // The reference fills a voxel's row when a path first asks for it (a hash table under a lock,
+        // lightdistrib.cpp:135-219).  Here rows are built up front: for every voxel while that is small
+        // (256 MB), else only for the voxels that can hold a surface point -- the ones the leaves of
+        // the scene's BVH overlap (k_voxel_mark), typically a few per cent of the grid.
+        int64_t nRows = nVox;
+        const int *voxList = nullptr;
+        S.voxel_rows = nullptr;
+        const int64_t topNodes = sc->n_bvhs > 0 ? (ctx->deviceBvh ? std::max(0, 2 * sc->bvhs[0].n_prims - 1) : sc->bvhs[0].n_nodes) : 0;
+        if (((double)nVox * rowFloats * 4.0 > 256e6 || ctx->sparseVoxels) && topNodes > 0) {
+            int *flags, *scan, *rows, *list;
+            if ((rc = dalloc(ctx, pool, nVox, &flags)) || (rc = dalloc(ctx, pool, nVox, &scan)) ||
+                (rc = dalloc(ctx, pool, nVox, &rows)) || (rc = dalloc(ctx, pool, nVox, &list)))
+                return rc;
+            CK(cudaMemsetAsync(flags, 0, (size_t)nVox * sizeof(int), ctx->stream));
+            k_voxel_mark<<<grid_for(ctx, topNodes), kBlock, 0, ctx->stream>>>(S, ctx->deviceBvh ? 0 : sc->bvhs[0].node_base, (int)topNodes, flags);
+            size_t tmpBytes = 0;
+            cub::DeviceScan::ExclusiveSum(nullptr, tmpBytes, flags, scan, (int)nVox, ctx->stream);
+            void *tmp;
+            if ((rc = dalloc(ctx, pool, (int64_t)tmpBytes + 16, (unsigned char **)&tmp))) return rc;
+            cub::DeviceScan::ExclusiveSum(tmp, tmpBytes, flags, scan, (int)nVox, ctx->stream);
+            k_voxel_rows<<<grid_for(ctx, nVox), kBlock, 0, ctx->stream>>>(flags, scan, nVox, rows, list);
+            int lastScan = 0, lastFlag = 0;
+            CK(cudaMemcpyAsync(&lastScan, scan + nVox - 1, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+            CK(cudaMemcpyAsync(&lastFlag, flags + nVox - 1, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+            CK(cudaStreamSynchronize(ctx->stream));
+            nRows = (int64_t)lastScan + lastFlag;
+            voxList = list;
+            S.voxel_rows = rows;
+        }
+        ctx->voxelRows = nRows;
+        const double bytes = (double)nRows * rowFloats * 4.0;
         if (bytes > 16e9)
             return fail(ctx, SPTX_EUNSUPPORTED,
                         "sptx_upload_scene: spatial light distribution for %d lights needs %.1f GB "
-                        "when built eagerly; use lightsamplestrategy \"power\" or \"uniform\"",
-                        nL, bytes * 1e-9);
+                        "(%lld of %lld voxels hold a surface); use lightsamplestrategy \"power\" or \"uniform\"",
+                        nL, bytes * 1e-9, (long long)nRows, (long long)nVox);
         // RadicalInverse(d, i), d = 0..4, i = 0..127 (bases 2, 3, 5, 7, 11)
         std::vector<float> h5(5 * 128);
         const uint32_t bases[5] = {2, 3, 5, 7, 11};
@@ -890,10 +927,11 @@ extern "C" int sptx_upload_scene(sptx_ctx *ctx, const sptx_scene_desc *sc) {
         const float *dH5;
         if ((rc = upload(ctx, pool, h5.data(), (int64_t)h5.size(), &dH5))) return rc;
         float *tables;
-        if ((rc = dalloc(ctx, pool, nVox * rowFloats, &tables))) return rc;
+        if ((rc = dalloc(ctx, pool, std::max<int64_t>(nRows, 1) * rowFloats, &tables))) return rc;
         S.voxel_tables = tables;
         mark("arrays");
-        k_voxel_tables<<<grid_for(ctx, nVox, 64), 64, 0, ctx->stream>>>(S, dH5, tables);
+        if (nRows > 0)
+            k_voxel_tables<<<grid_for(ctx, nRows, 64), 64, 0, ctx->stream>>>(S, dH5, tables, voxList, nRows);
         mark("voxel tables");
     }
 
@@ -1785,6 +1823,8 @@ extern "C" int sptx_intersect_batch_device(sptx_ctx *ctx, const void *d_rays, in
 }
 
 extern "C" int sptx_last_batch_sorted(sptx_ctx *ctx) { return ctx ? ctx->lastBatchSorted : 0; }
+
+extern "C" int64_t sptx_light_table_rows(sptx_ctx *ctx) { return ctx ? ctx->voxelRows : 0; }
 
 extern "C" int sptx_intersect_batch(sptx_ctx *ctx, const sptx_ray *rays, int64_t n, sptx_hit *hits,
                                     int any_hit, int with_counters) {

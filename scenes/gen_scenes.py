@@ -8,6 +8,7 @@ names:  cornell       C2: spectral Cornell box (diffuse + glass + metal), perspe
         instanced     C4: N x N displaced grid mesh, instanced on a lattice
         zoo           one of every supported material / shape / light / camera feature (parity)
         envbox        open scene under Light "infinite" (env=const | env=map), SURVEY 8(f) rank 3
+        manylights    an emissive 24 x 24 mesh = 1152 area lights under the spatial light distribution
         texbox        Texture "imagemap" Kd on matte / plastic (lens=R: thin-lens camera), 8(f) rank 3
         furnace_point / furnace_area   the known-answer scenes of the reference's
                       src/tests/analytic_scenes.cpp:68-165 written as scene files
@@ -269,6 +270,35 @@ def texbox(opts, out):
     return s + "WorldEnd\n"
 
 
+def manylights(opts, out):
+    """An emissive mesh: every triangle of an area-light shape is its own DiffuseAreaLight
+    (src/core/api.cpp:1377-1386), so a 24 x 24 grid puts 1152 lights into the spatial light
+    distribution -- the device's per-voxel tables switch to their sparse form."""
+    name = os.path.splitext(os.path.basename(out))[0]
+    cam = 'LookAt 0 1.0 3.6  0 -.2 0  0 1 0\nCamera "perspective" "float fov" [42]'
+    s = header(opts, cam, name) + "WorldBegin\n"
+    n = int(opts.get("cells", 24))
+    P, idx = [], []
+    for j in range(n + 1):
+        for i in range(n + 1):
+            x, z = -0.6 + 1.2 * i / n, -0.6 + 1.2 * j / n
+            P += [x, 1.5 + 0.05 * math.sin(7 * x) * math.cos(5 * z), z]
+    for j in range(n):
+        for i in range(n):
+            a = j * (n + 1) + i
+            idx += [a, a + 1, a + n + 2, a, a + n + 2, a + n + 1]
+    fmt = lambda v: " ".join(f"{x:.6g}" for x in v)
+    s += ('AttributeBegin\n  AreaLightSource "diffuse" "blackbody L" [5000 12]\n'
+          f'  Shape "trianglemesh" "integer indices" [{" ".join(map(str, idx))}]\n    "point P" [{fmt(P)}]\nAttributeEnd\n')
+    s += f'AttributeBegin\n  Material "matte" "spectrum Kd" {WHITE}\n'
+    s += "  " + quad((-3, -1, 3), (3, -1, 3), (3, -1, -3), (-3, -1, -3)) + "AttributeEnd\n"
+    s += (f'AttributeBegin\n  Material "matte" "spectrum Kd" {RED}\n  Translate -.8 -.55 0\n'
+          '  Shape "sphere" "float radius" [.45]\nAttributeEnd\n')
+    s += ('AttributeBegin\n  Material "plastic" "spectrum Kd" [400 .2 700 .6] "float roughness" [.1]\n  Translate .7 -.6 .3\n'
+          '  Shape "sphere" "float radius" [.4]\nAttributeEnd\n')
+    return s + "WorldEnd\n"
+
+
 def cornell(opts, out):
     cam = 'LookAt 0 0 3.8  0 0 0  0 1 0\nCamera "perspective" "float fov" [39]'
     return header(opts, cam, os.path.splitext(os.path.basename(out))[0]) + cornell_world()
@@ -428,6 +458,8 @@ def main(argv):
         text = envbox(opts, out)
     elif name == "texbox":
         text = texbox(opts, out)
+    elif name == "manylights":
+        text = manylights(opts, out)
     elif name == "furnace_point":
         text = furnace(opts, out, False)
     elif name == "furnace_area":

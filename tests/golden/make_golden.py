@@ -54,6 +54,7 @@ SCENES = {
     "texbox": dict(gen=["texbox", "res=64x48", "spp=16"], res=(64, 48), spp=16),
     "texbox_lens": dict(gen=["texbox", "res=64x48", "spp=16", "lens=.06", "strategy=power"], res=(64, 48), spp=16),
     "texbox_real": dict(gen=["texbox", "res=48x48", "spp=8", "camera=realistic", "strategy=uniform"], res=(48, 48), spp=8),
+    "manylights": dict(gen=["manylights", "res=48x36", "spp=8"], res=(48, 36), spp=8),
     "envbox_map": dict(gen=["envbox", "res=64x48", "spp=16", "env=map", "strategy=power"], res=(64, 48), spp=16),
     "killeroo128": dict(ref="killeroo-simple.pbrt", res=(128, 128), spp=8),
     # crop = croppedPixelBounds (ceil(res * cropwindow), core/film.cpp:57-63): the film / .dat size
