@@ -197,11 +197,18 @@ bool Builder::CheckMaterialTextures(const Material *m) {
         // Lambertian, Trowbridge-Reitz microfacet and specular reflection with
         // a dielectric Fresnel term, SpecularTransmission for Kt)
         if (x->bumpMap) return Fail("uber: bumpmap is not supported");
-        if (!IsConstant(x->Kd) || !IsConstant(x->Ks) || !IsConstant(x->Kr) ||
+        if ((!IsConstant(x->Kd) && !AsImage(x->Kd)) || !IsConstant(x->Ks) || !IsConstant(x->Kr) ||
             !IsConstant(x->Kt) || !IsConstant(x->opacity) ||
             !IsConstant(x->roughness) || !IsConstant(x->roughnessu) ||
             !IsConstant(x->roughnessv) || !IsConstant(x->eta))
-            return Fail("uber: only constant textures are supported");
+            return Fail("uber: only constant textures (and an imagemap Kd) are supported");
+        if (AsImage(x->Kd)) {
+            // kd = opacity * Kd (uber.cpp:52-57): the device takes the texture's value as it is
+            SurfaceInteraction si;
+            const Spectrum op = x->opacity->Evaluate(si);
+            for (int i = 0; i < nSpectralSamples; ++i)
+                if (op[i] != 1.f) return Fail("uber: an imagemap Kd needs opacity 1");
+        }
         return true;
     }
     if (auto *x = dynamic_cast<const TranslucentMaterial *>(m)) {
@@ -394,6 +401,8 @@ int Builder::AddMaterial(const Material *m) {
         kdSlot = const_cast<std::shared_ptr<Texture<Spectrum>> *>(&x->Kd);
     else if (auto *x = dynamic_cast<const PlasticMaterial *>(m))
         kdSlot = const_cast<std::shared_ptr<Texture<Spectrum>> *>(&x->Kd);
+    else if (auto *x = dynamic_cast<const UberMaterial *>(m))
+        kdSlot = const_cast<std::shared_ptr<Texture<Spectrum>> *>(&x->Kd);
     int texBlock = -1;
     std::shared_ptr<Texture<Spectrum>> savedKd;
     if (kdSlot && AsImage(*kdSlot)) {
@@ -435,6 +444,14 @@ int Builder::AddMaterial(const Material *m) {
             return -2;
         }
         l0.R = SPTX_TEX_ROW(texBlock);
+        // the device's textured shading variant evaluates Lambert and microfacet-reflection lobes
+        for (int i = 0; i < fm.n_lobes; ++i) {
+            const int ty = fs->lobes[(size_t)fm.first_lobe + i].type;
+            if (ty != SPTX_LOBE_LAMBERT && ty != SPTX_LOBE_MICROFACET_REFL) {
+                Fail("textured Kd: the material has lobes besides diffuse and glossy reflection (uber with Kr / Kt?)");
+                return -2;
+            }
+        }
     }
     int idx = (int)fs->materials.size();
     fs->materials.push_back(fm);

@@ -257,7 +257,10 @@ def texbox(opts, out):
     s += 'AttributeBegin\n  AreaLightSource "diffuse" "blackbody L" [5500 18]\n'
     s += "  " + quad((-.3, 1.6, -.3), (.3, 1.6, -.3), (.3, 1.6, .3), (-.3, 1.6, .3)) + "AttributeEnd\n"
     s += 'LightSource "point" "point from" [-2 1.5 2] "blackbody I" [4000 6]\n'
-    s += 'AttributeBegin\n  Material "matte" "texture Kd" "floor"\n'
+    floor_mat = 'Material "matte" "texture Kd" "floor"'
+    if opts.get("floor") == "uber":  # UberMaterial with a textured Kd: Lambert + Trowbridge-Reitz lobes
+        floor_mat = 'Material "uber" "texture Kd" "floor" "spectrum Ks" [400 .2 700 .2] "float roughness" [.15]'
+    s += f'AttributeBegin\n  {floor_mat}\n'
     s += "  " + quad((-3, -1, 3), (3, -1, 3), (3, -1, -6), (-3, -1, -6), uv=(0, 0, 1, 0, 1, 1, 0, 1)) + "AttributeEnd\n"
     s += f'AttributeBegin\n  Material "matte" "spectrum Kd" {WHITE}\n'
     s += "  " + quad((-3, -1, -6), (3, -1, -6), (3, 3, -6), (-3, 3, -6)) + "AttributeEnd\n"

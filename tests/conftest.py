@@ -17,7 +17,7 @@ if ROOT not in sys.path:
 GOLD = os.path.join(ROOT, "tests", "golden")
 GEN = os.path.join(ROOT, "scenes", "_gen")
 SCENES = ["cornell64", "cornell_lens48", "instanced", "furnace_point", "furnace_area", "killeroo128", "zoo",
-          "zoo_gauss", "uber_box", "lobes_box", "cornell_sobol", "envbox_const", "envbox_map", "texbox", "texbox_lens", "texbox_real", "manylights"]
+          "zoo_gauss", "uber_box", "lobes_box", "cornell_sobol", "envbox_const", "envbox_map", "texbox", "texbox_lens", "texbox_real", "texbox_uber", "manylights"]
 
 
 def pytest_configure(config):

@@ -53,6 +53,7 @@ SCENES = {
     "envbox_const": dict(gen=["envbox", "res=64x48", "spp=16", "env=const"], res=(64, 48), spp=16),
     "texbox": dict(gen=["texbox", "res=64x48", "spp=16"], res=(64, 48), spp=16),
     "texbox_lens": dict(gen=["texbox", "res=64x48", "spp=16", "lens=.06", "strategy=power"], res=(64, 48), spp=16),
+    "texbox_uber": dict(gen=["texbox", "res=56x40", "spp=8", "floor=uber", "strategy=power"], res=(56, 40), spp=8),
     "texbox_real": dict(gen=["texbox", "res=48x48", "spp=8", "camera=realistic", "strategy=uniform"], res=(48, 48), spp=8),
     "manylights": dict(gen=["manylights", "res=48x36", "spp=8"], res=(48, 36), spp=8),
     "envbox_map": dict(gen=["envbox", "res=64x48", "spp=16", "env=map", "strategy=power"], res=(64, 48), spp=16),

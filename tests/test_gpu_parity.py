@@ -92,7 +92,10 @@ def test_camera_rays(scene):
 # different value (all of them > 1e-3: discrete events, not drift -- a 1-ulp difference between the
 # device's and glibc's sinf / cosf in the sampled point of the sphere light or in the microfacet
 # half vector decides a grazing shadow ray on the finely tessellated mesh the other way).
-LI_ALLOWED_ABOVE_1E4 = {"killeroo128": 3e-3}
+# texbox_uber (glossy textured floor, roughness .15): 2 of 2048 samples between 1e-4 and 1e-3 -- the
+# Trowbridge-Reitz visible-normal sample (TrowbridgeReitzSample11) amplifies the last bits of its
+# inputs near grazing angles; none above 1e-3, render relRMSE 1e-6 (tools/diag_shade.py texbox_uber).
+LI_ALLOWED_ABOVE_1E4 = {"killeroo128": 3e-3, "texbox_uber": 2e-3}
 
 
 def test_per_sample_radiance(scene):
