@@ -55,13 +55,10 @@ __global__ void k_generate(DScene S, DCamera C, DSampler H, PathArrays A, Render
         A.info[i] = pack_info(0, 0, startDim);
         A.pfilm[i] = make_float2(pFilm.x, pFilm.y);
         A.spill[i] = 0;
-        // path-major spectra: 32 floats (one 128-byte line) per path
-        float4 *b4 = reinterpret_cast<float4 *>(A.beta[0] + (size_t)i * SPTX_SPECTRUM_STRIDE);
+        // path-major spectra: 32 floats (one 128-byte line) per path.  (beta = 1 at the camera vertex is
+        // not stored: RenderParams::betaOnes tells K3 / K4b of bounce 0)
         float4 *l4 = reinterpret_cast<float4 *>(A.L + (size_t)i * SPTX_SPECTRUM_STRIDE);
-        for (int q = 0; q < SPTX_SPECTRUM_STRIDE / 4; ++q) {
-            b4[q] = make_float4(1.f, 1.f, 1.f, 1.f);
-            l4[q] = make_float4(0.f, 0.f, 0.f, 0.f);
-        }
+        for (int q = 0; q < SPTX_SPECTRUM_STRIDE / 4; ++q) l4[q] = make_float4(0.f, 0.f, 0.f, 0.f);
         queue_push(A.q[0], A.counters + 0, (int)i, w > 0);
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&cnt->cameraRays, (unsigned long long)nPaths);

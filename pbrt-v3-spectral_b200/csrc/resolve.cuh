@@ -52,7 +52,7 @@ k_mis(DScene S, PathArrays A, DeviceCounters *cnt) {
 // correctly rounded reciprocal instead of an IEEE division per bin (11 % of the kernel's instructions).
 template <bool COUNT, bool FAST>
 __global__ void __launch_bounds__(kBlock, SPTX_ANYHIT_BLOCKS)
-k_resolve(DScene S, PathArrays A, int betaIn, DeviceCounters *cnt) {
+k_resolve(DScene S, PathArrays A, int betaIn, int betaOnes, DeviceCounters *cnt) {
     TravCounters tc{0, 0};
     const int n = A.counters[2];
     const float *beta = A.beta[betaIn];
@@ -94,7 +94,7 @@ k_resolve(DScene S, PathArrays A, int betaIn, DeviceCounters *cnt) {
                 at[j] = (size_t)ip * SPTX_SPECTRUM_STRIDE + lane;
                 va[j] = (on[j] && ((mA >> p) & 1u)) ? A.fa[at[j]] : 0.f;
                 vb[j] = (on[j] && ((mB >> p) & 1u)) ? A.fb[at[j]] : 0.f;
-                bt[j] = on[j] ? beta[at[j]] : 0.f;
+                bt[j] = on[j] ? (betaOnes ? 1.f : beta[at[j]]) : 0.f;
                 Lv[j] = on[j] ? A.L[at[j]] : 0.f;
                 // Ld = Spectrum(0) + fa + fb in the order EstimateDirect adds them
                 float Ld = 0.f;

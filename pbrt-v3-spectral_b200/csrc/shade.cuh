@@ -192,7 +192,7 @@ k_shade(const DScene *__restrict__ Sp, const DSampler *__restrict__ Hp, PathArra
             const float4 ra = sState[0][t], rb = sState[1][t];
             const float4 ha = sState[2][t], hb = sState[3][t];
             const float4 sx = sState[4][t];
-            prefetch_l2(A.beta[betaIn] + (size_t)i * SPTX_SPECTRUM_STRIDE);
+            if (!R.betaOnes) prefetch_l2(A.beta[betaIn] + (size_t)i * SPTX_SPECTRUM_STRIDE);
             {   // the next chunk of this block
                 const int kn = k + (int)(gridDim.x * blockDim.x);
                 if (kn < n) iNext = queue[kn];
@@ -408,7 +408,7 @@ k_shade(const DScene *__restrict__ Sp, const DSampler *__restrict__ Hp, PathArra
                 const float ad = absdot(wi, it.ns);
                 float4 bRow[8];
 #pragma unroll
-                for (int c = 0; c < 8; ++c) bRow[c] = bIn.ldro(c);
+                for (int c = 0; c < 8; ++c) bRow[c] = R.betaOnes ? make_float4(1.f, 1.f, 1.f, 1.f) : bIn.ldro(c);
 #pragma unroll
                 for (int c = 0; c < 8; ++c) {
                     const float4 fv = fsum4<LOBES>(S, f, c), b = bRow[c];
@@ -461,7 +461,7 @@ k_shade(const DScene *__restrict__ Sp, const DSampler *__restrict__ Hp, PathArra
             const Row4 Lr = row4(A.L, i), br = row4(A.beta[betaIn], i);
             for (int c = 0; c < 8; ++c) {
                 float4 l = Lr.ld(c);
-                const float4 b = br.ldro(c), e = spec4(S, emitRow, c);
+                const float4 b = R.betaOnes ? make_float4(1.f, 1.f, 1.f, 1.f) : br.ldro(c), e = spec4(S, emitRow, c);
                 l.x += b.x * e.x;
                 l.y += b.y * e.y;
                 l.z += b.z * e.z;
@@ -506,7 +506,7 @@ __global__ void k_shade_miss(const DScene *__restrict__ Sp, PathArrays A, Render
                     const EnvRgb e = env_le(S, S.lights[S.infinite[j]], d);
                     for (int c = 0; c < 8; ++c) {
                         float4 l = Lr.ld(c);
-                        const float4 b = br.ldro(c), le = env_bin4(S, e, c);
+                        const float4 b = R.betaOnes ? make_float4(1.f, 1.f, 1.f, 1.f) : br.ldro(c), le = env_bin4(S, e, c);
                         l.x += b.x * le.x;
                         l.y += b.y * le.y;
                         l.z += b.z * le.z;

@@ -1223,6 +1223,7 @@ static int render_pixels(sptx_ctx *ctx, int s0, int s1, const int *dSampleList =
             R.pixels = dPixels + p0;
             R.sampleList = dSampleList;
             R.ignoreRayWeight = ctx->metadataStrategy && !dSampleList;
+            R.betaOnes = 0;
             const int64_t nPaths = (int64_t)nPix * R.samplesInPass;
             const int g = grid_for(ctx, nPaths);
             if (ctx->metadataStrategy && !dSampleList) {
@@ -1265,6 +1266,7 @@ static int render_pixels(sptx_ctx *ctx, int s0, int s1, const int *dSampleList =
                         k_intersect<false><<<g, kBlock, 0, ctx->stream>>>(ctx->S, A, qi, ctx->dCnt);
                     toc();
                     tic(2);
+                    R.betaOnes = bounce == 0;
                     const bool env = ctx->S.n_infinite > 0;
                     const int nk = (ctx->shadeExact ? (env ? shade_exact_env::launch_shade : shade_exact::launch_shade)
                                                     : (env ? shade_fast_env::launch_shade : shade_fast::launch_shade))(
@@ -1277,15 +1279,15 @@ static int render_pixels(sptx_ctx *ctx, int s0, int s1, const int *dSampleList =
                         if (cv) {
                             k_mis<true><<<g, kBlock, 0, ctx->stream>>>(ctx->S, A, ctx->dCnt);
                             if (ctx->shadeExact)
-                                k_resolve<true, false><<<g, kBlock, 0, ctx->stream>>>(ctx->S, A, betaIn, ctx->dCnt);
+                                k_resolve<true, false><<<g, kBlock, 0, ctx->stream>>>(ctx->S, A, betaIn, bounce == 0, ctx->dCnt);
                             else
-                                k_resolve<true, true><<<g, kBlock, 0, ctx->stream>>>(ctx->S, A, betaIn, ctx->dCnt);
+                                k_resolve<true, true><<<g, kBlock, 0, ctx->stream>>>(ctx->S, A, betaIn, bounce == 0, ctx->dCnt);
                         } else {
                             k_mis<false><<<g, kBlock, 0, ctx->stream>>>(ctx->S, A, ctx->dCnt);
                             if (ctx->shadeExact)
-                                k_resolve<false, false><<<g, kBlock, 0, ctx->stream>>>(ctx->S, A, betaIn, ctx->dCnt);
+                                k_resolve<false, false><<<g, kBlock, 0, ctx->stream>>>(ctx->S, A, betaIn, bounce == 0, ctx->dCnt);
                             else
-                                k_resolve<false, true><<<g, kBlock, 0, ctx->stream>>>(ctx->S, A, betaIn, ctx->dCnt);
+                                k_resolve<false, true><<<g, kBlock, 0, ctx->stream>>>(ctx->S, A, betaIn, bounce == 0, ctx->dCnt);
                         }
                         ++launches;
                         toc();

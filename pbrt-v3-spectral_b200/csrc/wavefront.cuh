@@ -84,6 +84,8 @@ struct RenderParams {
                          // weight still gates Li
     int band, nBands;    // SpectralPathIntegrator: this launch traces band `band` of `nBands`
     const int *sampleList;  // debug: explicit sample number per path (or NULL)
+    int betaOnes;  // this bounce's incoming throughput is 1 in every bin (the camera vertex): its rows are
+                   // neither written by K1 nor read by K3 / K4b
 };
 
 struct DeviceCounters {
