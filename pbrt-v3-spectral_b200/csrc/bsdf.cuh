@@ -238,6 +238,13 @@ SPTX_DEV float4 fsum4(const DScene &S, const FSumN<MAXT> &f, int c) {
     return v;
 }
 
+// The same as ONE function per kernel instead of a copy per row loop: for the variants whose terms
+// carry per-bin Fresnel / microfacet code (three row loops per vertex call it; shade.cuh).
+template <int LOBES, int MAXT>
+static __device__ __noinline__ float4 fsum4_call(const DScene &S, const FSumN<MAXT> &f, int c) {
+    return fsum4<LOBES, MAXT>(S, f, c);
+}
+
 // ---- local shading frame trigonometry, core/reflection.h:55-100 ------------
 SPTX_DEV float cos_theta(V3 w) { return w.z; }
 SPTX_DEV float cos2_theta(V3 w) { return w.z * w.z; }
@@ -259,14 +266,18 @@ SPTX_DEV float sin2_phi(V3 w) { return sin_phi(w) * sin_phi(w); }
 SPTX_DEV bool same_hemisphere(V3 a, V3 b) { return a.z * b.z > 0; }
 
 // ---- Trowbridge-Reitz, core/microfacet.cpp:155-184, 238-344 -----------------
-SPTX_NOINL float tr_D(float ax, float ay, V3 wh) {
+// Real functions (scalar / by-value arguments, no per-thread structs behind pointers): inlined at every
+// use they were a third of the plastic / metal variant's 25 000 instructions, a kernel whose top stall
+// was `no_instruction` (profiles/r02zz_step_ncu.txt).
+#define SPTX_CALL static __device__ __noinline__
+SPTX_CALL float tr_D(float ax, float ay, V3 wh) {
     float tan2Theta = tan2_theta(wh);
     if (isinf(tan2Theta)) return 0.f;
     const float cos4Theta = cos2_theta(wh) * cos2_theta(wh);
     float e = (cos2_phi(wh) / (ax * ax) + sin2_phi(wh) / (ay * ay)) * tan2Theta;
     return 1.f / (kPi * ax * ay * cos4Theta * (1.f + e) * (1.f + e));
 }
-SPTX_NOINL float tr_lambda(float ax, float ay, V3 w) {
+SPTX_CALL float tr_lambda(float ax, float ay, V3 w) {
     float absTanTheta = fabsf(tan_theta(w));
     if (isinf(absTanTheta)) return 0.f;
     float alpha = sqrtf(cos2_phi(w) * ax * ax + sin2_phi(w) * ay * ay);
@@ -277,7 +288,7 @@ SPTX_DEV float tr_G1(float ax, float ay, V3 w) { return 1.f / (1.f + tr_lambda(a
 SPTX_DEV float tr_G(float ax, float ay, V3 wo, V3 wi) {
     return 1.f / (1.f + tr_lambda(ax, ay, wo) + tr_lambda(ax, ay, wi));
 }
-SPTX_NOINL float tr_pdf(const sptx_lobe &L, V3 wo, V3 wh) {
+SPTX_CALL float tr_pdf(const sptx_lobe &L, V3 wo, V3 wh) {
     if (L.sample_visible)
         return tr_D(L.alpha_x, L.alpha_y, wh) * tr_G1(L.alpha_x, L.alpha_y, wo) * absdot(wo, wh) /
                abs_cos_theta(wo);
@@ -315,7 +326,7 @@ SPTX_DEV void tr_sample11(float cosTheta, float U1, float U2, float *slope_x, fl
               (U2 * (U2 * (U2 * 0.093073f + 0.309420f) - 1.000000f) + 0.597999f);
     *slope_y = Sg * z * sqrtf(1.f + *slope_x * *slope_x);
 }
-SPTX_NOINL V3 tr_sample_wh(const sptx_lobe &L, V3 wo, V2 u) {
+SPTX_CALL V3 tr_sample_wh(const sptx_lobe &L, V3 wo, V2 u) {
     const float ax = L.alpha_x, ay = L.alpha_y;
     V3 wh;
     if (!L.sample_visible) {
