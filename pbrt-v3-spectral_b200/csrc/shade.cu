@@ -37,29 +37,29 @@ __global__ void k_stage_clocks_print() {
 #endif
 
 template <int V>
-static void launch_variant(cudaStream_t stream, int grid, const DScene *dS, const DSampler *dH, const PathArrays &A,
+static void launch_variant(cudaStream_t stream, int grid, const DScene &hS, const DSampler &hH, const PathArrays &A,
                            const RenderParams &R, int qi, int betaIn, int cls, DeviceCounters *cnt) {
-    k_shade<kVariantLobes[V], kVariantTerms[V]><<<grid, kShadeBlock, 0, stream>>>(dS, dH, A, R, qi, betaIn, cls, cnt);
+    k_shade<kVariantLobes[V], kVariantTerms[V]><<<grid, kShadeBlock, 0, stream>>>(hS, hH, A, R, qi, betaIn, cls, cnt);
 }
 
 // K3 for one bounce: one launch per shading class in use, each with the variant compiled for
 // the class's lobe types; one resident block per SM, a class queue is walked in block-sized
 // chunks.  Returns the number of kernels launched.
-int launch_shade(cudaStream_t stream, int smCount, int64_t nPaths, const DScene *dS, const DSampler *dH,
+int launch_shade(cudaStream_t stream, int smCount, int64_t nPaths, const DScene &hS, const DSampler &hH,
                  const PathArrays &A, const RenderParams &R, int qi, int betaIn, const ShadePlan &plan,
                  DeviceCounters *cnt) {
     const int grid = (int)std::min<int64_t>((nPaths + kShadeBlock - 1) / kShadeBlock,
                                             (int64_t)smCount * kShadeBlocksPerSM);
     int launches = 1;
-    // (class 0 has work only with bands or infinite lights; dS says which, the grid is sized for either)
-    k_shade_miss<<<std::max(1, std::min(grid, smCount * 4)), 256, 0, stream>>>(dS, A, R, betaIn, cnt);
+    // (class 0 has work only with bands or infinite lights; the scene says which, the grid is sized for either)
+    k_shade_miss<<<std::max(1, std::min(grid, smCount * 4)), 256, 0, stream>>>(hS, A, R, betaIn, cnt);
     for (int cls = 1; cls < kShadeClasses; ++cls) {
         switch (plan.variant[cls]) {
-        case 0: launch_variant<0>(stream, grid, dS, dH, A, R, qi, betaIn, cls, cnt); break;
-        case 1: launch_variant<1>(stream, grid, dS, dH, A, R, qi, betaIn, cls, cnt); break;
-        case 2: launch_variant<2>(stream, grid, dS, dH, A, R, qi, betaIn, cls, cnt); break;
-        case 3: launch_variant<3>(stream, grid, dS, dH, A, R, qi, betaIn, cls, cnt); break;
-        case 4: launch_variant<4>(stream, grid, dS, dH, A, R, qi, betaIn, cls, cnt); break;
+        case 0: launch_variant<0>(stream, grid, hS, hH, A, R, qi, betaIn, cls, cnt); break;
+        case 1: launch_variant<1>(stream, grid, hS, hH, A, R, qi, betaIn, cls, cnt); break;
+        case 2: launch_variant<2>(stream, grid, hS, hH, A, R, qi, betaIn, cls, cnt); break;
+        case 3: launch_variant<3>(stream, grid, hS, hH, A, R, qi, betaIn, cls, cnt); break;
+        case 4: launch_variant<4>(stream, grid, hS, hH, A, R, qi, betaIn, cls, cnt); break;
         default: continue;  // no primitive of the scene is in this class
         }
         ++launches;

@@ -131,10 +131,10 @@ SPTX_NOINL void camera_differentials(const DScene &S, const DSampler &H, uint64_
 
 template <int LOBES, int MAXT>
 __global__ void __launch_bounds__(kShadeBlock, kShadeBlocksPerSM)
-k_shade(const DScene *__restrict__ Sp, const DSampler *__restrict__ Hp, PathArrays A, RenderParams R,
+k_shade(const __grid_constant__ DScene S, const __grid_constant__ DSampler H, PathArrays A, RenderParams R,
         int qi, int betaIn, int cls, DeviceCounters *cnt) {
-    const DScene &S = *Sp;
-    const DSampler &H = *Hp;
+    // (S and H are read from the kernel's parameter bank: a table pointer or a sampler constant costs
+    //  no load.  __grid_constant__ lets the out-of-line helpers take their address without a local copy.)
     const int n = A.counters[kClassCounter0 + cls];
     const int nChunks = (n + (int)blockDim.x - 1) / (int)blockDim.x;
     const int *queue = A.qc + (size_t)cls * A.capacity;
@@ -507,9 +507,8 @@ k_shade(const DScene *__restrict__ Sp, const DSampler *__restrict__ Hp, PathArra
 // Class 0: paths whose ray left the scene.  PathIntegrator::Li adds the infinite lights' emission
 // (camera rays and rays leaving a specular bounce) and ends them; with SpectralPathIntegrator bands
 // the next band still needs the sampler dimension the path stopped at.
-__global__ void k_shade_miss(const DScene *__restrict__ Sp, PathArrays A, RenderParams R, int betaIn,
+__global__ void k_shade_miss(const __grid_constant__ DScene S, PathArrays A, RenderParams R, int betaIn,
                              DeviceCounters *cnt) {
-    const DScene &S = *Sp;
     const int n = A.counters[kClassCounter0];
     if (R.nBands > 1 || (kShadeEnv && S.n_infinite > 0))
         for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {

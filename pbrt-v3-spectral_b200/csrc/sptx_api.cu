@@ -20,7 +20,7 @@ using namespace sptx;
 namespace sptx {  // shade.cu, compiled once per arithmetic mode, with and without Light "infinite"
 #define SPTX_DECLARE_SHADE(ns)                                                                                  \
     namespace ns {                                                                                              \
-    int launch_shade(cudaStream_t stream, int smCount, int64_t nPaths, const DScene *dS, const DSampler *dH,   \
+    int launch_shade(cudaStream_t stream, int smCount, int64_t nPaths, const DScene &hS, const DSampler &hH,   \
                      const PathArrays &A, const RenderParams &R, int qi, int betaIn, const ShadePlan &plan,    \
                      DeviceCounters *cnt);                                                                      \
     }
@@ -1270,7 +1270,7 @@ static int render_pixels(sptx_ctx *ctx, int s0, int s1, const int *dSampleList =
                     const bool env = ctx->S.n_infinite > 0;
                     const int nk = (ctx->shadeExact ? (env ? shade_exact_env::launch_shade : shade_exact::launch_shade)
                                                     : (env ? shade_fast_env::launch_shade : shade_fast::launch_shade))(
-                        ctx->stream, ctx->smCount, nPaths, ctx->dS, ctx->dH, A, R, qi, betaIn, ctx->shadePlan,
+                        ctx->stream, ctx->smCount, nPaths, ctx->S, ctx->H, A, R, qi, betaIn, ctx->shadePlan,
                         ctx->dCnt);
                     toc();
                     launches += nk - 1;
