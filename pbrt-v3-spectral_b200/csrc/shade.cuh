@@ -78,9 +78,13 @@ __device__ unsigned long long g_stageClocks[32];
 // Which stage ends carry the barrier (bit s = after slot s).  Measured on one 4-spp pass of the
 // bench scene (shade ms): none 11.97, 0x01 9.39, 0x04 9.24, 0x10 9.13, 0x40 8.85, 0x100 9.31,
 // 0x11 9.56 (the previous setting), 0x44 9.21, 0x50 8.99, 0x140 9.40, 0x41 9.46 -- one barrier,
-// after the f / pdf / fa-row stage, is best; C1 -2.5 %, C3 -7.7 % with it as well.
+// after the f / pdf / fa-row stage, was best in round 1 (C1 -2.5 %, C3 -7.7 % with it as well).
+// End of round 2 (per-class variants, state staged through shared memory, descriptors in the
+// parameter bank, out-of-line microfacet helpers -- the code a warp walks per vertex is a third of
+// what it was): shade ms per bench step with mask 0 / 0x04 / 0x10 / 0x40 = 78.3 / 81.0 / 80.2 / 79.7.
+// No barrier.
 #ifndef SPTX_STAGE_MASK
-#define SPTX_STAGE_MASK 0x40
+#define SPTX_STAGE_MASK 0
 #endif
 #define SPTX_STAGE(slot)                                       \
     do {                                                       \
