@@ -140,7 +140,6 @@ k_shade(const __grid_constant__ DScene S, const __grid_constant__ DSampler H, Pa
     // (S and H are read from the kernel's parameter bank: a table pointer or a sampler constant costs
     //  no load.  __grid_constant__ lets the out-of-line helpers take their address without a local copy.)
     const int n = A.counters[kClassCounter0 + cls];
-    const int nChunks = (n + (int)blockDim.x - 1) / (int)blockDim.x;
     const int *queue = A.qc + (size_t)cls * A.capacity;
     const int noSpec = BSDF_ALL & ~BSDF_SPECULAR;
 #ifdef SPTX_STAGE_CLOCKS
@@ -163,14 +162,15 @@ k_shade(const __grid_constant__ DScene S, const __grid_constant__ DSampler H, Pa
     };
     int iCur = -1;
     {
-        const int k0 = (int)blockIdx.x * (int)blockDim.x + (int)threadIdx.x;
-        if (blockIdx.x < nChunks && k0 < n) {
+        const int k0 = (int)blockIdx.x * kShadeBlock + (int)threadIdx.x;
+        if (k0 < n) {
             iCur = queue[k0];
             stage_state(iCur);
         }
     }
-    for (int chunk = blockIdx.x; chunk < nChunks; chunk += gridDim.x) {
-        const int k = chunk * (int)blockDim.x + (int)threadIdx.x;
+    // (one block-uniform induction variable: the chunk's first queue entry)
+    for (int c0 = (int)blockIdx.x * kShadeBlock; c0 < n; c0 += (int)gridDim.x * kShadeBlock) {
+        const int k = c0 + (int)threadIdx.x;
         bool alive = k < n;
         const bool valid = alive;
         int i = 0, iNext = -1;
@@ -203,7 +203,7 @@ k_shade(const __grid_constant__ DScene S, const __grid_constant__ DSampler H, Pa
             const float4 sx = sState[4][t];
             if (!R.betaOnes) prefetch_l2(A.beta[betaIn] + (size_t)i * SPTX_SPECTRUM_STRIDE);
             {   // the next chunk of this block
-                const int kn = k + (int)(gridDim.x * blockDim.x);
+                const int kn = k + (int)gridDim.x * kShadeBlock;
                 if (kn < n) iNext = queue[kn];
             }
             ray.o = mk(ra.x, ra.y, ra.z);
