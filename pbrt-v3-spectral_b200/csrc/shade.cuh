@@ -6,9 +6,11 @@
 // One thread per path.  K2 hands the paths over sorted by shading class (one class per
 // material lobe signature), and K3 is launched once per class with the kernel VARIANT compiled
 // for that class's lobe types: a matte vertex runs code that contains no specular, microfacet or
-// Fresnel branch at all, a glass / mirror vertex code without next-event estimation.  No shared
-// memory is used (the L1 keeps the whole carve-out for the per-thread interaction / BSDF state).
-// Spectra are path-major ([P][32] floats): a thread moves its 128-byte rows as float4.
+// Fresnel branch at all, a glass / mirror vertex code without next-event estimation.  A block
+// walks its class queue in chunks; the scattered 76 bytes of path state of the NEXT chunk are
+// copied into shared memory (cp.async, 40 KB) while the current one is shaded.  The scene and
+// sampler descriptors are __grid_constant__ kernel parameters (table pointers come from the
+// parameter bank).  Spectra are path-major ([P][32] floats): a thread moves its 128-byte rows as float4.
 // The two rays EstimateDirect traces (shadow ray, BSDF-sampled MIS ray) are
 // written out with their per-bin contributions (fa, fb) and traced by K4.
 #pragma once
@@ -50,12 +52,10 @@ SPTX_DEV void cp_async4(void *smem, const void *g) {
 }
 SPTX_DEV void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
-// The vertex is cut into stages with a block barrier between them.  The
-// barriers are not needed for correctness: they keep the SM's warps inside the
-// same few KB of code, so that the instruction cache serves all of them from
-// one fetch (the kernel is ~200 KB of SASS and a warp walks most of it once per
-// vertex; free-running warps had a 53 % instruction-cache hit rate -- DESIGN.md 5).
-// One 512-thread block per SM (128 registers per thread).
+// The vertex is cut into stages.  In round 1 a block barrier between stages kept the SM's warps
+// inside the same few KB of code (the kernel was ~200 KB of SASS, free-running warps had a 53 %
+// instruction-cache hit rate -- DESIGN.md 5); the per-class variants of round 2 are a third of that
+// and run without barriers (SPTX_STAGE_MASK below).  One 512-thread block per SM (128 registers).
 #ifndef SPTX_SHADE_BLOCK
 #define SPTX_SHADE_BLOCK 512
 #endif
