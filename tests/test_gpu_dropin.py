@@ -25,6 +25,12 @@ CASES = {
     "zoo_gauss": ["zoo", "res=64x48", "spp=4", "strategy=uniform", "filter=gaussian"],
     "lobes_box": ["lobes_box", "res=64", "spp=16"],
     "meta_depth": ["instanced", "res=64", "spp=4", "grid=48", "inst=3", "metadata=depth"],
+    # SURVEY 8(f) rank 3 through the reference's own front end: image textures (PFM read by the host,
+    # MIPMap built by the reference's code, evaluated on the device), a mapped infinite light, and the
+    # many-light scene whose spatial light tables are sparse
+    "texbox_uber": ["texbox", "res=56x40", "spp=8", "floor=uber", "strategy=power"],
+    "envbox_map": ["envbox", "res=64x48", "spp=16", "env=map", "strategy=power"],
+    "manylights": ["manylights", "res=48x36", "spp=8"],
 }
 
 
