@@ -75,17 +75,23 @@ k_resolve(DScene S, PathArrays A, int betaIn, int betaOnes, DeviceCounters *cnt)
                 ++nShadow;
             }
         }
-        // bin phase: the warp walks its paths, lane = bin; four paths per round so that
+        // bin phase: the warp walks its paths, lane = bin; a few paths per round so that
         // their rows are in flight together
         const unsigned mA = __ballot_sync(0xffffffffu, useA);
         const unsigned mB = __ballot_sync(0xffffffffu, useB);
         unsigned m = mA | mB;
         while (m) {
-            size_t at[4];
-            float sel[4], va[4], vb[4], bt[4], Lv[4];
-            bool on[4];
+// paths per round (their rows are in flight together).  Under the any-hit walk's 64-register cap:
+// K4 per bench step with 1 / 2 / 3 / 4 / 6 paths = 48.4 / 31.5 / 29.6 / 32.6 / 35.2 ms
+#ifndef SPTX_NEE_ROUND
+#define SPTX_NEE_ROUND 3
+#endif
+            constexpr int kRound = SPTX_NEE_ROUND;
+            size_t at[kRound];
+            float sel[kRound], va[kRound], vb[kRound], bt[kRound], Lv[kRound];
+            bool on[kRound];
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
+            for (int j = 0; j < kRound; ++j) {
                 on[j] = m != 0;
                 const int p = on[j] ? __ffs(m) - 1 : 0;
                 m &= m - 1;
@@ -103,7 +109,7 @@ k_resolve(DScene S, PathArrays A, int betaIn, int betaOnes, DeviceCounters *cnt)
                 va[j] = Ld;
             }
 #pragma unroll
-            for (int j = 0; j < 4; ++j)
+            for (int j = 0; j < kRound; ++j)
                 // (lane 31 is the row's pad word: its 0 / sel would take the division's slow path
                 //  alone, with the other 31 lanes waiting)
                 if (on[j] && lane < SPTX_NBINS)
