@@ -63,24 +63,44 @@ __global__ void k_voxel_tables(DScene S, const float *halton5, float *tables, co
         V3 vmin = mk(fminf(a.x, c.x), fminf(a.y, c.y), fminf(a.z, c.z));
         V3 vmax = mk(fmaxf(a.x, c.x), fmaxf(a.y, c.y), fmaxf(a.z, c.z));
         float *row = tables + r * (int64_t)(2 * n + 2);
-        for (int j = 0; j < n; ++j) row[j] = 0.f;
         const int nSamples = 128;
-        for (int i = 0; i < nSamples; ++i) {
-            const float *h = halton5 + 5 * i;
-            RefPoint ref;
-            ref.p = mk(lerpf(h[0], vmin.x, vmax.x), lerpf(h[1], vmin.y, vmax.y), lerpf(h[2], vmin.z, vmax.z));
-            ref.pError = mk(0, 0, 0);
-            ref.n = mk(0, 0, 0);
-            V2 u{h[3], h[4]};
-            for (int j = 0; j < n; ++j) {
-                LiSample ls = light_sample_li(S, S.lights[j], ref, u);
+        // lightContrib[j] += Li.y() / pdf over the sample points in ascending order, as the reference adds them
+        // (lightdistrib.cpp:258-274); the light loop is the outer one here so that the sum lives in a register.
+        // Li.y() of a plain spectrum row (every area light: divisor 0) is the same number for every sample
+        // point: it is evaluated once per row, with the same operations.
+        int yRow = -1;
+        float yOfRow = 0.f;
+        for (int j = 0; j < n; ++j) {
+            const sptx_light L = S.lights[j];
+            float acc = 0.f;
+            for (int i = 0; i < nSamples; ++i) {
+                const float *h = halton5 + 5 * i;
+                RefPoint ref;
+                ref.p = mk(lerpf(__ldg(h), vmin.x, vmax.x), lerpf(__ldg(h + 1), vmin.y, vmax.y),
+                           lerpf(__ldg(h + 2), vmin.z, vmax.z));
+                ref.pError = mk(0, 0, 0);
+                ref.n = mk(0, 0, 0);
+                V2 u{__ldg(h + 3), __ldg(h + 4)};
+                LiSample ls = light_sample_li(S, L, ref, u);
                 if (ls.pdf > 0) {
                     float yy = 0.f;
-                    if (!ls.black)
-                        for (int b = 0; b < SPTX_NBINS; ++b) yy += S.cie_y[b] * li_bin(S, ls, b);
-                    row[j] += y_finish(S, yy) / ls.pdf;
+                    if (!ls.black) {
+                        if (!ls.isEnv && ls.divisor == 0.f) {
+                            if (ls.spectrum != yRow) {
+                                float t = 0.f;
+                                for (int b = 0; b < SPTX_NBINS; ++b) t += S.cie_y[b] * spec(S, ls.spectrum, b);
+                                yRow = ls.spectrum;
+                                yOfRow = t;
+                            }
+                            yy = yOfRow;
+                        } else {
+                            for (int b = 0; b < SPTX_NBINS; ++b) yy += S.cie_y[b] * li_bin(S, ls, b);
+                        }
+                    }
+                    acc += y_finish(S, yy) / ls.pdf;
                 }
             }
+            row[j] = acc;
         }
         float sum = 0.f;
         for (int j = 0; j < n; ++j) sum += row[j];

@@ -68,7 +68,7 @@ struct sptx_ctx {
     int2 *dPixels = nullptr;
     int64_t dPixelsCap = 0;
     int64_t nPixels = 0;          // entries of dPixels in use
-    int pixelsKey[8] = {-1, 0, 0, 0, 0, 0, 0, 0};  // what dPixels holds: {kind, bounds / partition ...}
+    int pixelsKey[12] = {-1, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};  // what dPixels holds: {kind, bounds / partition ...}
     // grow-only device scratch of the entry points that stage host data (ray batches, .dat planes):
     // no cudaMalloc / cudaFree per call (both are device-wide synchronisation points)
     // peer films mapped through CUDA IPC, kept open between merges (opening a handle costs
@@ -713,7 +713,7 @@ extern "C" int sptx_upload_scene(sptx_ctx *ctx, const sptx_scene_desc *sc) {
     mark("validate+drain");
     recycle_pool(ctx, ctx->sceneAllocs);
     ctx->haveScene = false;
-    ctx->pixelsKey[0] = -1;
+    // (the pixel list of the previous scene stays: its key holds every bound it was made from)
     mark("free");
     std::vector<void *> &pool = ctx->sceneAllocs;
     DScene &S = ctx->S;
@@ -955,6 +955,8 @@ extern "C" int sptx_upload_scene(sptx_ctx *ctx, const sptx_scene_desc *sc) {
         C.film_extent[3] = y / 2;
     }
 
+    mark("camera");
+
     // ---- sampler ----
     DSampler &H = ctx->H;
     memset(&H, 0, sizeof(H));
@@ -991,6 +993,8 @@ extern "C" int sptx_upload_scene(sptx_ctx *ctx, const sptx_scene_desc *sc) {
         if ((rc = upload(ctx, pool, sc->prime_sums, (int64_t)4 * 52, &H.prime_sums))) return rc;
     }
 
+    mark("sampler");
+
     // ---- film ----
     DFilm &F = ctx->F;
     memset(&F, 0, sizeof(F));
@@ -1011,8 +1015,9 @@ extern "C" int sptx_upload_scene(sptx_ctx *ctx, const sptx_scene_desc *sc) {
     CK(cudaMemcpyAsync(ctx->dH, &ctx->H, sizeof(DSampler), cudaMemcpyHostToDevice, ctx->stream));
     CK(cudaGetLastError());
     CK(cudaStreamSynchronize(ctx->stream));
+    mark("film+drain");
     drop_spares(ctx);  // buffers of the previous scene this one did not take back
-    mark("sampler+film");
+    mark("drop spares");
     ctx->haveScene = true;
     return SPTX_OK;
 }
@@ -1141,7 +1146,7 @@ static int render_serial(sptx_ctx *ctx, const int32_t *bounds, int part, int nPa
 // Device pixel list of a render region.  `key` says what the list describes (rectangle, tile
 // partition): the list of the previous call is kept when the key is the same, so a caller that
 // renders the same region sample range after sample range pays for it once.
-static int set_pixels(sptx_ctx *ctx, const int key[8], const std::vector<int2> &pixels) {
+static int set_pixels(sptx_ctx *ctx, const int key[12], const std::vector<int2> &pixels) {
     const int64_t n = (int64_t)pixels.size();
     if (n > ctx->dPixelsCap) {
         CK(cudaStreamSynchronize(ctx->stream));
@@ -1161,7 +1166,7 @@ static int set_pixels(sptx_ctx *ctx, const int key[8], const std::vector<int2> &
     memcpy(ctx->pixelsKey, key, sizeof(ctx->pixelsKey));
     return SPTX_OK;
 }
-static bool have_pixels(const sptx_ctx *ctx, const int key[8]) {
+static bool have_pixels(const sptx_ctx *ctx, const int key[12]) {
     return key[0] >= 0 && memcmp(ctx->pixelsKey, key, sizeof(ctx->pixelsKey)) == 0;
 }
 
@@ -1366,9 +1371,10 @@ extern "C" int sptx_render(sptx_ctx *ctx, const int32_t *pixel_bounds, int sampl
     };
     clip(ctx->integ.pixel_bounds);  // the InsideExclusive(pixel, pixelBounds) test
     if (pixel_bounds) clip(pixel_bounds);
-    const int key[8] = {1, b[0], b[1], b[2], b[3], 0, 0, 0};
+    const int key[12] = {1, b[0], b[1], b[2], b[3], 0, 0, 0, 0, 0, 0, 0};
     if (!have_pixels(ctx, key)) {
         std::vector<int2> pixels;
+        pixels.reserve((size_t)std::max(0, b[2] - b[0]) * (size_t)std::max(0, b[3] - b[1]));
         for (int y = b[1]; y < b[3]; ++y)
             for (int x = b[0]; x < b[2]; ++x) pixels.push_back(make_int2(x, y));
         int rc = set_pixels(ctx, key, pixels);
@@ -1391,8 +1397,7 @@ extern "C" int sptx_render_tiles(sptx_ctx *ctx, int part, int n_parts, int sampl
     const int tileSize = 16;
     const int ntx = (sb[2] - sb[0] + tileSize - 1) / tileSize;
     const int nty = (sb[3] - sb[1] + tileSize - 1) / tileSize;
-    const int key[8] = {2, part, n_parts, sb[0] ^ (sb[2] << 16), sb[1] ^ (sb[3] << 16), pb[0] ^ (pb[2] << 16),
-                        pb[1] ^ (pb[3] << 16), 0};
+    const int key[12] = {2, part, n_parts, sb[0], sb[1], sb[2], sb[3], pb[0], pb[1], pb[2], pb[3], 0};
     if (!have_pixels(ctx, key)) {
         std::vector<int2> pixels;
         for (int ty = 0; ty < nty; ++ty)
@@ -2009,7 +2014,7 @@ extern "C" int sptx_debug_radiance(sptx_ctx *ctx, const int32_t *px, const int32
     std::vector<void *> pool;
     const int32_t *dS;
     int rc = upload(ctx, pool, sample, n, &dS);
-    const int noKey[8] = {-1, 0, 0, 0, 0, 0, 0, 0};
+    const int noKey[12] = {-1, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
     if (rc == SPTX_OK) rc = set_pixels(ctx, noKey, pixels);
     if (rc == SPTX_OK) rc = render_pixels(ctx, 0, 1, dS);
     free_pool(ctx, pool);
