@@ -370,6 +370,9 @@ def bench_ours(args):
                        if world > 1 else "single GPU",
                        "l2": "path state of a pass (4.2 M paths, ~3.7 GB) exceeds L2 between launches",
                        "shade_arithmetic": ctx.shade_arithmetic,
+                       "last_segment": "not traced after a non-specular event at bounces == maxdepth - 1: the "
+                                       "reference intersects it and uses nothing of it (path.cpp:86-102); "
+                                       "films are bit-identical",
                        "sample_numbers_of_rank": [emu_rank, emu_world] if emu else None},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "steps": e2e_steps,

@@ -411,6 +411,17 @@ k_shade(const __grid_constant__ DScene S, const __grid_constant__ DSampler H, Pa
             A.misB[i] = make_float4(misD.y, misD.z, __int_as_float(lightNum), __int_as_float(neeFlags));
         }
         SPTX_STAGE(8);
+        // The segment after the last scattering event (bounces + 1 == maxDepth) is traced by the reference
+        // only to add the emission it finds, and that is added after a specular bounce only (path.cpp:86-99,
+        // then the break at :102): after any other event the ray cannot change L, and the path ends here.
+        // A variant without specular lobes then has no use for the BSDF sample either -- unless the sample's
+        // next band continues the sampler stream where this path leaves it (nBands > 1).
+#ifndef SPTX_TRACE_DEAD_SEGMENTS
+        const bool lastScatter = bounces + 1 >= R.maxDepth;
+#else
+        const bool lastScatter = false;
+#endif
+        if (lastScatter && (LOBES & kSpecularLobes) == 0 && R.nBands == 1) alive = false;
         // ---- stage 4: BSDF sample for the next path segment (path.cpp:131-150) ----
         if (alive) {
             V3 wi;
@@ -465,6 +476,7 @@ k_shade(const __grid_constant__ DScene S, const __grid_constant__ DSampler H, Pa
                         }
                     }
                 }
+                if (lastScatter && !(flags & BSDF_SPECULAR)) alive = false;
 #ifdef SPTX_TRACE_PATH
                 if (R.sampleList && i == 0)
                     printf("TRACE b%d sampled flags %d pdf %.9g wi %.9g %.9g %.9g alive %d p %.9g %.9g %.9g n %.9g %.9g %.9g\n",
