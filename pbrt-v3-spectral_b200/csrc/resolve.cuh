@@ -15,6 +15,7 @@ __global__ void __launch_bounds__(kBlock, SPTX_TRAV_BLOCKS)
 k_mis(DScene S, PathArrays A, DeviceCounters *cnt) {
     TravCounters tc{0, 0};
     const int n = A.counters[4];
+    unsigned long long nTraced = 0;
     for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
         const int i = A.qMis[k];
         const float4 ma = A.misA[i], mb = A.misB[i];
@@ -22,6 +23,21 @@ k_mis(DScene S, PathArrays A, DeviceCounters *cnt) {
         Ray r{mk(ma.x, ma.y, ma.z), mk(ma.w, mb.x, mb.y), kInf};
         HitRec h;
         bool useB = false;
+        // The ray counts only if its closest hit is the sampled light's own shape.  Sphere::Pdf gives every
+        // direction the cone's density (shapes/sphere.cpp:294-306: no test of wi against the sphere), so for a
+        // sphere light nearly all of these rays pass beside it: the walk's own sphere test, run on the
+        // unshortened ray first, says so, and no closer hit can turn a miss of the shape into a hit of it.
+        // (Triangle lights never get here with such a ray: Shape::Pdf intersects the triangle.)
+#ifndef SPTX_TRACE_DEAD_SEGMENTS
+        {
+            const sptx_light &Ls = S.lights[lightNum];
+            if (S.lights_top_level && Ls.type == SPTX_LIGHT_DIFFUSE_AREA && Ls.shape_kind == SPTX_PRIM_SPHERE) {
+                SphereHit sh;
+                if (!sphere_test(S.spheres[Ls.shape], r, &sh)) continue;
+            }
+        }
+#endif
+        ++nTraced;
         if (!scene_intersect<COUNT>(S, r, &h, &tc)) {
             // the sampled ray leaves the scene: an infinite light's Le(ray) (core/integrator.cpp:204-205)
             useB = S.lights[lightNum].type == SPTX_LIGHT_INFINITE;
@@ -43,7 +59,8 @@ k_mis(DScene S, PathArrays A, DeviceCounters *cnt) {
         atomicAdd(&cnt->nodes[1], (unsigned long long)tc.nodes);
         atomicAdd(&cnt->tests[1], (unsigned long long)tc.tests);
     }
-    if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&cnt->closestRays, (unsigned long long)n);
+    for (int o = 16; o > 0; o >>= 1) nTraced += __shfl_down_sync(0xffffffffu, nTraced, o);
+    if ((threadIdx.x & 31) == 0 && nTraced) atomicAdd(&cnt->closestRays, nTraced);
 }
 
 // (any-hit needs fewer registers than closest-hit: 8 resident blocks at 64 registers measured

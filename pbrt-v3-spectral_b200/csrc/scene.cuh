@@ -37,6 +37,9 @@ struct DScene {
     int n_infinite;         // number of infinite lights; their indices in lights[]:
     int infinite[4];
     int n_bvhs;
+    // every primitive that carries an area light sits in the top-level aggregate (the reference drops area
+    // lights inside object instances, api.cpp:1377-1386): its shape can be tested with a world-space ray
+    int lights_top_level;
     // image textures' blocks (sptx_scene_desc::tex_floats), or NULL; the camera (device copy), which
     // the textured shading variant needs for the camera ray's differentials
     const float *tex;

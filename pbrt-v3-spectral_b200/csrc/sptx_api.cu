@@ -794,6 +794,11 @@ extern "C" int sptx_upload_scene(sptx_ctx *ctx, const sptx_scene_desc *sc) {
             S.infinite[S.n_infinite++] = (int)i;
         }
     S.n_bvhs = (int)sc->n_bvhs;
+    S.lights_top_level = sc->n_bvhs > 0;
+    for (int64_t p = 0; p < sc->n_prims && S.lights_top_level; ++p)
+        if (sc->prims[p].light >= 0 &&
+            (p < sc->bvhs[0].prim_base || p >= (int64_t)sc->bvhs[0].prim_base + sc->bvhs[0].n_prims))
+            S.lights_top_level = 0;
     for (int i = 0; i < SPTX_SPECTRUM_STRIDE; ++i) S.cie_y[i] = i < SPTX_NBINS ? sc->cie_y[i] : 0.f;
     S.y_scale_num = (float)(705 - 395);  // sampledLambdaEnd - sampledLambdaStart
     S.y_scale_den = (float)(sc->cie_y_integral * (float)SPTX_NBINS);
